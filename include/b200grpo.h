@@ -1,0 +1,244 @@
+/*
+ * b200grpo.h -- C ABI of libb200grpo.so: the trainer-side GRPO hot path of
+ * ServiceNow/PipelineRL-SWE re-built as hand-written sm_100a CUDA kernels.
+ *
+ * The reference has no FFI (it is pure Python over torch); the boundary it offers is the
+ * Python call signatures rl_step / populate_rl_data.  Each entry point
+ * below names the reference lines whose work it replaces, relative to
+ * /root/reference/pipelinerl/.  The Python mirror of those signatures lives in
+ * pipelinerl_swe_b200/ and reaches this library through ctypes only
+ * (INTEGRATION.md shows the binding).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), allocation
+ *     free (the caller passes workspace), re-entrant, and returns 0 on success or a
+ *     negative B200GRPO_E* code; b200grpo_last_error() gives a thread-local message;
+ *   - bf16 tensors are row-major with the given leading dimension in ELEMENTS;
+ *   - there is no CPU fallback: without a compute-capability-10.x device calls fail.
+ */
+#ifndef B200GRPO_H_
+#define B200GRPO_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200GRPO_ABI_VERSION 1
+
+enum {
+  B200GRPO_OK = 0,
+  B200GRPO_EINVAL = -1,    /* bad argument (shape, alignment, null pointer) */
+  B200GRPO_ECUDA = -2,     /* CUDA runtime / driver error */
+  B200GRPO_EWORKSPACE = -3,/* workspace too small */
+  B200GRPO_EARCH = -4      /* device is not sm_100 */
+};
+
+const char* b200grpo_last_error(void);
+int b200grpo_abi_version(void);
+
+/* ---------------------------------------------------------------------------------------
+ * K1  lm_head forward fused with online log-softmax / entropy / target gather.
+ * Replaces finetune/rl/__init__.py:197-208 (logits = lm_head(hidden); /temperature;
+ * log_softmax; softmax; entropy; gather) without materialising [tokens x vocab].
+ *
+ *   hidden  bf16 [M, H]   (ldh elements between rows)   rows = shifted token positions
+ *   weight  bf16 [Vloc,H] (ldw)                         this rank's vocab rows
+ *   targets i64  [M]      global vocab id scored at each row (input_ids[t+1])
+ *   v_offset              global id of weight row 0 (0 when the vocab is not sharded)
+ *   stats   f32  [M,4]    out: (max z, sum exp(z-max), sum exp(z-max)*z, z[target] or 0)
+ *                         with z = logit / temperature, over this rank's vocab rows
+ * ------------------------------------------------------------------------------------- */
+size_t b200grpo_lmhead_fwd_workspace(int M, int H, int Vloc);
+int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw,
+                        const int64_t* targets, int M, int H, int Vloc, int64_t v_offset,
+                        float inv_temperature, float* stats, void* workspace,
+                        size_t workspace_bytes, void* stream);
+
+/* Combine per-rank stats (all-gathered, [R, M, 4]) into per-token results.
+ * logprob = z_target - lse ; entropy = lse - (sum e*z)/(sum e)   (rl/__init__.py:202-208).
+ * R = 1 when the vocab is not sharded.  Outputs f32 [M]. */
+int b200grpo_lmhead_finalize(const float* stats, int R, int M, float* logprob, float* entropy,
+                             float* lse, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K3  per-token RL loss + all reductions + gradient coefficients in one launch.
+ * Replaces rl/__init__.py:152-181 (masks, segments), :213-292 (ratios, KL, surrogate,
+ * weights, loss), :294-313 (value loss), :315-375 (stats) and rl/utils.py:25-30,66-87.
+ * ------------------------------------------------------------------------------------- */
+typedef struct b200grpo_loss_cfg {
+  int32_t policy_loss;          /* 0 = "ppo", 1 = "reinforce"              (:269-283) */
+  int32_t use_advantages;       /* log_p_weights = advantages else rewards (:250)     */
+  int32_t relu_log_p_weights;   /* clamp(min=0)                            (:251-252) */
+  int32_t group_normalization;  /* weight = 1/group_tokens else 1/batch    (:220-225) */
+  int32_t overlong_filtering;   /* weight *= 1-overflow                    (:227-230) */
+  int32_t is_packed;            /* segments from position_ids==0           (:158-178) */
+  int32_t has_values;           /* value-head branch                       (:239-246) */
+  int32_t batch_size;           /* config.batch_size                                  */
+  float epsilon;                /* ratio clip                                         */
+  float clamp_log_ratio_ref_new;/* C                                       (:254-260) */
+  float kl_coef;                /* already linearly decayed                (:266)     */
+  float entropy_coef;           /* already linearly decayed                (:265)     */
+  float value_loss_coef;        /*                                         (:308)     */
+  float reserved;
+} b200grpo_loss_cfg;
+
+/* slots of the f64 metrics vector written by b200grpo_token_loss */
+enum {
+  B200GRPO_M_LOSS = 0,        /* final loss (policy + value_loss_coef*value)          */
+  B200GRPO_M_N_MASKED,        /* masks_shifted.sum()                                  */
+  B200GRPO_M_N_SEQ,           /* number of segments (packed) / rows (unpacked)        */
+  B200GRPO_M_NUM_NANS,        /* isnan(per-token loss).sum()                          */
+  B200GRPO_M_REWARD, B200GRPO_M_ENTROPY, B200GRPO_M_OLD_LP, B200GRPO_M_NEW_LP,
+  B200GRPO_M_REF_LP, B200GRPO_M_ADVANTAGE, B200GRPO_M_KL, B200GRPO_M_POLICY,
+  B200GRPO_M_SURR1, B200GRPO_M_SURR2, B200GRPO_M_RATIO, B200GRPO_M_RATIO_SUM,
+  B200GRPO_M_RATIO_SQ_SUM, B200GRPO_M_RATIO_REF_NEW, B200GRPO_M_RATIO_REF_OLD,
+  B200GRPO_M_CLAMP_REF_NEW, B200GRPO_M_CLAMP_NEW_OLD, B200GRPO_M_TOKEN_WEIGHT,
+  B200GRPO_M_VALUE_MEAN, B200GRPO_M_VALUE_LOSS, B200GRPO_M_VALUE_MSE,
+  B200GRPO_M_MAX_REWARD, B200GRPO_M_MIN_REWARD, B200GRPO_M_MAX_ADV, B200GRPO_M_MIN_ADV,
+  B200GRPO_M_MAX_KL, B200GRPO_M_MIN_KL, B200GRPO_M_MAX_TW, B200GRPO_M_MIN_TW,
+  B200GRPO_M_MAX_VALUE, B200GRPO_M_MIN_VALUE,
+  B200GRPO_M_FLAGS,           /* bit set of B200GRPO_F_* as a double                  */
+  B200GRPO_M_COUNT = 40
+};
+enum {
+  B200GRPO_F_NEW_LP_NONFINITE = 1,  /* assert :209 */
+  B200GRPO_F_REF_NEW_NONFINITE = 2, /* assert :237 */
+  B200GRPO_F_KL_NONFINITE = 4,      /* assert :264 */
+  B200GRPO_F_LOSS_NONFINITE = 8,    /* assert :313 */
+  B200GRPO_F_GROUP_TOKENS_LE0 = 16  /* assert :222 */
+};
+
+/* Inputs are the UN-shifted [rows, L] batch tensors (finetune/types.py:54-65); the
+ * kernel applies the [:,1:] shift itself.  logprob/entropy are [rows, L-1].
+ * values (nullable unless has_values) is [rows, L] f32.
+ * Outputs: metrics f64[B200GRPO_M_COUNT]; loss f32[1] (nullable; = metrics[0]);
+ * coef_lp/coef_ent f32[rows,L-1] = dLoss/dlogprob,
+ * dLoss/dentropy for an upstream gradient of 1; coef_value f32[rows,L] (nullable). */
+size_t b200grpo_token_loss_workspace(int rows, int L);
+int b200grpo_token_loss(const float* logprob, const float* entropy, const int64_t* labels,
+                        const int64_t* position_ids, const float* rewards,
+                        const float* advantages, const float* ref_logprobs,
+                        const float* old_logprobs, const float* group_tokens,
+                        const float* num_labels, const float* overflow, const float* values,
+                        int rows, int L, const b200grpo_loss_cfg* cfg_host, double* metrics,
+                        float* loss, float* coef_lp, float* coef_ent, float* coef_value, void* workspace,
+                        size_t workspace_bytes, void* stream);
+
+/* Segment boundaries exactly as rl/__init__.py:159-170: starts where position_ids==0 plus
+ * index 0, then T.  bounds i32[T+1] (capacity), n_bounds i32[1] = S+1.
+ * workspace: 4*ceil(T/1024) bytes. */
+int b200grpo_segment_bounds(const int64_t* position_ids, int T, int32_t* bounds,
+                            int32_t* n_bounds, void* workspace, size_t workspace_bytes,
+                            void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K2  lm_head backward.  Replaces autograd through rl/__init__.py:197-208:
+ *   dlogit[t,j] = (s/temperature) * ( coef_lp[t]*(1[j==target_t] - p[t,j])
+ *                                   - coef_ent[t]*p[t,j]*(logp[t,j] + entropy[t]) )
+ * recomputed tile by tile from hidden/weight and the saved lse (logits are never stored),
+ * written as bf16 to a workspace chunk, then dH = dlogits . W and dW = dlogits^T . hidden
+ * as tcgen05 GEMMs.  s = *grad_scale (device scalar, nullable = 1).
+ *   grad_hidden bf16 [M,H] (ldgh)   -- partial sum over this rank's vocab rows
+ *   grad_weight bf16 or f32 [Vloc,H] (ldgw); accumulate != 0 adds into it (f32 only)
+ * ------------------------------------------------------------------------------------- */
+size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc);
+int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw,
+                        const int64_t* targets, const float* lse, const float* entropy,
+                        const float* coef_lp, const float* coef_ent, const float* grad_scale,
+                        int M, int H, int Vloc, int64_t v_offset, float inv_temperature,
+                        void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw,
+                        int grad_weight_is_f32, int accumulate, void* workspace,
+                        size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K4  group-normalised advantages.  Replaces the pandas path rl/__init__.py:394-499.
+ * Per rollout row i (n_rows): reward f64 (rewards[0] of the row, :402), group_key i32
+ * (dense id of group_id+"_"+step_index, :395), row_offsets i64[n_rows+1] (token ranges),
+ * n_labels i32 (:487), has_eos u8 (:481-484).  token_rewards f64[total] (nullable: every
+ * token of a row then carries row_reward, the documented assumption at :401) feeds the
+ * numerator (:466).  Outputs f32[total]: advantages, group_tokens, num_labels, overflow.
+ * Group mean / ddof=1 std / mean length are computed in f64 like pandas (:408-416);
+ * a singleton group has std NaN -> 0 (:466).
+ * ------------------------------------------------------------------------------------- */
+size_t b200grpo_group_advantage_workspace(int n_rows, int n_groups);
+int b200grpo_group_advantage(const double* row_reward, const int32_t* group_key,
+                             const int64_t* row_offsets, const int32_t* n_labels,
+                             const uint8_t* has_eos, const double* token_rewards, int n_rows,
+                             int n_groups, int divide_by_std, float* advantages,
+                             float* group_tokens, float* num_labels, float* overflow,
+                             void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * K6  weight-update buckets.  Replaces the per-parameter loop of
+ * finetune_loop.py:236-248 (sender: param.data.bfloat16() + broadcast) and
+ * vllm1.py:81-94 (receiver: torch.empty + broadcast + load_weights) with a gather of many
+ * parameters into one contiguous bf16 bucket (and the scatter back).  The NCCL broadcast
+ * of the bucket itself is issued by the host layer on the same stream.
+ *   src_ptrs_host / dst_ptrs_host: n device pointers (host array); numel_host: n counts;
+ *   src_is_f32_host: per-tensor flag (fp32 master weights are cast to bf16 while packing).
+ *   table workspace: device scratch the call fills asynchronously from the host arrays
+ *   (the host arrays must stay valid until the stream reaches the kernel).
+ * ------------------------------------------------------------------------------------- */
+size_t b200grpo_bucket_workspace(int n_tensors);
+/* elements the bucket needs: every tensor is padded to a multiple of 8 elements (16 B) */
+int64_t b200grpo_bucket_numel(const int64_t* numel_host, int n_tensors);
+int b200grpo_bucket_pack(const void* const* src_ptrs_host, const int64_t* numel_host,
+                         const uint8_t* src_is_f32_host, int n_tensors, void* bucket_bf16,
+                         int64_t bucket_capacity, void* workspace, size_t workspace_bytes,
+                         void* stream);
+int b200grpo_bucket_unpack(const void* bucket_bf16, void* const* dst_ptrs_host,
+                           const int64_t* numel_host, const uint8_t* dst_is_f32_host,
+                           int n_tensors, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Host-buffer entry point (the end-to-end call): one GRPO logprob+loss forward/backward
+ * over a packed row whose inputs live in PINNED HOST memory.  Copies inputs to the device
+ * workspace, runs K1 -> finalize -> K3 -> K2 and copies metrics (f64[B200GRPO_M_COUNT])
+ * back, all on `stream`.  weight / grad_weight stay device resident (model state).
+ * Same math as calling the entry points above one by one.
+ * ------------------------------------------------------------------------------------- */
+typedef struct b200grpo_host_batch {
+  const void* hidden_bf16;       /* [L, H]  pinned host */
+  const int64_t* input_ids;      /* [L] */
+  const int64_t* labels;         /* [L] */
+  const int64_t* position_ids;   /* [L] */
+  const float* rewards;          /* [L] ... all f32 [L] below */
+  const float* advantages;
+  const float* ref_logprobs;
+  const float* old_logprobs;
+  const float* group_tokens;
+  const float* num_labels;
+  const float* overflow;
+} b200grpo_host_batch;
+
+size_t b200grpo_rl_step_host_workspace(int L, int H, int V);
+int b200grpo_rl_step_host(const b200grpo_host_batch* batch_host, int L, int H, int V,
+                          const void* weight, int64_t ldw, float temperature,
+                          const b200grpo_loss_cfg* cfg_host, void* grad_hidden_host_bf16,
+                          void* grad_weight, int grad_weight_is_f32, int accumulate,
+                          double* metrics_host, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Building block exposed for tests: C[M,N] = A . B^T-style GEMM on the same tcgen05
+ * mainloop the lm_head kernels use.  a_mn_major / b_mn_major select the operand layout:
+ *   0: operand is [rows = M or N, cols = K] (K contiguous)
+ *   1: operand is [rows = K, cols = M or N] (M/N contiguous)
+ * C is f32 (c_is_f32) or bf16, row-major [M, ldc]; accumulate adds into f32 C.
+ * ------------------------------------------------------------------------------------- */
+int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb,
+                       int b_mn_major, void* C, int64_t ldc, int c_is_f32, int accumulate,
+                       int M, int N, int K, void* stream);
+
+/* Tunables (for experiments from the test/bench harness; defaults are the shipped ones).
+ * name in {"fwd_splits","two_cta","gemm_stages","watchdog_ms"}; returns previous value. */
+int b200grpo_set_tunable(const char* name, int value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GRPO_H_ */

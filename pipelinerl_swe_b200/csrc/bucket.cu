@@ -1,0 +1,133 @@
+// K6: gather many parameters into one contiguous bf16 bucket (and scatter back), so the
+// trainer->actor weight update of /root/reference/pipelinerl/finetune_loop.py:236-248 and
+// vllm1.py:81-94 becomes a few large NCCL broadcasts instead of one launch + one
+// allocation per parameter.  HBM-bound byte copy: 4 B/element (bf16 in + bf16 out), or
+// 6 B/element when the source holds fp32 master weights (cast fused into the pack).
+// Every tensor starts on a 16-byte boundary inside the bucket (offsets rounded up to 8
+// elements) so both sides move 128-bit vectors.
+#include "common.cuh"
+#include <vector>
+
+namespace b200grpo {
+
+constexpr int BK_THREADS = 256;
+constexpr int BK_CHUNK = 8192;  // elements per work item (32 per thread)
+
+struct BucketEntry {
+  void* ptr;            // parameter storage (src for pack, dst for unpack)
+  int64_t numel;
+  int64_t bucket_off;   // element offset inside the bucket (multiple of 8)
+  int64_t chunk_start;  // first work item of this tensor
+  int32_t is_f32;
+  int32_t pad;
+};
+
+__device__ __forceinline__ int find_entry(const BucketEntry* tab, int n, int64_t chunk) {
+  int lo = 0, hi = n - 1;
+  while (lo < hi) {  // last entry with chunk_start <= chunk
+    const int mid = (lo + hi + 1) >> 1;
+    if (tab[mid].chunk_start <= chunk) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+template <bool PACK>
+__global__ void __launch_bounds__(BK_THREADS) bucket_kernel(const BucketEntry* __restrict__ tab, int n,
+                                                            int64_t total_chunks, __nv_bfloat16* bucket) {
+  for (int64_t chunk = blockIdx.x; chunk < total_chunks; chunk += gridDim.x) {
+    const BucketEntry e = tab[find_entry(tab, n, chunk)];
+    const int64_t begin = (chunk - e.chunk_start) * BK_CHUNK;
+    const int64_t end = min(begin + (int64_t)BK_CHUNK, e.numel);
+    __nv_bfloat16* b = bucket + e.bucket_off;
+    const bool vec_ok = ((uintptr_t)e.ptr & 15) == 0;
+    if (!e.is_f32) {
+      __nv_bfloat16* p = (__nv_bfloat16*)e.ptr;
+      const int64_t vend = vec_ok ? begin + ((end - begin) & ~7LL) : begin;
+      for (int64_t i = begin + threadIdx.x * 8LL; i < vend; i += BK_THREADS * 8LL) {
+        if (PACK) *(uint4*)(b + i) = __ldg((const uint4*)(p + i));
+        else *(uint4*)(p + i) = __ldg((const uint4*)(b + i));
+      }
+      for (int64_t i = vend + threadIdx.x; i < end; i += BK_THREADS) {
+        if (PACK) b[i] = p[i]; else p[i] = b[i];
+      }
+    } else {
+      float* p = (float*)e.ptr;  // fp32 master weights: cast while packing; unpack widens
+      const int64_t vend = vec_ok ? begin + ((end - begin) & ~7LL) : begin;
+      for (int64_t i = begin + threadIdx.x * 8LL; i < vend; i += BK_THREADS * 8LL) {
+        if (PACK) {
+          const float4 x = __ldg((const float4*)(p + i)), y = __ldg((const float4*)(p + i + 4));
+          __nv_bfloat162 o[4] = {__floats2bfloat162_rn(x.x, x.y), __floats2bfloat162_rn(x.z, x.w),
+                                 __floats2bfloat162_rn(y.x, y.y), __floats2bfloat162_rn(y.z, y.w)};
+          *(uint4*)(b + i) = *(uint4*)o;
+        } else {
+          const uint4 raw = __ldg((const uint4*)(b + i));
+          const __nv_bfloat162* o = (const __nv_bfloat162*)&raw;
+          const float2 f0 = __bfloat1622float2(o[0]), f1 = __bfloat1622float2(o[1]);
+          const float2 f2 = __bfloat1622float2(o[2]), f3 = __bfloat1622float2(o[3]);
+          *(float4*)(p + i) = make_float4(f0.x, f0.y, f1.x, f1.y);
+          *(float4*)(p + i + 4) = make_float4(f2.x, f2.y, f3.x, f3.y);
+        }
+      }
+      for (int64_t i = vend + threadIdx.x; i < end; i += BK_THREADS) {
+        if (PACK) b[i] = __float2bfloat16_rn(p[i]); else p[i] = __bfloat162float(b[i]);
+      }
+    }
+  }
+}
+
+static int run_bucket(bool pack, void* const* ptrs, const int64_t* numel, const uint8_t* is_f32, int n, void* bucket,
+                      int64_t capacity, void* workspace, size_t workspace_bytes, void* stream) {
+  if (int e = check_device_sm100()) return e;
+  B200_REQUIRE(n >= 0, "bucket: n_tensors < 0");
+  if (n == 0) return B200GRPO_OK;
+  B200_REQUIRE(ptrs && numel && bucket && workspace, "bucket: null pointer");
+  B200_REQUIRE(((uintptr_t)bucket & 15) == 0, "bucket: bucket must be 16-byte aligned");
+  if (workspace_bytes < b200grpo_bucket_workspace(n)) { set_error("bucket: workspace too small"); return B200GRPO_EWORKSPACE; }
+  std::vector<BucketEntry> tab(n);
+  int64_t off = 0, chunks = 0;
+  for (int i = 0; i < n; ++i) {
+    B200_REQUIRE(numel[i] >= 0 && (numel[i] == 0 || ptrs[i]), "bucket: tensor %d invalid", i);
+    tab[i] = BucketEntry{ptrs[i], numel[i], off, chunks, is_f32 ? (int32_t)is_f32[i] : 0, 0};
+    off += (numel[i] + 7) / 8 * 8;
+    chunks += (numel[i] + BK_CHUNK - 1) / BK_CHUNK;
+  }
+  B200_REQUIRE(capacity < 0 || off <= capacity, "bucket: needs %lld elements, capacity %lld", (long long)off, (long long)capacity);
+  if (chunks == 0) return B200GRPO_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA_OK(cudaMemcpyAsync(workspace, tab.data(), sizeof(BucketEntry) * n, cudaMemcpyHostToDevice, st));
+  int64_t grid = chunks;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  if (grid > cap) grid = cap;
+  if (pack) bucket_kernel<true><<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
+  else bucket_kernel<false><<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200GRPO_OK;
+}
+
+}  // namespace b200grpo
+
+using namespace b200grpo;
+
+extern "C" size_t b200grpo_bucket_workspace(int n_tensors) {
+  return align_up(sizeof(BucketEntry) * (size_t)(n_tensors > 0 ? n_tensors : 1), 256);
+}
+
+extern "C" int64_t b200grpo_bucket_numel(const int64_t* numel_host, int n_tensors) {
+  int64_t off = 0;
+  for (int i = 0; i < n_tensors; ++i) off += (numel_host[i] + 7) / 8 * 8;
+  return off;
+}
+
+extern "C" int b200grpo_bucket_pack(const void* const* src_ptrs_host, const int64_t* numel_host,
+                                    const uint8_t* src_is_f32_host, int n_tensors, void* bucket_bf16,
+                                    int64_t bucket_capacity, void* workspace, size_t workspace_bytes, void* stream) {
+  return run_bucket(true, (void* const*)src_ptrs_host, numel_host, src_is_f32_host, n_tensors, bucket_bf16,
+                    bucket_capacity, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200grpo_bucket_unpack(const void* bucket_bf16, void* const* dst_ptrs_host, const int64_t* numel_host,
+                                      const uint8_t* dst_is_f32_host, int n_tensors, void* workspace,
+                                      size_t workspace_bytes, void* stream) {
+  return run_bucket(false, dst_ptrs_host, numel_host, dst_is_f32_host, n_tensors, (void*)bucket_bf16, -1, workspace,
+                    workspace_bytes, stream);
+}

@@ -1,0 +1,71 @@
+// Shared host/device helpers for libb200grpo (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "../../include/b200grpo.h"
+
+namespace b200grpo {
+
+// ---- error plumbing -----------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int check_device_sm100();  // 0 or B200GRPO_EARCH / ECUDA (cached per thread)
+int get_tunable(int id);
+enum { TUNE_FWD_SPLITS = 0, TUNE_TWO_CTA = 1, TUNE_GEMM_STAGES = 2, TUNE_WATCHDOG_MS = 3, TUNE_COUNT = 4 };
+
+#define B200_CUDA_OK(expr)                                                              \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      ::b200grpo::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),     \
+                            __FILE__, __LINE__);                                        \
+      return B200GRPO_ECUDA;                                                            \
+    }                                                                                   \
+  } while (0)
+
+#define B200_REQUIRE(cond, ...)                                                         \
+  do {                                                                                  \
+    if (!(cond)) {                                                                      \
+      ::b200grpo::set_error(__VA_ARGS__);                                               \
+      return B200GRPO_EINVAL;                                                           \
+    }                                                                                   \
+  } while (0)
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+int sm_count();  // multiprocessors of the current device (cached)
+
+// ---- device helpers -------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ unsigned warp_or(unsigned v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v |= __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+#endif
+
+}  // namespace b200grpo
