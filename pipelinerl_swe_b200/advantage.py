@@ -1,0 +1,100 @@
+"""Advantage step: populate_rl_data / prepare_rl_fields / filter_zero_advantage_groups.
+
+Drop-ins for pipelinerl/finetune/rl/__init__.py:380-525 and preprocess.py:287-324 with the
+same list-of-dict in/out contract.  The pandas groupby/merge/apply of the reference is
+replaced by: per-ROLLOUT scalars gathered on the host (reward, dense group key, length,
+label count, has-eos; no per-token Python work), one K4 launch on the GPU that expands
+them into the four per-token columns, one D2H copy.
+"""
+from __future__ import annotations
+
+from typing import Any
+
+import numpy as np
+import torch
+
+from . import ops
+
+IGNORE = -100
+
+
+def prepare_rl_fields(encoding: dict[str, Any], reward: float, old_logprobs: list[float], ref_logprobs: list[float]) -> dict[str, Any]:
+    """rl/__init__.py:504-525 (pure host list bookkeeping; nothing to accelerate)."""
+    n = len(encoding["labels"])
+    n_target = sum(1 for t in encoding["labels"] if t != IGNORE)
+    assert n_target == len(old_logprobs), f"Target tokens: {n_target}, old logprobs: {len(old_logprobs)}"
+    encoding["rewards"] = [reward] * n
+    encoding["advantages"] = [0.0] * n
+    encoding["old_logprobs"] = [0] * (n - len(old_logprobs)) + old_logprobs
+    encoding["ref_logprobs"] = [0] * (n - len(ref_logprobs)) + ref_logprobs
+    encoding["overflow"] = [0] * n
+    encoding["group_tokens"] = [0] * n
+    encoding["num_labels"] = [1 if t != IGNORE else 0 for t in encoding["labels"]]
+    return encoding
+
+
+def rollout_scalars(dataset: list[dict[str, Any]], eos_token_id: int):
+    """Host side of K4's input: one record per rollout row (17 B/rollout), no per-token loops in Python."""
+    keys: dict[str, int] = {}
+    n = len(dataset)
+    reward = np.empty(n, dtype=np.float64)
+    gkey = np.empty(n, dtype=np.int32)
+    lens = np.empty(n, dtype=np.int64)
+    nlab = np.empty(n, dtype=np.int32)
+    eos = np.empty(n, dtype=np.uint8)
+    seen: dict[tuple[int, Any], float] = {}
+    uniform = True
+    for i, row in enumerate(dataset):
+        k = f"{row['group_id']}_{row['step_index']}"  # :395
+        gkey[i] = keys.setdefault(k, len(keys))
+        r = row["rewards"]
+        reward[i] = r[0]  # :402
+        # :405 -- one reward per (group, rollout)
+        assert seen.setdefault((int(gkey[i]), row["rollout_index"]), r[0]) == r[0]
+        ra = np.asarray(r, dtype=np.float64)
+        uniform = uniform and bool((ra == ra[0]).all())
+        ids = np.asarray(row["input_ids"])
+        lens[i] = ids.shape[0]
+        nlab[i] = int((np.asarray(row["labels"]) != IGNORE).sum())
+        eos[i] = bool((ids == eos_token_id).any())
+    offsets = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(lens, out=offsets[1:])
+    tok_rewards = None
+    if not uniform:  # per-token rewards differ inside a row: ship them (f64) so :466 is followed literally
+        tok_rewards = np.concatenate([np.asarray(row["rewards"], dtype=np.float64) for row in dataset])
+    return reward, gkey, offsets, nlab, eos, len(keys), tok_rewards
+
+
+def populate_rl_data(dataset: list[dict[str, Any]], eos_token_id: int, config, device: torch.device | str | None = None) -> list[dict[str, Any]]:
+    """rl/__init__.py:380-501: fills advantages / group_tokens / overflow / num_labels per token, in place."""
+    if not dataset:
+        return dataset
+    dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+    reward, gkey, offsets, nlab, eos, n_groups, tok_rewards = rollout_scalars(dataset, eos_token_id)
+    to = lambda a: torch.from_numpy(a).to(dev, non_blocking=True)  # noqa: E731
+    out = ops.group_advantage(to(reward), to(gkey), to(offsets), to(nlab), to(eos), n_groups,
+                              bool(config.divide_advantage_by_std), None if tok_rewards is None else to(tok_rewards))
+    host = out.cpu().numpy().astype(np.float64)  # python floats carry the f32 values the trainer will see
+    for i, row in enumerate(dataset):
+        a, b = int(offsets[i]), int(offsets[i + 1])
+        n_adv = len(row["rewards"])
+        row["advantages"] = host[0, a:a + n_adv].tolist()
+        row["group_tokens"] = host[1, a:b].tolist()
+        row["overflow"] = [float(host[3, a])] * len(row["overflow"]) if b > a else []
+        row["num_labels"] = [int(nlab[i])] * (b - a)
+    return dataset
+
+
+def filter_zero_advantage_groups(dataset: list[dict], epsilon: float = 1e-6) -> tuple[list[dict], int]:
+    """preprocess.py:287-324: drop groups whose advantages are all within epsilon of zero."""
+    groups: dict[Any, list[dict]] = {}
+    for entry in dataset:
+        groups.setdefault(entry["group_id"], []).append(entry)
+    kept: list[dict] = []
+    dropped = 0
+    for entries in groups.values():
+        if any(bool((np.abs(np.asarray(e["advantages"], dtype=np.float64)) > epsilon).any()) for e in entries):
+            kept.extend(entries)
+        else:
+            dropped += len(entries)
+    return kept, dropped

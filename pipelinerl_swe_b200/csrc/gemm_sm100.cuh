@@ -1,0 +1,377 @@
+// Persistent warp-specialised tcgen05 GEMM mainloop for sm_100a with pluggable epilogues.
+//
+//   D[M,N] (f32 in TMEM) = A[M,K] . B[N,K]^T          bf16 operands, fp32 accumulate
+//
+// One CTA (or a cta_group::2 pair) owns 128 (256) rows x BLOCK_N columns per tile:
+//   warp 0 lane 0 : TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem ring)
+//   warp 1 lane 0 : MMA issuer    (tcgen05.mma, accumulators double-buffered in TMEM)
+//   warp 2        : TMEM allocator
+//   warps 4..7    : epilogue      (tcgen05.ld: thread == accumulator row, 32 cols per load)
+// Pipelines: smem full/empty mbarriers (TMA <-> MMA) and TMEM full/empty mbarriers
+// (MMA <-> epilogue), so the epilogue of tile i overlaps the MMAs of tile i+1.
+//
+// Work decomposition: item = (m_block, split); an item sweeps a contiguous range of
+// n-blocks for one row block, which lets the forward epilogue keep its running
+// (max, sum-exp, sum e*z) per row in registers across the sweep.  Items are dealt
+// round-robin with m_block fastest, so CTAs running together share the same B (weight)
+// tiles through L2 while A (hidden) stays L2 resident.
+#pragma once
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace b200grpo {
+
+enum { EPI_STORE = 0, EPI_FWD_STATS = 1, EPI_BWD_DLOGITS = 2 };
+enum { MAJOR_K = 0, MAJOR_MN = 1 };
+
+constexpr int GEMM_BLOCK_M = 128;   // rows per CTA (TMEM lanes)
+constexpr int GEMM_BLOCK_K = 64;    // one 128-byte swizzle atom of bf16
+constexpr int GEMM_UMMA_K = 16;
+constexpr int GEMM_THREADS = 256;
+constexpr int GEMM_EPI_WARP0 = 4;
+constexpr float LOG2E_F = 1.4426950408889634f;
+constexpr float LN2_F = 0.6931471805599453f;
+
+struct GemmParams {
+  int M, N, K;
+  int m_blocks, n_blocks, n_splits;
+  // EPI_STORE
+  void* C;
+  long long ldc;
+  int c_is_f32, accumulate;
+  // EPI_FWD_STATS / EPI_BWD_DLOGITS
+  const long long* targets;
+  long long v_offset;
+  float inv_temp;
+  float* part;              // [n_splits][M][4]  (max z, sum e, sum e*z, z_target|0)
+  const float *lse, *entropy, *coef_lp, *coef_ent, *grad_scale;
+  __nv_bfloat16* dlogits;   // [M][ldd]
+  long long ldd;
+};
+
+template <int BLOCK_N, int kCtas, int kStages>
+struct GemmSmem {
+  static constexpr int LOAD_N = BLOCK_N / kCtas;
+  static constexpr int A_BYTES = GEMM_BLOCK_M * GEMM_BLOCK_K * 2;
+  static constexpr int B_BYTES = LOAD_N * GEMM_BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_OFFSET = kStages * STAGE_BYTES;
+  static constexpr int TOTAL = BAR_OFFSET + (2 * kStages + 4) * 8 + 16 + 1024;  // + alignment slack
+};
+
+__device__ __forceinline__ void item_range(const GemmParams& p, int item, int& m_blk, int& nb_begin, int& nb_end) {
+  m_blk = item % p.m_blocks;
+  const int sp = item / p.m_blocks;
+  nb_begin = (int)((long long)sp * p.n_blocks / p.n_splits);
+  nb_end = (int)((long long)(sp + 1) * p.n_blocks / p.n_splits);
+}
+
+// ---------------------------------------------------------------------------------------
+// Epilogues.  Each thread owns one accumulator row; v[] holds 32 consecutive columns.
+// ---------------------------------------------------------------------------------------
+// MUFU.EX2 directly: 2^x with ~2^-22 relative error, ex2(-inf) = +0 (no range fix-up code)
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+struct FwdRowState { float m_raw, s, u, tgt; int tcol; };
+
+__device__ __forceinline__ void fwd_chunk(FwdRowState& st, const uint32_t (&v)[32], int col0, int n_valid, float scale2) {
+  // n_valid = number of real vocab columns in this chunk (32 except at the vocab tail)
+  float cmax = -INFINITY;
+  if (n_valid >= 32) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) cmax = fmaxf(cmax, __uint_as_float(v[j]));
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) if (j < n_valid) cmax = fmaxf(cmax, __uint_as_float(v[j]));
+  }
+  if (cmax > st.m_raw) {
+    const float r = fast_exp2((st.m_raw - cmax) * scale2);
+    st.s *= r; st.u *= r; st.m_raw = cmax;
+  }
+  const float neg = -st.m_raw * scale2;
+  float s = 0.f, u = 0.f;
+  if (n_valid >= 32) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float a = __uint_as_float(v[j]);
+      const float e = fast_exp2(fmaf(a, scale2, neg));
+      s += e; u = fmaf(e, a, u);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) if (j < n_valid) {
+      const float a = __uint_as_float(v[j]);
+      const float e = fast_exp2(fmaf(a, scale2, neg));
+      s += e; u = fmaf(e, a, u);
+    }
+  }
+  st.s += s; st.u += u;
+  const int t = st.tcol - col0;
+  if (t >= 0 && t < 32) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) if (j == t) st.tgt = __uint_as_float(v[j]);
+  }
+}
+
+struct BwdRowConst { float lse2, a, e, ent; int tcol; };
+
+__device__ __forceinline__ void bwd_chunk(const BwdRowConst& rc, const uint32_t (&v)[32], int col0, int n_valid,
+                                          float scale2, __nv_bfloat16* out_row) {
+  uint32_t packed[16];
+  const int t = rc.tcol - col0;
+#pragma unroll
+  for (int j = 0; j < 32; j += 2) {
+    float d[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const float y2 = fmaf(__uint_as_float(v[j + q]), scale2, -rc.lse2);  // log2 p
+      const float pr = fast_exp2(y2);
+      float g = -pr * fmaf(rc.e, fmaf(y2, LN2_F, rc.ent), rc.a);           // -p*(a + e*(logp + H))
+      if (j + q == t) g += rc.a;
+      d[q] = g;
+    }
+    const __nv_bfloat162 b = __floats2bfloat162_rn(d[0], d[1]);
+    packed[j >> 1] = *reinterpret_cast<const uint32_t*>(&b);
+  }
+  if (n_valid >= 32) {
+    uint4* o = reinterpret_cast<uint4*>(out_row + col0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) o[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < n_valid) {
+        const uint32_t w = packed[j >> 1];
+        const unsigned short h = (j & 1) ? (unsigned short)(w >> 16) : (unsigned short)(w & 0xffffu);
+        reinterpret_cast<unsigned short*>(out_row + col0)[j] = h;
+      }
+  }
+}
+
+__device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t (&v)[32], int row, int col0, int n_valid) {
+  if (p.c_is_f32) {
+    float* o = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + col0;
+    if (n_valid >= 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+      float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        float4 x = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
+                               __uint_as_float(v[4 * q + 3]));
+        if (p.accumulate) { const float4 y = o4[q]; x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w; }
+        o4[q] = x;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < n_valid) o[j] = (p.accumulate ? o[j] : 0.f) + __uint_as_float(v[j]);
+    }
+  } else {
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.C) + (long long)row * p.ldc + col0;
+    if (n_valid >= 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+      uint4* o4 = reinterpret_cast<uint4*>(o);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint32_t w[4];
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const __nv_bfloat162 b = __floats2bfloat162_rn(__uint_as_float(v[8 * q + 2 * h]), __uint_as_float(v[8 * q + 2 * h + 1]));
+          w[h] = *reinterpret_cast<const uint32_t*>(&b);
+        }
+        o4[q] = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < n_valid) o[j] = __float2bfloat16_rn(__uint_as_float(v[j]));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// The kernel
+// ---------------------------------------------------------------------------------------
+template <int kEpi, int kAMajor, int kBMajor, int kCtas, int BLOCK_N, int kStages>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, const GemmParams p) {
+  using L = GemmSmem<BLOCK_N, kCtas, kStages>;
+  constexpr int LOAD_N = L::LOAD_N;
+  constexpr int UMMA_M = GEMM_BLOCK_M * kCtas;
+  constexpr uint32_t TMEM_COLS = 2 * BLOCK_N <= 32 ? 32 : 2 * BLOCK_N <= 64 ? 64 : 2 * BLOCK_N <= 128 ? 128 : 2 * BLOCK_N <= 256 ? 256 : 512;
+  static_assert(2 * BLOCK_N <= 512, "two accumulator stages must fit the 512 TMEM columns");
+  static_assert(BLOCK_N % 32 == 0 && LOAD_N % 64 == 0, "tile shape");
+  static_assert(kBMajor == MAJOR_K || LOAD_N % 64 == 0, "MN-major B is loaded in 64-wide atoms");
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t pad = (1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u;
+  uint8_t* smem = smem_raw + pad;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFFSET);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta_rank = kCtas > 1 ? ptx::cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
+  const int cluster_id = blockIdx.x / kCtas, n_clusters = gridDim.x / kCtas;
+  const int n_items = p.m_blocks * p.n_splits;
+  const int num_kb = (p.K + GEMM_BLOCK_K - 1) / GEMM_BLOCK_K;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tm_a);
+    ptx::prefetch_tensormap(&tm_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages; ++i) { ptx::mbar_init(&full_bar[i], kCtas); ptx::mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], 128 * kCtas); }
+    ptx::fence_mbar_init();
+  }
+  if (kCtas > 1) ptx::cluster_sync();   // peer barriers initialised before anyone signals them
+  if (warp == 2) ptx::tmem_alloc<kCtas>(tmem_ptr, TMEM_COLS);
+  ptx::tc_fence_before();
+  if (kCtas > 1) ptx::cluster_sync(); else __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer =====================
+    uint32_t stage = 0, phase = 0;
+    for (int item = cluster_id; item < n_items; item += n_clusters) {
+      int m_blk, nb0, nb1;
+      item_range(p, item, m_blk, nb0, nb1);
+      const int m0 = (m_blk * kCtas + (int)cta_rank) * GEMM_BLOCK_M;
+      for (int nb = nb0; nb < nb1; ++nb) {
+        const int n0 = nb * BLOCK_N + (int)cta_rank * LOAD_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1, 1);
+          uint8_t* sa = smem + stage * L::STAGE_BYTES;
+          uint8_t* sb = sa + L::A_BYTES;
+          if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], L::STAGE_BYTES * kCtas);
+          else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
+          const int k0 = kb * GEMM_BLOCK_K;
+          auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
+            if constexpr (kCtas == 1) ptx::tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
+            else ptx::tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
+          };
+          if constexpr (kAMajor == MAJOR_K) {
+            load(sa, &tm_a, k0, m0);                                   // box {64 k, 128 rows}
+          } else {
+#pragma unroll
+            for (int a = 0; a < GEMM_BLOCK_M / 64; ++a) load(sa + a * 8192, &tm_a, m0 + a * 64, k0);  // box {64 m, 64 k}
+          }
+          if constexpr (kBMajor == MAJOR_K) {
+            load(sb, &tm_b, k0, n0);                                   // box {64 k, LOAD_N rows}
+          } else {
+#pragma unroll
+            for (int a = 0; a < LOAD_N / 64; ++a) load(sb + a * 8192, &tm_b, n0 + a * 64, k0);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0 && leader) {
+    // ===================== MMA issuer (leader CTA, one thread) =====================
+    constexpr uint32_t idesc = ptx::idesc_bf16_f32(UMMA_M, BLOCK_N, kAMajor, kBMajor);
+    constexpr uint32_t A_LBO = kAMajor == MAJOR_K ? 0 : GEMM_BLOCK_K * 128, B_LBO = kBMajor == MAJOR_K ? 0 : GEMM_BLOCK_K * 128;
+    constexpr uint32_t A_KSTEP = (kAMajor == MAJOR_K ? GEMM_UMMA_K * 2 : GEMM_UMMA_K * 128) >> 4;
+    constexpr uint32_t B_KSTEP = (kBMajor == MAJOR_K ? GEMM_UMMA_K * 2 : GEMM_UMMA_K * 128) >> 4;
+    uint32_t stage = 0, phase = 0, tile_iter = 0;
+    for (int item = cluster_id; item < n_items; item += n_clusters) {
+      int m_blk, nb0, nb1;
+      item_range(p, item, m_blk, nb0, nb1);
+      for (int nb = nb0; nb < nb1; ++nb, ++tile_iter) {
+        const uint32_t as = tile_iter & 1, aphase = (tile_iter >> 1) & 1;
+        ptx::mbar_wait(&tmem_empty[as], aphase ^ 1, 2);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(&full_bar[stage], phase, 3);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(smem + stage * L::STAGE_BYTES), sb = sa + L::A_BYTES;
+          const uint64_t da = ptx::smem_desc_sw128(sa, A_LBO, 1024), db = ptx::smem_desc_sw128(sb, B_LBO, 1024);
+#pragma unroll
+          for (int k = 0; k < GEMM_BLOCK_K / GEMM_UMMA_K; ++k)
+            ptx::umma_bf16<kCtas>(d_tmem, da + (uint64_t)(k * A_KSTEP), db + (uint64_t)(k * B_KSTEP), idesc, (kb | k) != 0);
+          ptx::umma_commit<kCtas>(&empty_bar[stage]);              // frees the smem slot when the MMAs retire
+          if (kb == num_kb - 1) ptx::umma_commit<kCtas>(&tmem_full[as]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    if (kCtas > 1 && tile_iter > 0) {  // drain: peer epilogue arrivals must land before teardown
+      const uint32_t last = tile_iter - 1;
+      ptx::mbar_wait(&tmem_empty[last & 1], (last >> 1) & 1, 4);
+      if (tile_iter > 1) ptx::mbar_wait(&tmem_empty[(last - 1) & 1], ((last - 1) >> 1) & 1, 5);
+    }
+  } else if (warp >= GEMM_EPI_WARP0) {
+    // ===================== epilogue (4 warps, thread == TMEM lane == tile row) ============
+    const int quad = warp & 3;
+    const int row_in_tile = quad * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    const float scale2 = p.inv_temp * LOG2E_F;
+    uint32_t tile_iter = 0;
+    for (int item = cluster_id; item < n_items; item += n_clusters) {
+      int m_blk, nb0, nb1;
+      item_range(p, item, m_blk, nb0, nb1);
+      const int row = (m_blk * kCtas + (int)cta_rank) * GEMM_BLOCK_M + row_in_tile;
+      const bool row_ok = row < p.M;
+      FwdRowState fs;
+      BwdRowConst bc;
+      if constexpr (kEpi == EPI_FWD_STATS) {
+        fs.m_raw = -INFINITY; fs.s = 0.f; fs.u = 0.f; fs.tgt = 0.f;
+        const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
+        fs.tcol = (t >= 0 && t < p.N) ? (int)t : -1000000;
+      }
+      if constexpr (kEpi == EPI_BWD_DLOGITS) {
+        const float gs = (p.grad_scale ? *p.grad_scale : 1.0f) * p.inv_temp;
+        bc.lse2 = row_ok ? p.lse[row] * LOG2E_F : 0.f;
+        bc.a = row_ok ? p.coef_lp[row] * gs : 0.f;
+        bc.e = row_ok ? p.coef_ent[row] * gs : 0.f;
+        bc.ent = row_ok ? p.entropy[row] : 0.f;
+        const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
+        bc.tcol = (t >= 0 && t < p.N) ? (int)t : -1000000;
+      }
+      for (int nb = nb0; nb < nb1; ++nb, ++tile_iter) {
+        const uint32_t as = tile_iter & 1, aphase = (tile_iter >> 1) & 1;
+        ptx::mbar_wait(&tmem_full[as], aphase, 6);
+        ptx::tc_fence_after();
+        const uint32_t t_addr = tmem_base + lane_addr + as * BLOCK_N;
+        const int n0 = nb * BLOCK_N;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 32; ++c) {
+          const int col0 = n0 + c * 32;
+          if (col0 >= p.N) break;                    // warp-uniform
+          uint32_t v[32];
+          __syncwarp();
+          ptx::tmem_ld_32x32(t_addr + c * 32, v);
+          ptx::tmem_ld_wait();
+          const int n_valid = min(32, p.N - col0);
+          if constexpr (kEpi == EPI_FWD_STATS) fwd_chunk(fs, v, col0, n_valid, scale2);
+          if constexpr (kEpi == EPI_BWD_DLOGITS) { if (row_ok) bwd_chunk(bc, v, col0, n_valid, scale2, p.dlogits + (long long)row * p.ldd); }
+          if constexpr (kEpi == EPI_STORE) { if (row_ok) store_chunk(p, v, row, col0, n_valid); }
+        }
+        ptx::tc_fence_before();
+        if (kCtas == 1) ptx::mbar_arrive(&tmem_empty[as]); else ptx::mbar_arrive_cluster(&tmem_empty[as], 0);
+      }
+      if constexpr (kEpi == EPI_FWD_STATS) {
+        if (row_ok) {
+          const int sp = item / p.m_blocks;
+          float4 o = make_float4(fs.m_raw * p.inv_temp, fs.s, fs.u * p.inv_temp, fs.tgt * p.inv_temp);
+          reinterpret_cast<float4*>(p.part)[(long long)sp * p.M + row] = o;
+        }
+      }
+    }
+  }
+
+  // ===================== teardown =====================
+  __syncwarp();
+  ptx::tc_fence_before();
+  if (kCtas > 1) ptx::cluster_sync(); else __syncthreads();
+  if (warp == 2) { ptx::tc_fence_after(); ptx::tmem_dealloc<kCtas>(tmem_base, TMEM_COLS); }
+}
+
+}  // namespace b200grpo

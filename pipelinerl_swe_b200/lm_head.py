@@ -1,0 +1,136 @@
+"""lm_head projection fused with log-softmax / entropy / gather (K1) and its backward (K2).
+
+Replaces ``model(**inputs).logits`` -> ``/temperature`` -> ``log_softmax`` -> ``softmax`` ->
+entropy -> ``gather`` of pipelinerl/finetune/rl/__init__.py:197-208: the [tokens x vocab]
+logits never exist in HBM.  ``FusedLMHead`` is a drop-in for ``model.lm_head``: it owns the
+same ``weight`` Parameter, so ZeRO-3 / FSDP gather hooks and tied embeddings keep working,
+and only switches to the fused op while ``rl_step`` has an active ``LogprobRequest``.
+"""
+from __future__ import annotations
+
+import threading
+from dataclasses import dataclass
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from . import ops
+
+
+class LMHeadLogprobFunction(torch.autograd.Function):
+    """(hidden [M,H] bf16, weight [Vloc,H] bf16, targets [M] i64) -> out f32 [M,2] = (logprob, entropy).
+
+    With a process ``group`` the vocab rows are sharded contiguously over its ranks
+    (vocab-parallel): each rank reduces its rows to (max, sumexp, sum e*z, z_target), the
+    [M,4] stats are all-gathered over NCCL and merged; backward all-reduces grad_hidden.
+    """
+
+    @staticmethod
+    def forward(ctx, hidden, weight, targets, inv_temperature: float, group=None, v_offset: int = 0):
+        stats = ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset)
+        if group is not None and dist.get_world_size(group) > 1:
+            gathered = torch.empty(dist.get_world_size(group), *stats.shape, dtype=stats.dtype, device=stats.device)
+            dist.all_gather_into_tensor(gathered, stats, group=group)
+            stats = gathered
+        logprob, entropy, lse = ops.lmhead_finalize(stats)
+        ctx.save_for_backward(hidden, weight, targets, lse, entropy)
+        ctx.inv_temperature, ctx.group, ctx.v_offset = inv_temperature, group, v_offset
+        return torch.stack((logprob, entropy), dim=1)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        hidden, weight, targets, lse, entropy = ctx.saved_tensors
+        g = grad_out.float()
+        coef_lp, coef_ent = g[:, 0].contiguous(), g[:, 1].contiguous()
+        need_h, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        gh, gw = ops.lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, ctx.inv_temperature, ctx.v_offset,
+                                need_grad_hidden=need_h, need_grad_weight=need_w)
+        if gh is not None and ctx.group is not None and dist.get_world_size(ctx.group) > 1:
+            dist.all_reduce(gh, group=ctx.group)  # dH = sum over vocab shards
+        return gh, gw, None, None, None, None
+
+
+def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch.Tensor, temperature: float, group=None,
+                    v_offset: int = 0) -> torch.Tensor:
+    """hidden [B,L,H], input_ids [B,L] -> f32 [B,L,2]: (logprob of input_ids[t+1], entropy) per position.
+
+    Position L-1 of every row has no next token: it is scored against token 0 and the
+    caller drops it (the reference slices ``[:, :-1]``, rl/__init__.py:200,208).
+    """
+    B, L, H = hidden.shape
+    targets = torch.roll(input_ids, shifts=-1, dims=1).reshape(-1).contiguous()
+    h2 = hidden.reshape(B * L, H)
+    if h2.dtype != torch.bfloat16:
+        h2 = h2.to(torch.bfloat16)
+    w = weight if weight.dtype == torch.bfloat16 else weight.to(torch.bfloat16)
+    out = LMHeadLogprobFunction.apply(h2.contiguous(), w.contiguous(), targets, 1.0 / float(temperature), group, v_offset)
+    return out.reshape(B, L, 2)
+
+
+@dataclass
+class LogprobRequest:
+    """What ``rl_step`` asks the swapped lm_head to compute during ``model(**inputs)``."""
+    input_ids: torch.Tensor
+    temperature: float
+    group: object = None
+    v_offset: int = 0
+
+
+_tls = threading.local()
+
+
+class logprob_request:
+    """Context manager activating a LogprobRequest for FusedLMHead on this thread."""
+
+    def __init__(self, req: LogprobRequest):
+        self.req = req
+
+    def __enter__(self):
+        _tls.req = self.req
+        return self.req
+
+    def __exit__(self, *exc):
+        _tls.req = None
+        return False
+
+
+class FusedLMHead(nn.Module):
+    """Swap-in for ``model.lm_head`` (an ``nn.Linear(H, V, bias=False)``).
+
+    Outside ``rl_step`` it is the plain projection (generation / evaluation unchanged).
+    Inside, ``forward(hidden)`` returns [B, L, 2] (logprob, entropy) in place of logits.
+    """
+
+    def __init__(self, linear: nn.Module):
+        super().__init__()
+        if getattr(linear, "bias", None) is not None:
+            raise ValueError("FusedLMHead supports bias-free lm_head only (all Qwen2.5 / Llama heads)")
+        self.weight = linear.weight  # same Parameter object: tied embeddings and ZeRO/FSDP hooks stay valid
+        self.in_features = linear.weight.shape[1]
+        self.out_features = linear.weight.shape[0]
+
+    def forward(self, hidden: torch.Tensor) -> torch.Tensor:
+        req = getattr(_tls, "req", None)
+        if req is None:
+            return nn.functional.linear(hidden, self.weight)
+        return lmhead_logprobs(hidden, self.weight, req.input_ids, req.temperature, req.group, req.v_offset)
+
+
+def install_fused_lm_head(model: nn.Module) -> FusedLMHead:
+    """Idempotently replace ``model.lm_head`` (also through one ``.module`` / ``.model`` wrapper level)."""
+    owner = model
+    for _ in range(4):
+        if hasattr(owner, "lm_head"):
+            break
+        nxt = getattr(owner, "module", None) or getattr(owner, "model", None)
+        if nxt is None:
+            break
+        owner = nxt
+    head = getattr(owner, "lm_head", None)
+    if head is None:
+        raise AttributeError("rl_step needs a model with an `lm_head` projection to fuse")
+    if not isinstance(head, FusedLMHead):
+        head = FusedLMHead(head)
+        owner.lm_head = head
+    return head

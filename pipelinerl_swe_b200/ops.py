@@ -1,0 +1,203 @@
+"""Tensor-level wrappers over the C ABI: torch owns memory and streams, the library computes.
+
+Each wrapper validates dtype / contiguity, sizes the workspace with the library's own
+``*_workspace`` query, and passes raw device pointers plus the current CUDA stream.
+No wrapper computes anything in torch.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Sequence
+
+import torch
+
+from . import _abi
+from ._abi import LossCfg, M_COUNT, check, lib
+
+_ws_cache: dict[tuple[int, str], torch.Tensor] = {}
+
+
+def _workspace(device: torch.device, nbytes: int, tag: str = "main") -> torch.Tensor:
+    """Grow-only per-device scratch; calls are stream-ordered so one buffer per tag suffices."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), tag)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: torch.Tensor | None) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def _req(t: torch.Tensor, dtype: torch.dtype, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise _abi.B200GrpoError(f"{name} must be a CUDA tensor (pipelinerl_swe_b200 has no CPU path)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name}: expected {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t
+
+
+def lmhead_fwd_stats(hidden: torch.Tensor, weight: torch.Tensor, targets: torch.Tensor, inv_temperature: float,
+                     v_offset: int = 0) -> torch.Tensor:
+    """K1: per-row (max, sumexp, sum e*z, z_target) over this rank's vocab rows -> f32 [M,4]."""
+    _req(hidden, torch.bfloat16, "hidden"); _req(weight, torch.bfloat16, "weight"); _req(targets, torch.int64, "targets")
+    M, H = hidden.shape
+    V = weight.shape[0]
+    assert weight.shape[1] == H and targets.numel() == M
+    stats = torch.empty(M, 4, dtype=torch.float32, device=hidden.device)
+    n = lib().b200grpo_lmhead_fwd_workspace(M, H, V)
+    ws = _workspace(hidden.device, n)
+    check(lib().b200grpo_lmhead_fwd(hidden.data_ptr(), H, weight.data_ptr(), H, targets.data_ptr(), M, H, V, v_offset,
+                                    float(inv_temperature), stats.data_ptr(), ws.data_ptr(), ws.numel(), _stream()))
+    return stats
+
+
+def lmhead_finalize(stats: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """stats f32 [R,M,4] (or [M,4]) -> (logprob, entropy, lse) f32 [M]."""
+    _req(stats, torch.float32, "stats")
+    if stats.dim() == 2:
+        stats = stats[None]
+    R, M, _ = stats.shape
+    out = torch.empty(3, M, dtype=torch.float32, device=stats.device)
+    check(lib().b200grpo_lmhead_finalize(stats.data_ptr(), R, M, out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(), _stream()))
+    return out[0], out[1], out[2]
+
+
+def lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, inv_temperature, v_offset=0, grad_scale=None,
+               need_grad_hidden=True, need_grad_weight=True, grad_weight_out: torch.Tensor | None = None,
+               accumulate: bool = False):
+    """K2: (grad_hidden bf16 [M,H] | None, grad_weight [V,H] | None)."""
+    _req(hidden, torch.bfloat16, "hidden"); _req(weight, torch.bfloat16, "weight"); _req(targets, torch.int64, "targets")
+    for name, t in (("lse", lse), ("entropy", entropy), ("coef_lp", coef_lp), ("coef_ent", coef_ent)):
+        _req(t, torch.float32, name)
+    M, H = hidden.shape
+    V = weight.shape[0]
+    gh = torch.empty(M, H, dtype=torch.bfloat16, device=hidden.device) if need_grad_hidden else None
+    gw = None
+    if need_grad_weight:
+        gw = grad_weight_out if grad_weight_out is not None else torch.empty(V, H, dtype=torch.bfloat16, device=hidden.device)
+        assert gw.shape == (V, H) and gw.is_contiguous() and gw.dtype in (torch.bfloat16, torch.float32)
+    n = lib().b200grpo_lmhead_bwd_workspace(M, H, V)
+    ws = _workspace(hidden.device, n, "dlogits")
+    check(lib().b200grpo_lmhead_bwd(hidden.data_ptr(), H, weight.data_ptr(), H, targets.data_ptr(), lse.data_ptr(),
+                                    entropy.data_ptr(), coef_lp.data_ptr(), coef_ent.data_ptr(), _ptr(grad_scale), M, H, V,
+                                    v_offset, float(inv_temperature), _ptr(gh), H, _ptr(gw), H,
+                                    int(gw is not None and gw.dtype == torch.float32), int(accumulate), ws.data_ptr(),
+                                    ws.numel(), _stream()))
+    return gh, gw
+
+
+def token_loss(logprob, entropy, batch: dict, cfg: LossCfg, values=None):
+    """K3 -> (loss f32[1], metrics f64[M_COUNT], coef_lp, coef_ent, coef_value|None)."""
+    labels = _req(batch["labels"], torch.int64, "labels")
+    rows, L = labels.shape
+    dev = labels.device
+    f32 = lambda k: _req(batch[k], torch.float32, k)  # noqa: E731
+    pos = batch.get("position_ids")
+    if pos is not None:
+        _req(pos, torch.int64, "position_ids")
+    _req(logprob, torch.float32, "logprob"); _req(entropy, torch.float32, "entropy")
+    assert logprob.numel() == rows * (L - 1) and entropy.numel() == rows * (L - 1)
+    metrics = torch.empty(M_COUNT, dtype=torch.float64, device=dev)
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    coef = torch.empty(2, rows, max(L - 1, 0), dtype=torch.float32, device=dev)
+    coef_v = torch.empty(rows, L, dtype=torch.float32, device=dev) if values is not None else None
+    if values is not None:
+        _req(values, torch.float32, "values")
+    n = lib().b200grpo_token_loss_workspace(rows, L)
+    ws = _workspace(dev, n)
+    check(lib().b200grpo_token_loss(
+        logprob.data_ptr(), entropy.data_ptr(), labels.data_ptr(), _ptr(pos), f32("rewards").data_ptr(),
+        f32("advantages").data_ptr(), f32("ref_logprobs").data_ptr(), f32("old_logprobs").data_ptr(),
+        f32("group_tokens").data_ptr(), f32("num_labels").data_ptr(), f32("overflow").data_ptr(), _ptr(values), rows, L,
+        C.byref(cfg), metrics.data_ptr(), loss.data_ptr(), coef[0].data_ptr(), coef[1].data_ptr(), _ptr(coef_v),
+        ws.data_ptr(), ws.numel(), _stream()))
+    return loss, metrics, coef[0], coef[1], coef_v
+
+
+def segment_bounds(position_ids: torch.Tensor) -> torch.Tensor:
+    """int32 boundaries [S+1] of a packed row, as rl/__init__.py:159-170 (one D2H sync for S)."""
+    pos = _req(position_ids.reshape(-1), torch.int64, "position_ids")
+    T = pos.numel()
+    bounds = torch.empty(T + 1, dtype=torch.int32, device=pos.device)
+    n = torch.empty(1, dtype=torch.int32, device=pos.device)
+    ws = _workspace(pos.device, 4 * ((T + 1023) // 1024) + 256)
+    check(lib().b200grpo_segment_bounds(pos.data_ptr(), T, bounds.data_ptr(), n.data_ptr(), ws.data_ptr(), ws.numel(), _stream()))
+    return bounds[: int(n.item())]
+
+
+def gemm_bf16(A: torch.Tensor, B: torch.Tensor, a_mn_major=False, b_mn_major=False, out_dtype=torch.float32,
+              out: torch.Tensor | None = None, accumulate=False) -> torch.Tensor:
+    """C[M,N] = A.B^T on the tcgen05 mainloop (test surface).  MN-major operands are given as [K, M|N]."""
+    _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B")
+    (K, M) = A.shape if a_mn_major else A.shape[::-1]
+    (K2, N) = B.shape if b_mn_major else B.shape[::-1]
+    assert K == K2
+    if out is None:
+        out = torch.empty(M, N, dtype=out_dtype, device=A.device)
+    check(lib().b200grpo_gemm_bf16(A.data_ptr(), A.stride(0), int(a_mn_major), B.data_ptr(), B.stride(0), int(b_mn_major),
+                                   out.data_ptr(), out.stride(0), int(out.dtype == torch.float32), int(accumulate), M, N, K,
+                                   _stream()))
+    return out
+
+
+def group_advantage(row_reward: torch.Tensor, group_key: torch.Tensor, row_offsets: torch.Tensor, n_labels: torch.Tensor,
+                    has_eos: torch.Tensor, n_groups: int, divide_by_std: bool, token_rewards: torch.Tensor | None = None):
+    """K4 -> f32 [4, total_tokens]: advantages, group_tokens, num_labels, overflow."""
+    _req(row_reward, torch.float64, "row_reward"); _req(group_key, torch.int32, "group_key")
+    _req(row_offsets, torch.int64, "row_offsets"); _req(n_labels, torch.int32, "n_labels"); _req(has_eos, torch.uint8, "has_eos")
+    if token_rewards is not None:
+        _req(token_rewards, torch.float64, "token_rewards")
+    n_rows = row_reward.numel()
+    total = int(row_offsets[-1].item()) if n_rows else 0
+    out = torch.empty(4, total, dtype=torch.float32, device=row_reward.device)
+    n = lib().b200grpo_group_advantage_workspace(n_rows, n_groups)
+    ws = _workspace(row_reward.device, n)
+    check(lib().b200grpo_group_advantage(row_reward.data_ptr(), group_key.data_ptr(), row_offsets.data_ptr(), n_labels.data_ptr(),
+                                         has_eos.data_ptr(), _ptr(token_rewards), n_rows, n_groups, int(divide_by_std),
+                                         out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(), out[3].data_ptr(),
+                                         ws.data_ptr(), ws.numel(), _stream()))
+    return out
+
+
+def _tensor_table(tensors: Sequence[torch.Tensor]):
+    n = len(tensors)
+    ptrs = (C.c_void_p * n)(*[t.data_ptr() for t in tensors])
+    numel = (C.c_int64 * n)(*[t.numel() for t in tensors])
+    is_f32 = (C.c_uint8 * n)(*[int(t.dtype == torch.float32) for t in tensors])
+    for t in tensors:
+        if t.dtype not in (torch.bfloat16, torch.float32) or not t.is_contiguous() or not t.is_cuda:
+            raise TypeError("bucket tensors must be contiguous CUDA bf16 or f32")
+    return ptrs, numel, is_f32
+
+
+def bucket_numel(tensors: Sequence[torch.Tensor]) -> int:
+    n = len(tensors)
+    numel = (C.c_int64 * n)(*[t.numel() for t in tensors])
+    return int(lib().b200grpo_bucket_numel(numel, n))
+
+
+def bucket_pack(tensors: Sequence[torch.Tensor], bucket: torch.Tensor) -> None:
+    """K6: gather parameters (bf16, or f32 cast on the fly) into one contiguous bf16 bucket."""
+    _req(bucket, torch.bfloat16, "bucket")
+    ptrs, numel, is_f32 = _tensor_table(tensors)
+    n = len(tensors)
+    ws = _workspace(bucket.device, lib().b200grpo_bucket_workspace(n), "bucket")
+    check(lib().b200grpo_bucket_pack(ptrs, numel, is_f32, n, bucket.data_ptr(), bucket.numel(), ws.data_ptr(), ws.numel(), _stream()))
+
+
+def bucket_unpack(bucket: torch.Tensor, tensors: Sequence[torch.Tensor]) -> None:
+    """K6 inverse: scatter a received bucket into the destination parameters."""
+    _req(bucket, torch.bfloat16, "bucket")
+    ptrs, numel, is_f32 = _tensor_table(tensors)
+    n = len(tensors)
+    ws = _workspace(bucket.device, lib().b200grpo_bucket_workspace(n), "bucket")
+    check(lib().b200grpo_bucket_unpack(bucket.data_ptr(), ptrs, numel, is_f32, n, ws.data_ptr(), ws.numel(), _stream()))

@@ -1,0 +1,140 @@
+"""Diagnostic probes run one per process on the GPU box (a trapped kernel poisons its context).
+
+    python tests/gpu_probe.py list            -> probe names
+    python tests/gpu_probe.py <name>          -> runs one probe, prints PROBE <name> OK|FAIL ...
+
+Used while bringing kernels up; the parity tests proper live in tests/test_gpu_*.py.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def _rel(a, b):
+    return float((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-12))
+
+
+def probe_gemm(a_mn, b_mn, two_cta, M, N, K, dtype=torch.float32):
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", two_cta)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    A = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    B = torch.randn(N, K, device="cuda", generator=g).bfloat16()
+    ref = A.float() @ B.float().t()
+    Ain = A.t().contiguous() if a_mn else A
+    Bin = B.t().contiguous() if b_mn else B
+    out = ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out_dtype=dtype)
+    torch.cuda.synchronize()
+    err = _rel(out, ref)
+    tol = 1e-2 if dtype == torch.bfloat16 else 1e-4
+    return err < tol, f"rel_err={err:.3e}"
+
+
+def probe_fwd(two_cta, M, H, V, temp=1.0, splits=0):
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", two_cta)
+    _abi.set_tunable("fwd_splits", splits)
+    g = torch.Generator(device="cuda").manual_seed(2)
+    h = torch.randn(M, H, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(V, H, device="cuda", generator=g) * 0.05).bfloat16()
+    tgt = torch.randint(0, V, (M,), device="cuda", generator=g)
+    stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp)
+    lp, ent, lse = ops.lmhead_finalize(stats)
+    torch.cuda.synchronize()
+    z = (h.float() @ w.float().t()) / temp
+    logp = torch.log_softmax(z, -1)
+    ref_lp = logp.gather(1, tgt[:, None]).squeeze(1)
+    ref_ent = -(logp.exp() * logp).sum(-1)
+    e1, e2 = float((lp - ref_lp).abs().max()), float((ent - ref_ent).abs().max())
+    return e1 < 2e-3 and e2 < 2e-3, f"max|dlogprob|={e1:.3e} max|dentropy|={e2:.3e}"
+
+
+def probe_bwd(two_cta, M, H, V, temp=1.0):
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", two_cta)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    h = torch.randn(M, H, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(V, H, device="cuda", generator=g) * 0.05).bfloat16()
+    tgt = torch.randint(0, V, (M,), device="cuda", generator=g)
+    c_lp = torch.randn(M, device="cuda", generator=g) * 0.1
+    c_ent = torch.randn(M, device="cuda", generator=g) * 0.01
+    hr, wr = h.float().requires_grad_(True), w.float().requires_grad_(True)
+    z = (hr @ wr.t()) / temp
+    logp = torch.log_softmax(z, -1)
+    lp = logp.gather(1, tgt[:, None]).squeeze(1)
+    ent = -(logp.exp() * logp).sum(-1)
+    ((lp * c_lp).sum() + (ent * c_ent).sum()).backward()
+    stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp)
+    lp2, ent2, lse = ops.lmhead_finalize(stats)
+    gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent2, c_lp, c_ent, 1.0 / temp)
+    torch.cuda.synchronize()
+    e1, e2 = _rel(gh, hr.grad), _rel(gw, wr.grad)
+    return e1 < 2e-2 and e2 < 2e-2, f"rel dH={e1:.3e} rel dW={e2:.3e}"
+
+
+def probe_speed(two_cta, M, H, V):
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", two_cta)
+    h = torch.randn(M, H, device="cuda").bfloat16()
+    w = (torch.randn(V, H, device="cuda") * 0.02).bfloat16()
+    tgt = torch.randint(0, V, (M,), device="cuda")
+    c_lp = torch.randn(M, device="cuda") * 0.1
+    c_ent = torch.zeros(M, device="cuda")
+    out = []
+    for name, fn in (("fwd", lambda: ops.lmhead_finalize(ops.lmhead_fwd_stats(h, w, tgt, 1.0))),):
+        for _ in range(2):
+            r = fn()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(3):
+            r = fn()
+        t1.record(); torch.cuda.synchronize()
+        ms = t0.elapsed_time(t1) / 3
+        out.append(f"{name} {ms:.3f} ms = {2 * M * H * V / ms / 1e9:.1f} TFLOP/s")
+    lp, ent, lse = r
+    for _ in range(2):
+        ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(3):
+        ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0)
+    t1.record(); torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1) / 3
+    out.append(f"bwd {ms:.3f} ms = {6 * M * H * V / ms / 1e9:.1f} TFLOP/s executed")
+    return True, "; ".join(out)
+
+
+PROBES = {}
+for ctas in (0, 1):
+    for a_mn in (0, 1):
+        for b_mn in (0, 1):
+            PROBES[f"gemm_a{a_mn}b{b_mn}_c{ctas + 1}"] = (probe_gemm, (a_mn, b_mn, ctas, 256, 512, 256))
+            PROBES[f"gemm_a{a_mn}b{b_mn}_c{ctas + 1}_odd"] = (probe_gemm, (a_mn, b_mn, ctas, 1000, 776, 1192))
+    PROBES[f"gemm_bf16out_c{ctas + 1}"] = (probe_gemm, (0, 0, ctas, 384, 512, 192, torch.bfloat16))
+    PROBES[f"fwd_small_c{ctas + 1}"] = (probe_fwd, (ctas, 300, 128, 1000, 0.7))
+    PROBES[f"fwd_mid_c{ctas + 1}"] = (probe_fwd, (ctas, 2047, 896, 20000 + 8, 1.0))
+    PROBES[f"fwd_mid_split1_c{ctas + 1}"] = (probe_fwd, (ctas, 513, 256, 5000, 1.3, 1))
+    PROBES[f"bwd_small_c{ctas + 1}"] = (probe_bwd, (ctas, 300, 128, 1000, 0.7))
+    PROBES[f"bwd_mid_c{ctas + 1}"] = (probe_bwd, (ctas, 1023, 512, 9000, 1.0))
+    PROBES[f"speed_c2shape_c{ctas + 1}"] = (probe_speed, (ctas, 8192, 1536, 151936))
+    PROBES[f"speed_c3shape_c{ctas + 1}"] = (probe_speed, (ctas, 8192, 3584, 152064))
+
+if __name__ == "__main__":
+    name = sys.argv[1]
+    if name == "list":
+        print("\n".join(PROBES))
+        sys.exit(0)
+    fn, args = PROBES[name]
+    t = time.time()
+    try:
+        ok, msg = fn(*args)
+    except Exception as e:  # noqa: BLE001
+        ok, msg = False, f"{type(e).__name__}: {e}"
+    print(f"PROBE {name} {'OK' if ok else 'FAIL'} {msg} ({time.time() - t:.1f}s)", flush=True)
+    sys.exit(0 if ok else 1)
