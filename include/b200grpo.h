@@ -238,6 +238,16 @@ int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B
  * name in {"fwd_splits","two_cta","gemm_stages","watchdog_ms"}; returns previous value. */
 int b200grpo_set_tunable(const char* name, int value);
 
+/* Per-launch device timing (diagnostic, single-threaded): while enabled, every kernel group the
+ * library launches is bracketed by CUDA events on its stream.  read() waits for the recorded
+ * events, writes up to `capacity` (tag, milliseconds) pairs in launch order, clears the ring and
+ * returns the count.  Tags: 1 fwd GEMM+stats, 2 split merge, 3 finalize, 4 token loss,
+ * 5 bwd recompute->dlogits GEMM, 6 dH GEMM, 7 dW GEMM, 8 plain GEMM, 9 advantages, 10 bucket,
+ * 11 segments, 12 fused logits GEMM, 13 logits->dlogits pass, 14 split-K reduce.
+ * enable(0) switches it off. */
+int b200grpo_profile_enable(int capacity);
+int b200grpo_profile_read(int32_t* tags_host, float* ms_host, int capacity);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,10 +20,12 @@ from .grpo_oracle import (  # noqa: F401
     oracle_filter_zero_advantage_groups,
     oracle_linear_decay_coef,
     oracle_logprobs_entropy,
+    oracle_merge_stats,
     oracle_populate_rl_data,
     oracle_prepare_rl_fields,
     oracle_rl_step,
     oracle_segments,
     oracle_sentinel_batch,
+    oracle_shard_stats,
     oracle_token_loss,
 )

@@ -70,6 +70,8 @@ SIGNATURES = {
     "b200grpo_rl_step_host_workspace": (_sz, [_i, _i, _i]),
     "b200grpo_rl_step_host": (_i, [C.POINTER(HostBatch), _i, _i, _i, _p, _i64, _f, C.POINTER(LossCfg), _p, _p, _i, _i, _p, _p,
                                    _sz, _p]),
+    "b200grpo_profile_enable": (_i, [_i]),
+    "b200grpo_profile_read": (_i, [_p, _p, _i]),
     "b200grpo_gemm_bf16": (_i, [_p, _i64, _i, _p, _i64, _i, _p, _i64, _i, _i, _i, _i, _i, _p]),
 }
 
@@ -100,6 +102,24 @@ def check(code: int) -> None:
     if code != 0:
         msg = lib().b200grpo_last_error().decode(errors="replace")
         raise B200GrpoError(f"libb200grpo error {code}: {msg}")
+
+
+PROF_TAGS = {1: "fwd_gemm_stats", 2: "fwd_merge", 3: "finalize", 4: "token_loss", 5: "bwd_recompute_dlogits", 6: "bwd_dH_gemm",
+             7: "bwd_dW_gemm", 8: "gemm", 9: "group_advantage", 10: "bucket", 11: "segments", 12: "fused_logits_gemm",
+             13: "dlogits_pass", 14: "splitk_reduce"}
+
+
+def profile_enable(capacity: int) -> None:
+    check(lib().b200grpo_profile_enable(int(capacity)))
+
+
+def profile_read(capacity: int = 4096) -> list[tuple[str, float]]:
+    tags = (C.c_int32 * capacity)()
+    ms = (C.c_float * capacity)()
+    n = lib().b200grpo_profile_read(tags, ms, capacity)
+    if n < 0:
+        check(n)
+    return [(PROF_TAGS.get(tags[i], str(tags[i])), float(ms[i])) for i in range(n)]
 
 
 def set_tunable(name: str, value: int) -> int:

@@ -1,6 +1,7 @@
 // Library-wide plumbing: thread-local error text, device check, tunables.
 #include "common.cuh"
 #include <string.h>
+#include <vector>
 
 namespace b200grpo {
 
@@ -47,9 +48,52 @@ int check_device_sm100() {
 static int g_tunables[TUNE_COUNT] = {0, 0, 0, 4000};
 int get_tunable(int id) { return g_tunables[id]; }
 
+// ---- profiling ring (diagnostic; single-threaded use) -------------------------------------
+struct ProfSlot { cudaEvent_t a, b; int tag; };
+static std::vector<ProfSlot> g_prof;
+static int g_prof_used = 0;
+static bool g_prof_on = false;
+
+ProfScope::ProfScope(int tag, cudaStream_t s) : idx(-1), st(s) {
+  if (!g_prof_on || g_prof_used >= (int)g_prof.size()) return;
+  idx = g_prof_used++;
+  g_prof[idx].tag = tag;
+  cudaEventRecord(g_prof[idx].a, st);
+}
+ProfScope::~ProfScope() {
+  if (idx >= 0) cudaEventRecord(g_prof[idx].b, st);
+}
+
 }  // namespace b200grpo
 
 using namespace b200grpo;
+
+extern "C" int b200grpo_profile_enable(int capacity) {
+  if (int e = check_device_sm100()) return e;
+  g_prof_on = capacity > 0;
+  g_prof_used = 0;
+  while ((int)g_prof.size() < capacity) {
+    ProfSlot s;
+    B200_CUDA_OK(cudaEventCreate(&s.a));
+    B200_CUDA_OK(cudaEventCreate(&s.b));
+    s.tag = 0;
+    g_prof.push_back(s);
+  }
+  return B200GRPO_OK;
+}
+
+extern "C" int b200grpo_profile_read(int32_t* tags_host, float* ms_host, int capacity) {
+  const int n = g_prof_used < capacity ? g_prof_used : capacity;
+  for (int i = 0; i < n; ++i) {
+    B200_CUDA_OK(cudaEventSynchronize(g_prof[i].b));
+    float ms = 0.f;
+    B200_CUDA_OK(cudaEventElapsedTime(&ms, g_prof[i].a, g_prof[i].b));
+    tags_host[i] = g_prof[i].tag;
+    ms_host[i] = ms;
+  }
+  g_prof_used = 0;
+  return n;
+}
 
 extern "C" const char* b200grpo_last_error(void) { return g_err; }
 extern "C" int b200grpo_abi_version(void) { return B200GRPO_ABI_VERSION; }

@@ -80,6 +80,7 @@ extern "C" int b200grpo_group_advantage(const double* row_reward, const int32_t*
   }
   cudaStream_t st = (cudaStream_t)stream;
   GroupStat* stats = (GroupStat*)workspace;
+  ProfScope ps(PROF_ADVANTAGE, st);
   group_stats_kernel<<<ceil_div(n_groups, 128), 128, 0, st>>>(row_reward, group_key, row_offsets, n_rows, n_groups, stats);
   int grid = ceil_div(n_rows, 8);
   const int cap = sm_count() * 8;

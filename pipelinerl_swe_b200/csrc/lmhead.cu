@@ -195,7 +195,8 @@ extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* 
   CUtensorMap ta, tb;
   if (int e = make_ab_maps(&ta, &tb, hidden, ldh, 0, weight, ldw, 0, M, Vloc, H, ctas)) return e;
   cudaStream_t st = (cudaStream_t)stream;
-  if (int e = dispatch<EPI_FWD_STATS>(0, 0, ctas, ta, tb, p, st)) return e;
+  { ProfScope ps(PROF_FWD_GEMM, st); if (int e = dispatch<EPI_FWD_STATS>(0, 0, ctas, ta, tb, p, st)) return e; }
+  ProfScope ps(PROF_FWD_MERGE, st);
   fwd_merge_kernel<<<ceil_div(M, 256), 256, 0, st>>>((const float4*)workspace, p.n_splits, M, (float4*)stats);
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
@@ -204,6 +205,7 @@ extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* 
 extern "C" int b200grpo_lmhead_finalize(const float* stats, int R, int M, float* logprob, float* entropy, float* lse, void* stream) {
   if (int e = check_device_sm100()) return e;
   B200_REQUIRE(stats && logprob && entropy && R >= 1 && M >= 1, "lmhead_finalize: bad argument");
+  ProfScope ps(PROF_FINALIZE, (cudaStream_t)stream);
   finalize_kernel<<<ceil_div(M, 256), 256, 0, (cudaStream_t)stream>>>((const float4*)stats, R, M, logprob, entropy, lse);
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
@@ -236,6 +238,7 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
     p.lse = lse; p.entropy = entropy; p.coef_lp = coef_lp; p.coef_ent = coef_ent; p.grad_scale = grad_scale;
     p.dlogits = (__nv_bfloat16*)workspace; p.ldd = (long long)ldd;
     if (int e = make_ab_maps(&ta, &tb, hidden, ldh, 0, weight, ldw, 0, M, Vloc, H, ctas)) return e;
+    ProfScope ps(PROF_BWD_DLOGITS, st);
     if (int e = dispatch<EPI_BWD_DLOGITS>(0, 0, ctas, ta, tb, p, st)) return e;
   }
   if (grad_hidden) {  // 2. dH[M,H] = dlogits[M,V] . W[V,H]   (B is MN-major: vocab rows are the K axis)
@@ -243,6 +246,7 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
     fill_tiling(p, M, H, Vloc, ctas, 0);
     p.C = grad_hidden; p.ldc = ldgh; p.c_is_f32 = 0; p.accumulate = 0;
     if (int e = make_ab_maps(&ta, &tb, workspace, (long long)ldd, 0, weight, ldw, 1, M, H, Vloc, ctas)) return e;
+    ProfScope ps(PROF_BWD_DH, st);
     if (int e = dispatch<EPI_STORE>(0, 1, ctas, ta, tb, p, st)) return e;
   }
   if (grad_weight) {  // 3. dW[V,H] = dlogits^T[V,M] . hidden[M,H]   (both operands MN-major: tokens are the K axis)
@@ -250,6 +254,7 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
     fill_tiling(p, Vloc, H, M, ctas, 0);
     p.C = grad_weight; p.ldc = ldgw; p.c_is_f32 = grad_weight_is_f32; p.accumulate = accumulate;
     if (int e = make_ab_maps(&ta, &tb, workspace, (long long)ldd, 1, hidden, ldh, 1, Vloc, H, M, ctas)) return e;
+    ProfScope ps(PROF_BWD_DW, st);
     if (int e = dispatch<EPI_STORE>(1, 1, ctas, ta, tb, p, st)) return e;
   }
   return B200GRPO_OK;
@@ -266,5 +271,6 @@ extern "C" int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, co
   p.C = C; p.ldc = ldc; p.c_is_f32 = c_is_f32; p.accumulate = accumulate;
   CUtensorMap ta, tb;
   if (int e = make_ab_maps(&ta, &tb, A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, ctas)) return e;
+  ProfScope ps(PROF_GEMM, (cudaStream_t)stream);
   return dispatch<EPI_STORE>(a_mn_major ? 1 : 0, b_mn_major ? 1 : 0, ctas, ta, tb, p, (cudaStream_t)stream);
 }

@@ -90,6 +90,7 @@ extern "C" int b200grpo_segment_bounds(const int64_t* position_ids, int T, int32
   if (workspace_bytes < (size_t)n_blocks * sizeof(int)) { set_error("segment_bounds: workspace too small"); return B200GRPO_EWORKSPACE; }
   cudaStream_t st = (cudaStream_t)stream;
   int* counts = (int*)workspace;
+  ProfScope ps(PROF_SEGMENTS, st);
   seg_count_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts);
   seg_scan_kernel<<<1, 1024, 0, st>>>(counts, n_blocks, n_bounds);
   seg_scatter_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts, n_bounds, bounds);

@@ -298,6 +298,7 @@ extern "C" int b200grpo_token_loss(const float* logprob, const float* entropy, c
   a.partial_flag = (unsigned*)(ws + off_flag); a.ticket = (unsigned*)(ws + off_ticket);
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA_OK(cudaMemsetAsync(a.ticket, 0, sizeof(unsigned), st));
+  ProfScope ps(PROF_TOKEN_LOSS, st);
   token_loss_kernel<<<grid, TL_THREADS, 0, st>>>(a);
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;

@@ -12,10 +12,10 @@ import threading
 from dataclasses import dataclass
 
 import torch
-import torch.distributed as dist
 from torch import nn
 
 from . import ops
+from .vocab_parallel import exchange_stats, reduce_grad_hidden
 
 
 class LMHeadLogprobFunction(torch.autograd.Function):
@@ -29,10 +29,8 @@ class LMHeadLogprobFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, hidden, weight, targets, inv_temperature: float, group=None, v_offset: int = 0):
         stats = ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset)
-        if group is not None and dist.get_world_size(group) > 1:
-            gathered = torch.empty(dist.get_world_size(group), *stats.shape, dtype=stats.dtype, device=stats.device)
-            dist.all_gather_into_tensor(gathered, stats, group=group)
-            stats = gathered
+        if group is not None:
+            stats = exchange_stats(stats, group)  # [R,M,4], 16 B/token/rank over NCCL
         logprob, entropy, lse = ops.lmhead_finalize(stats)
         ctx.save_for_backward(hidden, weight, targets, lse, entropy)
         ctx.inv_temperature, ctx.group, ctx.v_offset = inv_temperature, group, v_offset
@@ -46,8 +44,8 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         need_h, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         gh, gw = ops.lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, ctx.inv_temperature, ctx.v_offset,
                                 need_grad_hidden=need_h, need_grad_weight=need_w)
-        if gh is not None and ctx.group is not None and dist.get_world_size(ctx.group) > 1:
-            dist.all_reduce(gh, group=ctx.group)  # dH = sum over vocab shards
+        if gh is not None and ctx.group is not None:
+            reduce_grad_hidden(gh, ctx.group)  # dH = sum over vocab shards
         return gh, gw, None, None, None, None
 
 

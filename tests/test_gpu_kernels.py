@@ -1,0 +1,227 @@
+"""GPU parity for the HBM-bound kernels: K3 token loss, segment bounds, K4 advantages, K6 buckets, and
+the host-buffer C entry point.  Integer / index / byte work must be bit-exact."""
+import copy
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from helpers import GOLDEN, StubLM, assert_stats_close, near_policy_logprobs, synthetic_packed_batch
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _to_dev(batch):
+    return {k: (v.to(_dev()) if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+
+
+# ---- segment boundaries: bit-exact (rl/__init__.py:159-170) ------------------------------------
+@pytest.mark.parametrize("T,p_zero,first", [(1, 0.0, 5), (9, 0.3, 0), (1024, 0.01, 7), (1025, 0.5, 0), (8192, 0.002, 3),
+                                            (1 << 20, 0.001, 0), (5000, 0.0, 9), (4097, 1.0, 0)])
+def test_segment_bounds_bit_exact(T, p_zero, first):
+    from pipelinerl_swe_b200 import ops
+    g = torch.Generator().manual_seed(T)
+    pos = torch.randint(1, 100, (T,), generator=g)
+    pos[torch.rand(T, generator=g) < p_zero] = 0
+    pos[0] = first
+    want, n = oracle.oracle_segments(pos.clone())
+    got = ops.segment_bounds(pos.to(_dev()))
+    assert got.dtype == torch.int32
+    assert got.cpu().tolist() == want.tolist()
+    assert got.numel() == n + 1
+
+
+# ---- K3: loss, 34 stats and the gradient coefficients vs the oracle -----------------------------
+K3_CASES = {
+    "ppo_kl": dict(policy_loss="ppo", kl_coef=0.1, final_kl_coef=0.1, batch_size=64, epsilon=0.2, clamp_log_ratio_ref_new_value=0.3),
+    "ppo_gn_of_ent": dict(policy_loss="ppo", kl_coef=0.02, final_kl_coef=0.3, entropy_bonus=0.01, final_entropy_bonus=0.02,
+                          group_normalization=True, overlong_filtering=True, batch_size=8, epsilon=0.05),
+    "reinforce": dict(policy_loss="reinforce", kl_coef=0.1, final_kl_coef=0.1, batch_size=16, epsilon=0.1),
+    "reinforce_rewards_relu": dict(policy_loss="reinforce", use_advantages=False, relu_log_p_weights=True, kl_coef=0.0,
+                                   final_kl_coef=0.0, batch_size=4),
+}
+
+
+@pytest.mark.parametrize("name", list(K3_CASES))
+@pytest.mark.parametrize("packed,lens,rows", [(True, [700, 33, 1, 2, 1500, 260], 1), (False, [257], 5), (True, [8192], 1)])
+def test_token_loss_vs_oracle(name, packed, lens, rows):
+    from pipelinerl_swe_b200 import RLConfig
+    from pipelinerl_swe_b200 import rl as prl
+    cfgkw = K3_CASES[name]
+    batch = synthetic_packed_batch(lens, 1000, seed=len(name) + rows, rows=rows, packed=packed)
+    L = batch["labels"].shape[1]
+    g = torch.Generator().manual_seed(1)
+    lp = -(torch.rand(rows, L - 1, generator=g) * 2 + 0.05)
+    ent = torch.rand(rows, L - 1, generator=g) * 3
+    m = (batch["labels"][:, 1:] != -100).float()
+    batch["old_logprobs"][:, 1:] = (lp + 0.2 * torch.randn(lp.shape, generator=g)) * m
+    batch["ref_logprobs"][:, 1:] = (lp + 0.4 * torch.randn(lp.shape, generator=g)) * m
+    ocfg = oracle.OracleRLConfig(**cfgkw)
+    lp_r, ent_r = lp.clone().requires_grad_(True), ent.clone().requires_grad_(True)
+    want_loss, want_stats = oracle.oracle_token_loss(lp_r, ent_r, batch, 3, 10, ocfg)
+    want_loss.backward()
+
+    cfg = prl.make_loss_cfg(RLConfig(**cfgkw), 3, 10, packed, False)
+    db = _to_dev(batch)
+    lp_d, ent_d = lp.to(_dev()).requires_grad_(True), ent.to(_dev()).requires_grad_(True)
+    sink = {}
+    loss = prl.TokenLossFunction.apply(lp_d, ent_d, None, db, cfg, sink)
+    loss.backward()
+    metr = sink["metrics"].tolist()
+    stats = prl.stats_from_metrics(metr, cfg, batch["input_ids"].numel(), False,
+                                   (oracle.oracle_linear_decay_coef(3, 10, ocfg.kl_coef, ocfg.final_kl_coef),
+                                    oracle.oracle_linear_decay_coef(3, 10, ocfg.entropy_bonus, ocfg.final_entropy_bonus)))
+    assert abs(loss.item() - want_loss.item()) <= 1e-4 * abs(want_loss.item()) + 1e-6
+    assert_stats_close(stats, want_stats, rtol=2e-4, atol=1e-5)
+    # integer-valued stats are exact
+    for k in ("num_output_tokens_sum", "num_nans", "input_size"):
+        assert stats[k] == want_stats[k]
+    torch.testing.assert_close(lp_d.grad.cpu(), lp_r.grad, rtol=1e-4, atol=1e-7)
+    torch.testing.assert_close(ent_d.grad.cpu(), ent_r.grad, rtol=1e-4, atol=1e-9)
+
+
+def test_token_loss_flags_nonfinite():
+    from pipelinerl_swe_b200 import RLConfig
+    from pipelinerl_swe_b200 import rl as prl
+    batch = synthetic_packed_batch([40, 24], 100, seed=2)
+    L = batch["labels"].shape[1]
+    lp = -torch.rand(1, L - 1)
+    lp[0, 30] = float("nan")
+    cfg = prl.make_loss_cfg(RLConfig(batch_size=2), 0, 1, True, False)
+    sink = {}
+    prl.TokenLossFunction.apply(lp.to(_dev()), torch.zeros(1, L - 1, device=_dev()), None, _to_dev(batch), cfg, sink)
+    with pytest.raises(AssertionError):
+        prl.stats_from_metrics(sink["metrics"].tolist(), cfg, L, False)
+
+
+def test_rl_step_requires_cuda_batch():
+    from pipelinerl_swe_b200 import RLConfig, rl_step
+    from pipelinerl_swe_b200._abi import B200GrpoError
+    batch = synthetic_packed_batch([20, 12], 100, seed=2)
+    model = StubLM(32, 100, 32)
+    with pytest.raises(B200GrpoError):
+        rl_step(model, batch, 0, 1, RLConfig(batch_size=2))
+
+
+# ---- rl_step on a mid-size packed row vs the oracle (tests the whole K1->K3->K2 chain) ------------
+@pytest.mark.parametrize("policy", ["ppo", "reinforce"])
+def test_rl_step_midsize_vs_oracle(policy):
+    from pipelinerl_swe_b200 import RLConfig, rl_step
+    H, V, lens = 256, 32000, [300, 211, 129, 384]
+    T = sum(lens)
+    batch = synthetic_packed_batch(lens, V, seed=11, n_prompt=32)
+    model = StubLM(H, V, T, seed=5, w_std=0.05)
+    cfgkw = dict(policy_loss=policy, batch_size=4, kl_coef=0.1, final_kl_coef=0.05, temperature=0.9, epsilon=0.02,
+                 entropy_bonus=0.001, final_entropy_bonus=0.001)
+    near_policy_logprobs(batch, model.hidden.detach()[0], model.lm_head.weight.detach(), 0.9, seed=3)
+    hidden = model.hidden.detach().float()[0].requires_grad_(True)
+    weight = model.lm_head.weight.detach().float().requires_grad_(True)
+    want_loss, want_stats = oracle.oracle_rl_step(hidden, weight, batch, 2, 10, oracle.OracleRLConfig(**cfgkw))
+    want_loss.backward()
+    model = model.to(_dev())
+    loss, stats = rl_step(model, _to_dev(batch), 2, 10, RLConfig(**cfgkw))
+    loss.backward()
+    assert abs(loss.item() - want_loss.item()) <= 1e-3 * abs(want_loss.item()) + 1e-6
+    assert_stats_close(stats, want_stats, rtol=2e-3, atol=2e-4)
+    gw, gh = model.lm_head.weight.grad.float().cpu(), model.hidden.grad.float().cpu()[0]
+    assert float((gw - weight.grad).abs().max() / weight.grad.abs().max()) < 2e-2
+    assert float((gh - hidden.grad).abs().max() / hidden.grad.abs().max()) < 2e-2
+
+
+# ---- K4: advantages vs the reference's pandas output (golden) and the oracle -------------------
+ADV = json.load(open(os.path.join(GOLDEN, "advantages.json")))
+
+
+@pytest.mark.parametrize("name", [k for k in ADV if k != "collate_packed"])
+def test_populate_rl_data_vs_reference_golden(name):
+    from pipelinerl_swe_b200 import RLConfig, populate_rl_data
+    case = ADV[name]
+    rows = copy.deepcopy(case["input"])
+    res = populate_rl_data(rows, case["eos"], RLConfig(**case["cfg"]))
+    assert res is rows
+    for got, want in zip(res, case["output"]):
+        assert got["num_labels"] == want["num_labels"]          # integer: exact
+        assert got["overflow"] == want["overflow"]              # 0.0 / 1.0: exact
+        g = np.asarray(got["group_tokens"], dtype=np.float32)
+        w = np.asarray(want["group_tokens"], dtype=np.float32)
+        assert g.tobytes() == w.tobytes()                       # fp32 view bit-exact
+        ga = np.asarray(got["advantages"], dtype=np.float32)
+        wa = np.asarray(want["advantages"], dtype=np.float32)
+        np.testing.assert_allclose(ga, wa, rtol=2e-7, atol=1e-9)  # <= 1 ulp (fp64 summation order)
+
+
+def test_populate_rl_data_large_vs_oracle():
+    from pipelinerl_swe_b200 import RLConfig, populate_rl_data
+    g = np.random.default_rng(3)
+    rows = []
+    for gi in range(64):
+        for a in range(16):
+            n = int(g.integers(8, 400))
+            ids = g.integers(3, 1000, n).tolist()
+            if (gi + a) % 4:
+                ids[-1] = 2
+            npmt = int(g.integers(1, 6))
+            labels = [-100] * npmt + ids[npmt:]
+            rows.append(dict(group_id=f"g{gi}", rollout_index=a, step_index=0, input_ids=ids, labels=labels,
+                             rewards=[float(g.integers(0, 2))] * n, advantages=[0.0] * n, overflow=[0] * n,
+                             group_tokens=[0] * n, num_labels=[1 if t != -100 else 0 for t in labels]))
+    want = oracle.oracle_populate_rl_data(copy.deepcopy(rows), 2, oracle.OracleRLConfig(divide_advantage_by_std=True))
+    got = populate_rl_data(rows, 2, RLConfig(divide_advantage_by_std=True))
+    for a, b in zip(got, want):
+        assert a["num_labels"] == b["num_labels"] and a["overflow"] == b["overflow"]
+        assert np.asarray(a["group_tokens"], np.float32).tobytes() == np.asarray(b["group_tokens"], np.float32).tobytes()
+        np.testing.assert_allclose(np.asarray(a["advantages"], np.float32), np.asarray(b["advantages"], np.float32),
+                                   rtol=3e-7, atol=1e-9)
+
+
+# ---- K6: bucket pack / unpack round trip, byte-exact --------------------------------------------
+def test_bucket_roundtrip_bit_exact():
+    from pipelinerl_swe_b200 import ops
+    d = _dev()
+    g = torch.Generator(device=d).manual_seed(0)
+    shapes = [(3584,), (512, 3584), (1,), (7,), (18944, 128), (0,), (129, 3), (1000003,)]
+    src = [torch.randn(*s, device=d, generator=g).bfloat16() for s in shapes]
+    src[4] = torch.randn(*shapes[4], device=d, generator=g)  # an fp32 master weight: cast fused into the pack
+    n = ops.bucket_numel(src)
+    assert n == sum((t.numel() + 7) // 8 * 8 for t in src)
+    bucket = torch.zeros(n, dtype=torch.bfloat16, device=d)
+    ops.bucket_pack(src, bucket)
+    off = 0
+    for t in src:  # wire content == param.data.bfloat16() (finetune_loop.py:247)
+        want = t.bfloat16().reshape(-1)
+        assert torch.equal(bucket[off:off + t.numel()].view(torch.int16), want.view(torch.int16))
+        off += (t.numel() + 7) // 8 * 8
+    dst = [torch.empty_like(t) for t in src]
+    ops.bucket_unpack(bucket, dst)
+    for a, b in zip(dst, src):
+        assert torch.equal(a.bfloat16().view(torch.int16), b.bfloat16().view(torch.int16))
+
+
+# ---- host-buffer C entry point == the piecewise calls -------------------------------------------
+def test_rl_step_host_entry_matches_piecewise():
+    from pipelinerl_swe_b200 import RLConfig, rl_step
+    from pipelinerl_swe_b200 import rl as prl
+    from pipelinerl_swe_b200 import host_step
+    H, V, lens = 128, 5000, [100, 60, 95]
+    T = sum(lens)
+    batch = synthetic_packed_batch(lens, V, seed=21)
+    model = StubLM(H, V, T, seed=8).to(_dev())
+    cfgkw = dict(policy_loss="ppo", batch_size=3, kl_coef=0.1, final_kl_coef=0.1, temperature=1.0)
+    loss, stats = rl_step(model, _to_dev(batch), 0, 1, RLConfig(**cfgkw))
+    loss.backward()
+    step = host_step.HostRLStep(T, H, V, model.lm_head.weight.detach(), RLConfig(**cfgkw), 0, 1)
+    step.load_batch(batch, model.hidden.detach()[0].cpu())
+    m = step.run(want_grad_hidden=True)
+    torch.cuda.synchronize()
+    stats2 = prl.stats_from_metrics(m.tolist(), step.cfg, T, False)
+    assert_stats_close(stats2, stats, rtol=1e-6, atol=1e-7)
+    assert torch.equal(step.grad_weight, model.lm_head.weight.grad)
+    assert torch.equal(step.grad_hidden_host.view(torch.int16)[:-1], model.hidden.grad[0].cpu().view(torch.int16)[:-1])

@@ -1,0 +1,175 @@
+"""GPU parity: the CUDA path (through the C ABI) against the oracle and the reference's golden vectors.
+
+Tolerances are the north-star's: logprobs / loss 1e-3 relative (bf16 inputs, fp32 accumulate),
+gradients 2e-2 relative (max-norm), advantages and segment indexing bit-exact.
+"""
+import copy
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from helpers import (GOLDEN, StubLM, assert_stats_close, golden_rl_cases, load_rl_case, near_policy_logprobs,
+                     synthetic_packed_batch)
+
+pytestmark = pytest.mark.gpu
+
+LP_RTOL = 1e-3   # logprobs, loss, stats
+GRAD_RTOL = 2e-2  # gradients, relative to the largest reference entry
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _to_dev(batch):
+    return {k: (v.to(_dev()) if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+
+
+def _rel(a, b):
+    return float((a.float().cpu() - b.float().cpu()).abs().max() / (b.float().abs().max() + 1e-20))
+
+
+class GoldenLM(torch.nn.Module):
+    """hidden/weight of a golden case as a model whose forward goes through lm_head."""
+
+    def __init__(self, hidden, weight, values=None):
+        super().__init__()
+        self.hidden = torch.nn.Parameter(hidden.to(torch.bfloat16))
+        V, H = weight.shape
+        self.lm_head = torch.nn.Linear(H, V, bias=False, dtype=torch.bfloat16)
+        with torch.no_grad():
+            self.lm_head.weight.copy_(weight.to(torch.bfloat16))
+        if values is not None:
+            self.value_head = True
+            self.values = torch.nn.Parameter(values.float())
+
+    def forward(self, **kw):
+        import types
+        out = types.SimpleNamespace(logits=self.lm_head(self.hidden))
+        if hasattr(self, "values"):
+            out.value = self.values
+        return out
+
+
+# ---------------------------------------------------------------------------------------------
+# rl_step end to end vs the REFERENCE's own outputs (tests/golden, generated from /root/reference)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", golden_rl_cases())
+def test_rl_step_vs_reference_golden(name):
+    from pipelinerl_swe_b200 import RLConfig, rl_step
+    batch, ocfg, meta, x = load_rl_case(name)
+    model = GoldenLM(x["hidden"], x["weight"], x.get("values")).to(_dev())
+    cfg = RLConfig(**meta["cfg"])
+    loss, stats = rl_step(model, _to_dev(batch), meta["step"], meta["max_step"], cfg)
+    assert loss.dim() == 0 and loss.requires_grad
+    want = float(x["loss"])
+    assert abs(loss.item() - want) <= LP_RTOL * abs(want) + 1e-5, (loss.item(), want)
+    assert_stats_close(stats, meta["stats"], rtol=2e-3, atol=2e-4)
+    assert list(stats.keys()) == list(meta["stats"].keys()) or set(stats) == set(meta["stats"])
+    if "grad_weight" in x:
+        loss.backward()
+        assert _rel(model.lm_head.weight.grad, x["grad_weight"]) < GRAD_RTOL
+        assert _rel(model.hidden.grad.reshape(x["grad_hidden"].shape), x["grad_hidden"]) < GRAD_RTOL
+        if "grad_values" in x:
+            assert _rel(model.values.grad, x["grad_values"]) < GRAD_RTOL
+    else:  # sentinel: loss*0 must still backprop (finetune_loop.py:664-666)
+        (loss * 0.0).backward()
+        assert torch.count_nonzero(model.lm_head.weight.grad) == 0
+
+
+# ---------------------------------------------------------------------------------------------
+# K1 / K2 at the real vocab size vs the oracle (fp32 math on the same bf16 values)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("two_cta", [0, 1])
+@pytest.mark.parametrize("T,H,V,temp", [(513, 896, 151936, 1.0), (300, 1536, 152064, 0.7)])
+def test_lmhead_fwd_bwd_vs_oracle(T, H, V, temp, two_cta):
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", two_cta)
+    try:
+        g = torch.Generator().manual_seed(T + H)
+        hidden = torch.randn(T, H, generator=g).bfloat16()
+        weight = (torch.randn(V, H, generator=g) * 0.03).bfloat16()
+        ids = torch.randint(0, V, (T,), generator=g)
+        hr, wr = hidden.float().requires_grad_(True), weight.float().requires_grad_(True)
+        lp_ref, ent_ref = oracle.oracle_logprobs_entropy(hr, wr, ids, temp)
+        c_lp = torch.randn(T - 1, generator=g) * 0.1
+        c_ent = torch.randn(T - 1, generator=g) * 0.01
+        ((lp_ref * c_lp).sum() + (ent_ref * c_ent).sum()).backward()
+
+        d = _dev()
+        h, w, tgt = hidden[:-1].contiguous().to(d), weight.to(d), ids[1:].contiguous().to(d)
+        stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp)
+        lp, ent, lse = ops.lmhead_finalize(stats)
+        assert float((lp.cpu() - lp_ref.detach()).abs().max()) <= LP_RTOL * float(lp_ref.abs().max())
+        assert float((ent.cpu() - ent_ref.detach()).abs().max()) <= LP_RTOL * float(ent_ref.abs().max())
+        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp.to(d), c_ent.to(d), 1.0 / temp)
+        assert _rel(gh, hr.grad[:-1]) < GRAD_RTOL
+        assert _rel(gw, wr.grad) < GRAD_RTOL
+    finally:
+        _abi.set_tunable("two_cta", 0)
+
+
+def test_lmhead_vocab_shards_equal_unsharded():
+    """Config-4 semantics on one GPU: R contiguous vocab shards (v_offset) merged by finalize == unsharded."""
+    from pipelinerl_swe_b200 import ops
+    d = _dev()
+    g = torch.Generator(device=d).manual_seed(4)
+    M, H, V = 700, 512, 152064
+    h = torch.randn(M, H, device=d, generator=g).bfloat16()
+    w = (torch.randn(V, H, device=d, generator=g) * 0.04).bfloat16()
+    tgt = torch.randint(0, V, (M,), device=d, generator=g)
+    lp0, ent0, lse0 = ops.lmhead_finalize(ops.lmhead_fwd_stats(h, w, tgt, 1.0))
+    c_lp = torch.randn(M, device=d, generator=g) * 0.1
+    c_ent = torch.randn(M, device=d, generator=g) * 0.01
+    gh0, gw0 = ops.lmhead_bwd(h, w, tgt, lse0, ent0, c_lp, c_ent, 1.0)
+    for R in (2, 4, 8):
+        Vs = V // R
+        parts = [ops.lmhead_fwd_stats(h, w[r * Vs:(r + 1) * Vs], tgt, 1.0, v_offset=r * Vs) for r in range(R)]
+        lp, ent, lse = ops.lmhead_finalize(torch.stack(parts))
+        assert float((lp - lp0).abs().max()) < 1e-4 and float((ent - ent0).abs().max()) < 1e-4
+        gh = torch.zeros(M, H, device=d)
+        for r in range(R):
+            gh_r, gw_r = ops.lmhead_bwd(h, w[r * Vs:(r + 1) * Vs], tgt, lse, ent, c_lp, c_ent, 1.0, v_offset=r * Vs)
+            gh += gh_r.float()
+            assert _rel(gw_r, gw0[r * Vs:(r + 1) * Vs]) < 1e-2
+        assert _rel(gh, gh0) < 1e-2
+
+
+def test_lmhead_properties_full_size():
+    """BASELINE config-2 size (T=8192, H=1536, V=151936): size-independent properties."""
+    from pipelinerl_swe_b200 import ops
+    d = _dev()
+    g = torch.Generator(device=d).manual_seed(9)
+    M, H, V = 8191, 1536, 151936
+    h = torch.randn(M, H, device=d, generator=g).bfloat16()
+    w = (torch.randn(V, H, device=d, generator=g) * 0.02).bfloat16()
+    tgt = torch.randint(0, V, (M,), device=d, generator=g)
+    lp, ent, lse = ops.lmhead_finalize(ops.lmhead_fwd_stats(h, w, tgt, 1.0))
+    assert bool((lp <= 0).all()) and bool(torch.isfinite(lp).all())
+    assert bool((ent >= 0).all()) and float(ent.max()) <= float(np.log(V)) + 1e-3
+    # spot rows against a torch fp32 computation of the same rows
+    rows = torch.tensor([0, 1, 127, 128, 4095, 8190], device=d)
+    z = h[rows].float() @ w.float().t()
+    logp = torch.log_softmax(z, -1)
+    assert float((lp[rows] - logp.gather(1, tgt[rows, None]).squeeze(1)).abs().max()) < 2e-3
+    assert float((ent[rows] + (logp.exp() * logp).sum(-1)).abs().max()) < 2e-3
+    # backward is linear in the coefficients; sum_j dlogits = -0 => dH of a pure-entropy-free uniform coef is finite
+    c = torch.randn(M, device=d, generator=g) * 0.1
+    zero = torch.zeros(M, device=d)
+    gh1, gw1 = ops.lmhead_bwd(h, w, tgt, lse, ent, c, zero, 1.0)
+    gh2, gw2 = ops.lmhead_bwd(h, w, tgt, lse, ent, 2 * c, zero, 1.0)
+    assert _rel(gh2, 2 * gh1.float()) < 1e-2 and _rel(gw2, 2 * gw1.float()) < 1e-2
+    # rows with a zero coefficient get exactly zero dH
+    c0 = c.clone(); c0[::2] = 0
+    gh3, _ = ops.lmhead_bwd(h, w, tgt, lse, ent, c0, zero, 1.0, need_grad_weight=False)
+    assert torch.count_nonzero(gh3[::2]) == 0
+    # dW check on a vocab slice against torch: dW[v] = sum_t dlogits[t,v] h[t]
+    vs = slice(1000, 1256)
+    p = torch.exp(h.float() @ w[vs].float().t() - lse[:, None])
+    onehot = (tgt[:, None] == torch.arange(1000, 1256, device=d)[None]).float()
+    dl = c[:, None] * (onehot - p)
+    assert _rel(gw1[vs], dl.t() @ h.float()) < GRAD_RTOL

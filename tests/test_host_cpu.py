@@ -1,0 +1,155 @@
+"""CPU: host logic of the drop-in layer vs the reference's golden outputs, the C-ABI library's exported
+symbols vs include/b200grpo.h, and loud failure without a GPU (no CPU fallback)."""
+import copy
+import ctypes
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from helpers import GOLDEN, StubLM, synthetic_packed_batch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ADV = json.load(open(os.path.join(GOLDEN, "advantages.json")))
+
+
+def _header_symbols():
+    src = open(os.path.join(ROOT, "include", "b200grpo.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200grpo_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_header_symbol():
+    from pipelinerl_swe_b200 import _abi
+    names = _header_symbols()
+    assert len(names) >= 20
+    handle = ctypes.CDLL(_abi.LIB_PATH)
+    for n in names:
+        assert hasattr(handle, n), f"libb200grpo.so does not export {n}"
+    assert set(names) == set(_abi.SIGNATURES), set(names) ^ set(_abi.SIGNATURES)
+    assert _abi.lib().b200grpo_abi_version() == 1
+
+
+def test_struct_layouts_match_header():
+    from pipelinerl_swe_b200 import _abi
+    assert ctypes.sizeof(_abi.LossCfg) == 8 * 4 + 6 * 4
+    assert ctypes.sizeof(_abi.HostBatch) == 11 * ctypes.sizeof(ctypes.c_void_p)
+    src = open(os.path.join(ROOT, "include", "b200grpo.h")).read()
+    body = src[src.index("B200GRPO_M_LOSS = 0"):src.index("B200GRPO_M_COUNT")]
+    slots = re.findall(r"B200GRPO_(M_[A-Z0-9_]+)", body)
+    for i, s in enumerate(slots):
+        assert getattr(_abi, s) == i, s
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback():
+    from pipelinerl_swe_b200 import RLConfig, _abi, ops, rl_step
+    batch = synthetic_packed_batch([20, 12], 100, seed=2)
+    with pytest.raises(_abi.B200GrpoError):
+        rl_step(StubLM(32, 100, 32), batch, 0, 1, RLConfig(batch_size=2))
+    with pytest.raises(_abi.B200GrpoError):
+        ops.segment_bounds(torch.zeros(8, dtype=torch.int64))
+    # the C side refuses too: no device -> error code + message, never a computed answer
+    rc = _abi.lib().b200grpo_lmhead_finalize(None, 1, 1, None, None, None, None)
+    assert rc != 0 and _abi.lib().b200grpo_last_error()
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "pipelinerl_swe_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+
+
+# ---- host-side mirrors of the reference's data model, vs golden ---------------------------------
+def test_collate_packed_vs_reference_golden():
+    from pipelinerl_swe_b200 import collate_packed
+    case = ADV["collate_packed"]
+    tok = type("Tok", (), {"eos_token_id": case["eos"]})()
+    got = collate_packed(copy.deepcopy(case["examples"]), tok, case["seq_parallel"])
+    for k, want in case["batch"].items():
+        g = getattr(got, k)
+        if isinstance(g, torch.Tensor):
+            assert g.tolist() == want, k
+        else:
+            assert g == want, k
+    assert got.seq_boundaries.dtype == torch.int32 and got.input_ids.dtype == torch.int64
+    assert got.rewards.dtype == torch.float32
+
+
+def test_make_slices_and_sentinel():
+    from pipelinerl_swe_b200 import collate_packed, create_sentinel_batch
+    case = ADV["collate_packed"]
+    tok = type("Tok", (), {"eos_token_id": 2})()
+    pb = collate_packed(copy.deepcopy(case["examples"]), tok, 4)
+    sl = pb.make_slices(4)
+    assert len(sl) == 4 and all(s.input_ids.shape[1] == pb.input_ids.shape[1] // 4 for s in sl)
+    assert torch.equal(torch.cat([s.labels for s in sl], 1), pb.labels)
+    with pytest.raises(ValueError):
+        pb.make_slices(7)
+    sb = create_sentinel_batch(None, tok, model_version=7)
+    z = np.load(os.path.join(GOLDEN, "rl_step_sentinel.npz"))
+    for k in ("input_ids", "labels", "position_ids", "group_tokens", "num_labels", "seq_boundaries"):
+        assert getattr(sb, k).tolist() == z[k].tolist(), k
+    assert sb.sentinel and sb.is_packed and sb.model_version == 7
+
+
+def test_prepare_rl_fields_and_filter():
+    from pipelinerl_swe_b200 import filter_zero_advantage_groups, prepare_rl_fields
+    enc = dict(input_ids=[5, 6, 7, 8], labels=[-100, -100, 7, 8])
+    got = prepare_rl_fields(dict(enc), 0.5, [-0.1, -0.2], [-0.3, -0.4])
+    want = oracle.oracle_prepare_rl_fields(dict(enc), 0.5, [-0.1, -0.2], [-0.3, -0.4])
+    assert got == want
+    with pytest.raises(AssertionError):
+        prepare_rl_fields(dict(enc), 0.5, [-0.1], [-0.3])
+    rows = [dict(group_id="a", advantages=[0.0, 1e-7]), dict(group_id="b", advantages=[0.0, 0.5]), dict(group_id="a", advantages=[0.0])]
+    kept, dropped = filter_zero_advantage_groups(rows)
+    assert dropped == 2 and [r["group_id"] for r in kept] == ["b"]
+
+
+def test_aggregate_rl_stats_vs_reference_golden():
+    from pipelinerl_swe_b200 import aggregate_rl_stats
+    case = json.load(open(os.path.join(GOLDEN, "aggregate.json")))
+    got = aggregate_rl_stats(case["input"], case["num_samples"])
+    assert got.keys() == case["output"].keys()
+    for k in got:
+        assert abs(got[k] - case["output"][k]) < 1e-6
+
+
+def test_rlconfig_ignores_unknown_keys_like_reference():
+    from pipelinerl_swe_b200 import RLConfig, linear_decay_coef
+    c = RLConfig(policy_loss="reinforce", aggregate_loss="sum", reward_minus_kl_coef=0.3)
+    assert c.policy_loss == "reinforce" and not hasattr(c, "aggregate_loss")
+    assert linear_decay_coef(3, 10, 0.1, 0.2) == oracle.oracle_linear_decay_coef(3, 10, 0.1, 0.2)
+
+
+def test_rollout_scalars_host_side():
+    from pipelinerl_swe_b200.advantage import rollout_scalars
+    case = ADV["singleton_and_steps"]
+    reward, gkey, offsets, nlab, eos, n_groups, tok = rollout_scalars(copy.deepcopy(case["input"]), case["eos"])
+    rows = case["input"]
+    assert offsets.tolist() == np.concatenate([[0], np.cumsum([len(r["input_ids"]) for r in rows])]).tolist()
+    assert n_groups == len({f"{r['group_id']}_{r['step_index']}" for r in rows})
+    assert nlab.tolist() == [sum(t != -100 for t in r["labels"]) for r in rows]
+    assert eos.tolist() == [int(case["eos"] in r["input_ids"]) for r in rows]
+    assert tok is None and reward.dtype == np.float64
+
+
+def test_plan_buckets():
+    from pipelinerl_swe_b200.weight_update import ParameterInfo, plan_buckets
+    infos = [ParameterInfo(name=f"p{i}", shape=s, dtype="torch.bfloat16") for i, s in
+             enumerate([[3584], [3584, 3584], [5], [152064, 3584], [18944, 3584], [7]])]
+    plan = plan_buckets(infos, 64 << 20)
+    assert [i for b in plan for i in b] == list(range(len(infos)))  # order preserved, nothing lost
+    assert [3] in plan                                               # oversize parameter gets its own bucket
+    cap = (64 << 20) // 2
+    for b in plan:
+        n = sum((int(np.prod(infos[i].shape)) + 7) // 8 * 8 for i in b)
+        assert n <= cap or len(b) == 1
+    assert plan_buckets(infos, 1 << 40) == [list(range(len(infos)))]

@@ -1,0 +1,143 @@
+"""CPU, world_size 2 over gloo: the host-side multi-rank logic (no CUDA kernels run here).
+
+ * vocab-parallel exchange: every rank reduces its vocab shard to [M,4] partials (the oracle stands in for
+   K1, which needs a GPU), ``exchange_stats`` all-gathers them, the merge equals the unsharded oracle and is
+   bit-identical on both ranks (so K3 needs no further exchange).
+ * weight update: sender and receivers derive the same bucket plan from one WeightUpdateRequest, and a
+   bucket broadcast delivers byte-identical parameters (pack/unpack emulated with torch on CPU tensors).
+"""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _init(rank, world, port):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+
+def _vocab_parallel_worker(rank, world, port, q):
+    _init(rank, world, port)
+    import oracle
+    from pipelinerl_swe_b200.vocab_parallel import exchange_stats, reduce_grad_hidden, shard_range
+    g = torch.Generator().manual_seed(0)
+    M, H, V, temp = 37, 16, 1003, 0.8
+    hidden = torch.randn(M, H, generator=g).bfloat16()
+    weight = (torch.randn(V, H, generator=g) * 0.3).bfloat16()
+    ids = torch.randint(0, V, (M + 1,), generator=g)
+    b, e = shard_range(V, world, rank)
+    stats = oracle.oracle_shard_stats(hidden, weight[b:e], ids[1:], b, temp)
+    allstats = exchange_stats(stats)
+    assert allstats.shape == (world, M, 4)
+    lp, ent, lse = oracle.oracle_merge_stats(allstats)
+    hfull = torch.cat([hidden, hidden[:1]])
+    lp_ref, ent_ref = oracle.oracle_logprobs_entropy(hfull, weight, ids, temp)
+    ok = bool(torch.allclose(lp, lp_ref, rtol=1e-5, atol=1e-5) and torch.allclose(ent, ent_ref, rtol=1e-5, atol=1e-5))
+    # dH = sum over shards of dlogits_r . W_r
+    p = torch.exp((hidden.float() @ weight[b:e].float().t()) / temp - lse[:, None])
+    gh = reduce_grad_hidden((-p) @ weight[b:e].float())
+    p_full = torch.softmax((hidden.float() @ weight.float().t()) / temp, -1)
+    ok = ok and bool(torch.allclose(gh, (-p_full) @ weight.float(), rtol=1e-4, atol=1e-4))
+    gathered = [None] * world
+    dist.all_gather_object(gathered, lp.numpy().tobytes())
+    ok = ok and all(x == gathered[0] for x in gathered)  # bit-identical on every rank
+    q.put((rank, ok, (b, e)))
+    dist.destroy_process_group()
+
+
+def _weight_update_worker(rank, world, port, q):
+    _init(rank, world, port)
+    from pipelinerl_swe_b200.weight_update import _bucket_elems, make_request, plan_buckets
+    g = torch.Generator().manual_seed(1)
+    shapes = [(64,), (33, 64), (5,), (1000, 64), (7, 3), (64,)]
+    params = [(f"p{i}", torch.randn(*s, generator=g)) for i, s in enumerate(shapes)]  # fp32 master weights
+    box = [make_request(params, version=3)] if rank == 0 else [None]
+    dist.broadcast_object_list(box, src=0)  # stands in for the HTTP POST of finetune_loop.py:157-172
+    req = box[0]
+    plan = plan_buckets(req.parameters_info, 64 * 1024)
+    ok = len(plan) > 1
+    got = {}
+    for idxs in plan:
+        n = _bucket_elems(req.parameters_info, idxs)
+        buf = torch.zeros(n, dtype=torch.bfloat16)
+        if rank == 0:
+            off = 0
+            for i in idxs:
+                t = params[i][1].bfloat16().reshape(-1)
+                buf[off:off + t.numel()] = t
+                off += (t.numel() + 7) // 8 * 8
+        dist.broadcast(buf, src=0)
+        off = 0
+        for i in idxs:
+            info = req.parameters_info[i]
+            numel = 1
+            for s in info.shape:
+                numel *= s
+            got[info.name] = buf[off:off + numel].view(tuple(info.shape)).clone()
+            off += (numel + 7) // 8 * 8
+    for name, p in params:  # every rank regenerates the same tensors -> byte equality with param.data.bfloat16()
+        ok = ok and torch.equal(got[name].view(torch.int16), p.bfloat16().view(torch.int16))
+    q.put((rank, ok, [list(b) for b in plan]))
+    dist.destroy_process_group()
+
+
+def _guard(worker, rank, world, port, q):
+    try:
+        worker(rank, world, port, q)
+    except Exception as e:  # noqa: BLE001  -- report instead of letting the parent wait for the timeout
+        import traceback
+        traceback.print_exc()
+        q.put((rank, False, repr(e)))
+
+
+def _run(worker, world=2):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_guard, args=(worker, r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok, _ in res), res
+    return sorted(res)
+
+
+def test_vocab_parallel_exchange_world2():
+    res = _run(_vocab_parallel_worker)
+    assert all(ok for _, ok, _ in res)
+    (b0, e0), (b1, e1) = res[0][2], res[1][2]
+    assert b0 == 0 and e0 == b1 and e1 == 1003 and (e0 - b0) % 8 == 0
+
+
+def test_weight_update_plan_world2():
+    res = _run(_weight_update_worker)
+    assert all(ok for _, ok, _ in res)
+    assert res[0][2] == res[1][2]
+
+
+def test_shard_range_covers_vocab():
+    from pipelinerl_swe_b200.vocab_parallel import shard_range
+    for V in (151936, 152064, 1003, 7):
+        for R in (1, 2, 4, 8):
+            cuts = [shard_range(V, R, r) for r in range(R)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == V
+            assert all(a[1] == b[0] for a, b in zip(cuts[:-1], cuts[1:]))
