@@ -44,7 +44,7 @@ CONFIGS = {
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--steps", type=int, default=32)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="c3", choices=sorted(CONFIGS))
@@ -101,15 +101,16 @@ def reference_step_cpu(hidden, weight, batch, cfg, n_tokens):
     import oracle
     sub = {k: (v[:, :n_tokens].clone() if isinstance(v, torch.Tensor) and v.dim() == 2 else v) for k, v in batch.items()}
     h = hidden[:n_tokens].float().requires_grad_(True)
-    w = weight.float().requires_grad_(True)
+    w = weight.detach().requires_grad_(True)  # fp32 copy made once by the caller (model weights, not per-step work)
     loss, stats = oracle.oracle_rl_step(h, w, sub, 0, 1, cfg)
     loss.backward()
-    return float(loss)
+    return float(loss.detach())
 
 
 def time_cpu_reference(hidden_cpu, weight_cpu, batch, ocfg, n_tokens, steps, warmup):
     import torch
     torch.set_num_threads(os.cpu_count() or 1)
+    weight_cpu = weight_cpu.float()
     for _ in range(warmup):
         reference_step_cpu(hidden_cpu, weight_cpu, batch, ocfg, n_tokens)
     t0 = time.perf_counter()
@@ -169,3 +170,259 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw), "reasons": sorted(reasons),
                 "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# the two arms
+# ------------------------------------------------------------------------------------------------
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"burst": d["bf16_tflops"], "sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "hbm": d["hbm_gbs"],
+                "source": "measured"}
+    return {"burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0, "source": "fallback"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port) on the host cores."""
+    import torch
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    import oracle
+    H, V, T, attempts, kl, clamp, B, desc = CONFIGS[args.config]
+    n_tok = args.cpu_sample_tokens or max(64, min(512, (1 << 31) // (V * 4 * 6)))
+    batch, _ = make_cpu_batch(T, V, attempts, seed=1236)
+    g = torch.Generator().manual_seed(1236)
+    hidden = torch.randn(n_tok, H, generator=g).bfloat16()
+    weight = (torch.randn(V, H, generator=g) * 0.02).bfloat16()
+    ocfg = oracle.OracleRLConfig(policy_loss="ppo", batch_size=B, kl_coef=kl, final_kl_coef=kl, clamp_log_ratio_ref_new_value=clamp)
+    tps, dt, threads = time_cpu_reference(hidden, weight, batch, ocfg, n_tok, args.steps, args.warmup)
+    sample = f"first {n_tok} tokens of the {args.config} packed row per step (fp32 math on bf16 values, fwd + autograd bwd)"
+    line = {
+        "impl": "reference", "metric": "grpo_logprob_loss_fwd_bwd_tokens_per_sec", "value": tps, "unit": "tokens/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "H": H, "V": V, "T": T, "tokens_per_step_sample": n_tok},
+        "cpu_baseline": {"value": tps, "unit": "tokens/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": tps, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+class DeviceWorkload:
+    """Everything one rank needs resident in HBM for the timed region (and pinned host copies for e2e)."""
+
+    def __init__(self, args, dev, rank, world):
+        import torch
+        from pipelinerl_swe_b200 import RLConfig, ops
+        from pipelinerl_swe_b200 import rl as prl
+        from pipelinerl_swe_b200.vocab_parallel import shard_range
+        self.torch, self.ops, self.prl = torch, ops, prl
+        H, V, T, attempts, kl, clamp, B, desc = CONFIGS[args.config]
+        self.H, self.V, self.T, self.desc = H, V, T, desc
+        self.vocab_parallel = args.parallelism == "vocab" and world > 1
+        seed = 1236 + (0 if self.vocab_parallel else rank)
+        self.rlcfg = RLConfig(policy_loss="ppo", batch_size=B, kl_coef=kl, final_kl_coef=kl, clamp_log_ratio_ref_new_value=clamp,
+                              epsilon=0.2, temperature=1.0)
+        self.cfg = prl.make_loss_cfg(self.rlcfg, 0, 1, True, False)
+        g = torch.Generator(device=dev).manual_seed(seed)
+        self.n_batches = 2
+        self.hidden = [torch.randn(T, H, device=dev, generator=g).bfloat16() for _ in range(self.n_batches)]
+        gw = torch.Generator(device=dev).manual_seed(99)  # same weights on every rank
+        wfull_rows = V
+        self.v_offset = 0
+        if self.vocab_parallel:
+            b, e = shard_range(V, world, rank)
+            self.v_offset, wfull_rows = b, e - b
+            full = (torch.randn(V, H, device=dev, generator=gw) * 0.02).bfloat16()
+            self.weight = full[b:e].contiguous()
+            del full
+        else:
+            self.weight = (torch.randn(V, H, device=dev, generator=gw) * 0.02).bfloat16()
+        self.Vloc = wfull_rows
+        self.grad_weight = torch.zeros(self.Vloc, H, dtype=torch.float32, device=dev)
+        self.cpu_batches, self.batches, self.targets = [], [], []
+        for i in range(self.n_batches):
+            cb, lens = make_cpu_batch(T, V, attempts, seed=seed * 10 + i)
+            db = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in cb.items()}
+            tgt = db["input_ids"][0, 1:].contiguous()
+            # old/ref logprobs near the current policy (SURVEY 8d): needs the policy's logprobs once
+            stats = self.fwd_stats(self.hidden[i][:-1], tgt)
+            lp, ent, lse = ops.lmhead_finalize(stats)
+            m = (db["labels"][0, 1:] != -100).float()
+            gn = torch.Generator(device=dev).manual_seed(seed * 10 + i)
+            db["old_logprobs"][0, 1:] = (lp + 0.05 * torch.randn(T - 1, device=dev, generator=gn)) * m
+            db["ref_logprobs"][0, 1:] = (lp + 0.10 * torch.randn(T - 1, device=dev, generator=gn)) * m
+            for k in ("old_logprobs", "ref_logprobs"):
+                cb[k] = db[k].cpu()
+            self.cpu_batches.append(cb); self.batches.append(db); self.targets.append(tgt)
+        self.hidden_m = [h[:-1] for h in self.hidden]  # rows that have a next token (contiguous view)
+        torch.cuda.synchronize()
+
+    def fwd_stats(self, h, tgt):
+        stats = self.ops.lmhead_fwd_stats(h, self.weight, tgt, 1.0, self.v_offset)
+        if self.vocab_parallel:
+            from pipelinerl_swe_b200.vocab_parallel import exchange_stats
+            stats = exchange_stats(stats)
+        return stats
+
+    def step(self, i: int):
+        """One device-resident fwd+bwd micro-batch; returns the device metrics vector."""
+        ops, torch = self.ops, self.torch
+        k = i % self.n_batches
+        h, tgt, b = self.hidden_m[k], self.targets[k], self.batches[k]
+        lp, ent, lse = ops.lmhead_finalize(self.fwd_stats(h, tgt))
+        loss, metrics, coef_lp, coef_ent, _ = ops.token_loss(lp[None], ent[None], b, self.cfg)
+        gh, _ = ops.lmhead_bwd(h, self.weight, tgt, lse, ent, coef_lp[0], coef_ent[0], 1.0, self.v_offset,
+                               grad_weight_out=self.grad_weight, accumulate=True)
+        if self.vocab_parallel:
+            from pipelinerl_swe_b200.vocab_parallel import reduce_grad_hidden
+            reduce_grad_hidden(gh)
+        return metrics
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from pipelinerl_swe_b200 import _abi
+    from pipelinerl_swe_b200.host_step import HostRLStep
+
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- pipelinerl_swe_b200 has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if args.mode != "auto":
+        _abi.set_tunable("bwd_mode", {"recompute": 0, "fused": 1}[args.mode])
+
+    wl = DeviceWorkload(args, dev, rank, world)
+    H, V, T = wl.H, wl.V, wl.T
+    K, W = args.steps, max(args.warmup, 3)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- device-resident value ----------------
+    for i in range(W):
+        wl.step(i)
+    barrier()
+    _abi.profile_enable(16 * K + 64)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        barrier()
+        e0.record()
+        for i in range(K):
+            metrics = wl.step(i)
+        e1.record()
+        barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    prof = _abi.profile_read(16 * K + 64)
+    _abi.profile_enable(0)
+    m = metrics.tolist()
+    assert m[_abi.M_FLAGS] == 0 and m[_abi.M_N_MASKED] > 0, "bench workload produced non-finite values"
+    ms_step = ms_total / K
+    tokens_per_step = T * (1 if wl.vocab_parallel else world)
+    value = tokens_per_step * K / (ms_total * 1e-3)
+
+    per_tag: dict[str, float] = {}
+    for tag, ms in prof:
+        per_tag[tag] = per_tag.get(tag, 0.0) + ms / K
+    gemm_tags = ("fwd_gemm_stats", "bwd_recompute_dlogits", "bwd_dH_gemm", "bwd_dW_gemm", "fused_logits_gemm")
+    gemm_ms = sum(per_tag.get(t, 0.0) for t in gemm_tags)
+    n_gemms = sum(1 for t in gemm_tags if t in per_tag)
+    peaks = load_peaks()
+    algo_flops = 6.0 * (T - 1) * H * wl.Vloc
+    achieved = algo_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    executed = 2.0 * (T - 1) * H * wl.Vloc * n_gemms / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    roofline = {
+        "bound": "tensor", "achieved": achieved, "peak": peaks["sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["sustained"],
+        "traffic": None, "peak_kind": f"bf16_tflops_sustained of {peaks['source']} (kernels timed inside a long step)",
+        "frac_of_burst_peak": achieved / peaks["burst"], "executed_tflops": executed, "gemm_ms_per_step": gemm_ms,
+        "share_of_step": gemm_ms / ms_step if world == 1 else None,
+        "kernels_ms_per_step": {k: round(v, 4) for k, v in sorted(per_tag.items())},
+        "note": "achieved = algorithmic 6*T*H*V FLOP per step / summed CUDA-event time of the lm_head GEMM launches of a step",
+    }
+    launches_per_step = len(prof) / K if K else 0
+
+    # ---------------- end to end through the host-buffer C entry point ----------------
+    e2e = None
+    if not args.no_e2e and not wl.vocab_parallel:
+        hs = [HostRLStep(T, H, V, wl.weight, wl.rlcfg, 0, 1, grad_weight_dtype=torch.float32) for _ in range(2)]
+        for k, s in enumerate(hs):
+            s.load_batch(wl.cpu_batches[k % wl.n_batches], wl.hidden[k % wl.n_batches].cpu())
+        for i in range(W):
+            hs[i % 2].run(accumulate=True)
+            torch.cuda.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        e0.record()
+        for i in range(K):
+            mh = hs[i % 2].run(accumulate=True)
+            torch.cuda.current_stream().synchronize()  # the trainer reads the step's metrics on the host every step
+            _ = float(mh[0])
+        e1.record()
+        barrier()
+        ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+        e2e = {"value": T * world * K / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hs[0].h2d_bytes,
+               "d2h_bytes_per_step": hs[0].d2h_bytes, "ms_per_step": ms_e2e / K,
+               "api": "b200grpo_rl_step_host (pinned host hidden + batch fields in, f64 metrics out; weight/grad stay on device)"}
+        del hs
+        torch.cuda.empty_cache()
+
+    # ---------------- CPU baseline (rank 0, N=1 only) ----------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        import oracle
+        n_tok = args.cpu_sample_tokens or 256
+        ocfg = oracle.OracleRLConfig(**wl.rlcfg.model_dump())
+        tps, dt, threads = time_cpu_reference(wl.hidden[0][:n_tok].cpu(), wl.weight.cpu(), wl.cpu_batches[0], ocfg, n_tok, 2, 1)
+        cpu = {"value": tps, "unit": "tokens/s", "cores": threads, "kind": "port",
+               "sample": f"first {n_tok} tokens of the same packed row, 1 warm-up + 2 timed fwd+bwd calls ({dt:.2f} s each), fp32 torch math on the bf16 values"}
+
+    if rank == 0:
+        line = {
+            "metric": "grpo_logprob_loss_fwd_bwd_tokens_per_sec", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if wl.vocab_parallel else "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": wl.desc, "H": H, "V": V, "T": T, "parallelism": ("vocab" if wl.vocab_parallel else "dp") + str(world),
+                       "grad_weight": "f32 accumulated across steps", "l2": "inputs exceed L2 (lm_head weight %.2f GB)" % (wl.weight.numel() * 2 / 1e9),
+                       "bwd_mode": args.mode, "tokens_per_gpu_per_sec": value / world if not wl.vocab_parallel else value},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(round(launches_per_step * K)),
+            "gpu_launches_per_step": launches_per_step, "clocks": clocks.summary(),
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -199,7 +199,9 @@ int b200grpo_bucket_unpack(const void* bucket_bf16, void* const* dst_ptrs_host,
  * over a packed row whose inputs live in PINNED HOST memory.  Copies inputs to the device
  * workspace, runs K1 -> finalize -> K3 -> K2 and copies metrics (f64[B200GRPO_M_COUNT])
  * back, all on `stream`.  weight / grad_weight stay device resident (model state).
- * Same math as calling the entry points above one by one.
+ * grad_hidden is always computed (the trunk's backward consumes it on the device, at
+ * b200grpo_rl_step_host_grad_hidden()); it is copied to the host only when
+ * grad_hidden_host_bf16 is given.  Same math as calling the entry points above one by one.
  * ------------------------------------------------------------------------------------- */
 typedef struct b200grpo_host_batch {
   const void* hidden_bf16;       /* [L, H]  pinned host */
@@ -216,6 +218,8 @@ typedef struct b200grpo_host_batch {
 } b200grpo_host_batch;
 
 size_t b200grpo_rl_step_host_workspace(int L, int H, int V);
+/* device address of grad_hidden bf16 [L,H] inside `workspace` (row L-1 is zero) */
+void* b200grpo_rl_step_host_grad_hidden(void* workspace, int L, int H, int V);
 int b200grpo_rl_step_host(const b200grpo_host_batch* batch_host, int L, int H, int V,
                           const void* weight, int64_t ldw, float temperature,
                           const b200grpo_loss_cfg* cfg_host, void* grad_hidden_host_bf16,

@@ -44,8 +44,8 @@ int check_device_sm100() {
   return 0;
 }
 
-// fwd_splits: 0 = auto; two_cta: 1 = cta_group::2 pairs; gemm_stages: 0 = auto; watchdog_ms
-static int g_tunables[TUNE_COUNT] = {0, 0, 0, 4000};
+// fwd_splits: 0 = auto; two_cta: 1 = cta_group::2 pairs (default); gemm_stages: 0 = auto; watchdog_ms
+static int g_tunables[TUNE_COUNT] = {0, 1, 0, 4000};
 int get_tunable(int id) { return g_tunables[id]; }
 
 // ---- profiling ring (diagnostic; single-threaded use) -------------------------------------

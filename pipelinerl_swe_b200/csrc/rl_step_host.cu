@@ -34,6 +34,10 @@ Layout make_layout(int L, int H, int V) {
 
 extern "C" size_t b200grpo_rl_step_host_workspace(int L, int H, int V) { return make_layout(L, H, V).total; }
 
+extern "C" void* b200grpo_rl_step_host_grad_hidden(void* workspace, int L, int H, int V) {
+  return workspace ? (char*)workspace + make_layout(L, H, V).ghid : nullptr;
+}
+
 extern "C" int b200grpo_rl_step_host(const b200grpo_host_batch* b, int L, int H, int V, const void* weight, int64_t ldw,
                                      float temperature, const b200grpo_loss_cfg* cfg, void* grad_hidden_host_bf16,
                                      void* grad_weight, int grad_weight_is_f32, int accumulate, double* metrics_host,
@@ -70,13 +74,12 @@ extern "C" int b200grpo_rl_step_host(const b200grpo_host_batch* b, int L, int H,
   if (grad_weight || grad_hidden_host_bf16) {
     e = b200grpo_lmhead_bwd(w + o.hidden, H, weight, ldw, targets, (const float*)(w + o.lse), (const float*)(w + o.entropy),
                             (const float*)(w + o.coef_lp), (const float*)(w + o.coef_ent), nullptr, M, H, V, 0,
-                            1.0f / temperature, grad_hidden_host_bf16 ? (void*)(w + o.ghid) : nullptr, H, grad_weight, H,
+                            1.0f / temperature, (void*)(w + o.ghid), H, grad_weight, H,
                             grad_weight_is_f32, accumulate, w + o.ws_bwd, o.n_bwd, stream);
     if (e) return e;
-    if (grad_hidden_host_bf16) {
-      B200_CUDA_OK(cudaMemsetAsync(w + o.ghid + (size_t)M * H * 2, 0, (size_t)H * 2, st));  // last position has no target
+    B200_CUDA_OK(cudaMemsetAsync(w + o.ghid + (size_t)M * H * 2, 0, (size_t)H * 2, st));  // last position has no target
+    if (grad_hidden_host_bf16)
       B200_CUDA_OK(cudaMemcpyAsync(grad_hidden_host_bf16, w + o.ghid, (size_t)L * H * 2, cudaMemcpyDeviceToHost, st));
-    }
   }
   B200_CUDA_OK(cudaMemcpyAsync(metrics_host, w + o.metrics, B200GRPO_M_COUNT * 8, cudaMemcpyDeviceToHost, st));
   return B200GRPO_OK;
