@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200GRPO_ABI_VERSION 1
+#define B200GRPO_ABI_VERSION 2
 
 enum {
   B200GRPO_OK = 0,
@@ -51,11 +51,18 @@ int b200grpo_abi_version(void);
  *   v_offset              global id of weight row 0 (0 when the vocab is not sharded)
  *   stats   f32  [M,4]    out: (max z, sum exp(z-max), sum exp(z-max)*z, z[target] or 0)
  *                         with z = logit / temperature, over this rank's vocab rows
+ *   saved   nullable, b200grpo_lmhead_saved_bytes(), 256-byte aligned.  When given, the
+ *           epilogue also keeps the bf16 logits of this micro-batch (stored relative to
+ *           their 256-column tile maximum, so the rounding error vanishes where softmax
+ *           mass is) for a recompute-free backward: the [M x Vloc] scratch lives only
+ *           between this call and the matching b200grpo_lmhead_bwd, which consumes it.
+ *           NULL: nothing of size [M x Vloc] is written by the forward.
  * ------------------------------------------------------------------------------------- */
 size_t b200grpo_lmhead_fwd_workspace(int M, int H, int Vloc);
+size_t b200grpo_lmhead_saved_bytes(int M, int H, int Vloc);
 int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw,
                         const int64_t* targets, int M, int H, int Vloc, int64_t v_offset,
-                        float inv_temperature, float* stats, void* workspace,
+                        float inv_temperature, float* stats, void* saved, void* workspace,
                         size_t workspace_bytes, void* stream);
 
 /* Combine per-rank stats (all-gathered, [R, M, 4]) into per-token results.
@@ -139,18 +146,22 @@ int b200grpo_segment_bounds(const int64_t* position_ids, int T, int32_t* bounds,
  * K2  lm_head backward.  Replaces autograd through rl/__init__.py:197-208:
  *   dlogit[t,j] = (s/temperature) * ( coef_lp[t]*(1[j==target_t] - p[t,j])
  *                                   - coef_ent[t]*p[t,j]*(logp[t,j] + entropy[t]) )
- * recomputed tile by tile from hidden/weight and the saved lse (logits are never stored),
- * written as bf16 to a workspace chunk, then dH = dlogits . W and dW = dlogits^T . hidden
- * as tcgen05 GEMMs.  s = *grad_scale (device scalar, nullable = 1).
+ * written as bf16 scratch, then dH = dlogits . W and dW = dlogits^T . hidden as tcgen05
+ * GEMMs.  Two ways to get the logits back:
+ *   saved == NULL : recomputed tile by tile from hidden/weight and lse (a third GEMM; the
+ *                   forward stored nothing of size [M x Vloc]);
+ *   saved != NULL : the buffer the forward filled; turned into dlogits IN PLACE by one
+ *                   HBM-bound pass (4 B/element) -- the buffer is consumed by this call.
+ * s = *grad_scale (device scalar, nullable = 1).
  *   grad_hidden bf16 [M,H] (ldgh)   -- partial sum over this rank's vocab rows
  *   grad_weight bf16 or f32 [Vloc,H] (ldgw); accumulate != 0 adds into it (f32 only)
  * ------------------------------------------------------------------------------------- */
-size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc);
+size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc, int with_saved);
 int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw,
                         const int64_t* targets, const float* lse, const float* entropy,
                         const float* coef_lp, const float* coef_ent, const float* grad_scale,
                         int M, int H, int Vloc, int64_t v_offset, float inv_temperature,
-                        void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw,
+                        void* saved, void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw,
                         int grad_weight_is_f32, int accumulate, void* workspace,
                         size_t workspace_bytes, void* stream);
 
@@ -203,6 +214,7 @@ int b200grpo_bucket_unpack(const void* bucket_bf16, void* const* dst_ptrs_host,
  * b200grpo_rl_step_host_grad_hidden()); it is copied to the host only when
  * grad_hidden_host_bf16 is given.  Same math as calling the entry points above one by one.
  * ------------------------------------------------------------------------------------- */
+/* save_logits != 0: recompute-free backward (forward keeps bf16 logits in the workspace). */
 typedef struct b200grpo_host_batch {
   const void* hidden_bf16;       /* [L, H]  pinned host */
   const int64_t* input_ids;      /* [L] */
@@ -233,13 +245,16 @@ int b200grpo_rl_step_host(const b200grpo_host_batch* batch_host, int L, int H, i
  *   0: operand is [rows = M or N, cols = K] (K contiguous)
  *   1: operand is [rows = K, cols = M or N] (M/N contiguous)
  * C is f32 (c_is_f32) or bf16, row-major [M, ldc]; accumulate adds into f32 C.
+ * group_m: row blocks per raster group (0 = all); k_splits > 1 splits K into f32 partial slabs
+ * (workspace >= k_splits*M*N*4 bytes, N % 4 == 0) reduced by a second kernel.
  * ------------------------------------------------------------------------------------- */
 int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb,
                        int b_mn_major, void* C, int64_t ldc, int c_is_f32, int accumulate,
-                       int M, int N, int K, void* stream);
+                       int M, int N, int K, int group_m, int k_splits, void* workspace,
+                       size_t workspace_bytes, void* stream);
 
 /* Tunables (for experiments from the test/bench harness; defaults are the shipped ones).
- * name in {"fwd_splits","two_cta","gemm_stages","watchdog_ms"}; returns previous value. */
+ * name in {"two_cta","dh_ksplit","dh_group_m","dw_group_m","save_logits",...}; returns the previous value. */
 int b200grpo_set_tunable(const char* name, int value);
 
 /* Per-launch device timing (diagnostic, single-threaded): while enabled, every kernel group the

@@ -53,13 +53,14 @@ SIGNATURES = {
     "b200grpo_abi_version": (_i, []),
     "b200grpo_set_tunable": (_i, [C.c_char_p, _i]),
     "b200grpo_lmhead_fwd_workspace": (_sz, [_i, _i, _i]),
-    "b200grpo_lmhead_fwd": (_i, [_p, _i64, _p, _i64, _p, _i, _i, _i, _i64, _f, _p, _p, _sz, _p]),
+    "b200grpo_lmhead_saved_bytes": (_sz, [_i, _i, _i]),
+    "b200grpo_lmhead_fwd": (_i, [_p, _i64, _p, _i64, _p, _i, _i, _i, _i64, _f, _p, _p, _p, _sz, _p]),
     "b200grpo_lmhead_finalize": (_i, [_p, _i, _i, _p, _p, _p, _p]),
     "b200grpo_token_loss_workspace": (_sz, [_i, _i]),
     "b200grpo_token_loss": (_i, [_p] * 12 + [_i, _i, C.POINTER(LossCfg)] + [_p] * 6 + [_sz, _p]),
     "b200grpo_segment_bounds": (_i, [_p, _i, _p, _p, _p, _sz, _p]),
-    "b200grpo_lmhead_bwd_workspace": (_sz, [_i, _i, _i]),
-    "b200grpo_lmhead_bwd": (_i, [_p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i64, _f, _p, _i64, _p, _i64, _i, _i,
+    "b200grpo_lmhead_bwd_workspace": (_sz, [_i, _i, _i, _i]),
+    "b200grpo_lmhead_bwd": (_i, [_p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i64, _f, _p, _p, _i64, _p, _i64, _i, _i,
                                  _p, _sz, _p]),
     "b200grpo_group_advantage_workspace": (_sz, [_i, _i]),
     "b200grpo_group_advantage": (_i, [_p] * 6 + [_i, _i, _i] + [_p] * 5 + [_sz, _p]),
@@ -73,7 +74,7 @@ SIGNATURES = {
                                    _sz, _p]),
     "b200grpo_profile_enable": (_i, [_i]),
     "b200grpo_profile_read": (_i, [_p, _p, _i]),
-    "b200grpo_gemm_bf16": (_i, [_p, _i64, _i, _p, _i64, _i, _p, _i64, _i, _i, _i, _i, _i, _p]),
+    "b200grpo_gemm_bf16": (_i, [_p, _i64, _i, _p, _i64, _i, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),
 }
 
 _lib = None

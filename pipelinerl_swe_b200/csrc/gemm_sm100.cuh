@@ -10,11 +10,18 @@
 // Pipelines: smem full/empty mbarriers (TMA <-> MMA) and TMEM full/empty mbarriers
 // (MMA <-> epilogue), so the epilogue of tile i overlaps the MMAs of tile i+1.
 //
-// Work decomposition: item = (m_block, split); an item sweeps a contiguous range of
-// n-blocks for one row block, which lets the forward epilogue keep its running
-// (max, sum-exp, sum e*z) per row in registers across the sweep.  Items are dealt
-// round-robin with m_block fastest, so CTAs running together share the same B (weight)
-// tiles through L2 while A (hidden) stays L2 resident.
+// Work decomposition: item = (output tile, k-split), dealt round-robin to the resident
+// clusters.  Tiles are rasterised in groups of `group_m` row blocks (row block fastest inside
+// a group) so that the clusters running together share operand tiles through L2:
+//   lm_head fwd / recompute : group_m = all row blocks -> the 74 live tiles read the same 2-3
+//                             weight tiles while hidden stays L2 resident;
+//   dW (tokens are K)       : group_m small -> one dlogits column slab is shared by the 14
+//                             n-tiles of its row block while hidden^T stays L2 resident;
+//   dH (vocab is K)         : square-ish patches (both operands stream, nothing is resident).
+// Every epilogue is stateless per tile (the forward writes per-tile softmax partials that a
+// merge kernel combines), which is what makes the tile order free.  k-splits (EPI_STORE only)
+// write f32 partial slabs reduced by a second kernel: they remove wave quantisation when the
+// tile count is a poor multiple of the cluster count (dH: 448 tiles on 74 clusters).
 #pragma once
 #include "common.cuh"
 #include "sm100_ptx.cuh"
@@ -34,16 +41,19 @@ constexpr float LN2_F = 0.6931471805599453f;
 
 struct GemmParams {
   int M, N, K;
-  int m_blocks, n_blocks, n_splits;
+  int m_blocks, n_blocks, k_splits, group_m, kb_total;
   // EPI_STORE
   void* C;
   long long ldc;
   int c_is_f32, accumulate;
+  float* slab;              // [k_splits][M][N] f32 partial sums when k_splits > 1
   // EPI_FWD_STATS / EPI_BWD_DLOGITS
   const long long* targets;
   long long v_offset;
   float inv_temp;
-  float* part;              // [n_splits][M][4]  (max z, sum e, sum e*z, z_target|0)
+  float* part;              // [n_blocks][M][4]  per-tile (max z, sum e, sum e*z, z_target|0)
+  __nv_bfloat16* zsave;     // optional [M][ldz]: (z - tile max) saved for a recompute-free backward
+  long long ldz;
   const float *lse, *entropy, *coef_lp, *coef_ent, *grad_scale;
   __nv_bfloat16* dlogits;   // [M][ldd]
   long long ldd;
@@ -59,11 +69,22 @@ struct GemmSmem {
   static constexpr int TOTAL = BAR_OFFSET + (2 * kStages + 4) * 8 + 16 + 1024;  // + alignment slack
 };
 
-__device__ __forceinline__ void item_range(const GemmParams& p, int item, int& m_blk, int& nb_begin, int& nb_end) {
-  m_blk = item % p.m_blocks;
-  const int sp = item / p.m_blocks;
-  nb_begin = (int)((long long)sp * p.n_blocks / p.n_splits);
-  nb_end = (int)((long long)(sp + 1) * p.n_blocks / p.n_splits);
+struct Item { int m_blk, nb, ks, kb0, kb1; };
+
+__device__ __forceinline__ Item decode_item(const GemmParams& p, int item) {
+  Item it;
+  const int tiles = p.m_blocks * p.n_blocks;
+  it.ks = item / tiles;
+  const int t = item - it.ks * tiles;
+  const int per_group = p.group_m * p.n_blocks;
+  const int g = t / per_group, w = t - g * per_group;
+  const int m_first = g * p.group_m;
+  const int gm = min(p.group_m, p.m_blocks - m_first);
+  it.nb = w / gm;
+  it.m_blk = m_first + (w - it.nb * gm);
+  it.kb0 = (int)((long long)it.ks * p.kb_total / p.k_splits);
+  it.kb1 = (int)((long long)(it.ks + 1) * p.kb_total / p.k_splits);
+  return it;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -76,10 +97,8 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
-struct FwdRowState { float m_raw, s, u, tgt; int tcol; };
-
-__device__ __forceinline__ void fwd_chunk(FwdRowState& st, const uint32_t (&v)[32], int col0, int n_valid, float scale2) {
-  // n_valid = number of real vocab columns in this chunk (32 except at the vocab tail)
+// Forward epilogue, pass 1: max over the valid columns of one 32-column chunk.
+__device__ __forceinline__ float chunk_max(const uint32_t (&v)[32], int n_valid) {
   float cmax = -INFINITY;
   if (n_valid >= 32) {
 #pragma unroll
@@ -88,10 +107,16 @@ __device__ __forceinline__ void fwd_chunk(FwdRowState& st, const uint32_t (&v)[3
 #pragma unroll
     for (int j = 0; j < 32; ++j) if (j < n_valid) cmax = fmaxf(cmax, __uint_as_float(v[j]));
   }
-  if (cmax > st.m_raw) {
-    const float r = fast_exp2((st.m_raw - cmax) * scale2);
-    st.s *= r; st.u *= r; st.m_raw = cmax;
-  }
+  return cmax;
+}
+
+struct FwdRowState { float m_raw, s, u, tgt; int tcol; };
+
+// Forward epilogue, pass 2: with the tile max known, accumulate sum e and sum e*z, pick the
+// target logit, and (optionally) save y = (z - tile max)/T as bf16 for the backward.
+template <bool kSave>
+__device__ __forceinline__ void fwd_chunk(FwdRowState& st, const uint32_t (&v)[32], int col0, int n_valid, float scale2,
+                                          float inv_temp, __nv_bfloat16* zrow) {
   const float neg = -st.m_raw * scale2;
   float s = 0.f, u = 0.f;
   if (n_valid >= 32) {
@@ -114,6 +139,28 @@ __device__ __forceinline__ void fwd_chunk(FwdRowState& st, const uint32_t (&v)[3
   if (t >= 0 && t < 32) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) if (j == t) st.tgt = __uint_as_float(v[j]);
+  }
+  if constexpr (kSave) {
+    uint32_t packed[16];
+    const float negm = -st.m_raw * inv_temp;
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+      const __nv_bfloat162 b = __floats2bfloat162_rn(fmaf(__uint_as_float(v[j]), inv_temp, negm),
+                                                     fmaf(__uint_as_float(v[j + 1]), inv_temp, negm));
+      packed[j >> 1] = *reinterpret_cast<const uint32_t*>(&b);
+    }
+    if (n_valid >= 32) {
+      uint4* o = reinterpret_cast<uint4*>(zrow + col0);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) o[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < n_valid) {
+          const uint32_t w = packed[j >> 1];
+          reinterpret_cast<unsigned short*>(zrow + col0)[j] = (j & 1) ? (unsigned short)(w >> 16) : (unsigned short)(w & 0xffffu);
+        }
+    }
   }
 }
 
@@ -152,8 +199,19 @@ __device__ __forceinline__ void bwd_chunk(const BwdRowConst& rc, const uint32_t 
   }
 }
 
-__device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t (&v)[32], int row, int col0, int n_valid) {
-  if (p.c_is_f32) {
+__device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t (&v)[32], int row, int col0, int n_valid, int ks) {
+  if (p.k_splits > 1) {  // f32 partial of this k-split; reduced (and cast / accumulated) by splitk_reduce_kernel
+    float* o = p.slab + ((long long)ks * p.M + row) * p.N + col0;
+    if (n_valid >= 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+      float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        o4[q] = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) if (j < n_valid) o[j] = __uint_as_float(v[j]);
+    }
+  } else if (p.c_is_f32) {
     float* o = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + col0;
     if (n_valid >= 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
       float4* o4 = reinterpret_cast<float4*>(o);
@@ -194,7 +252,7 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t 
 // ---------------------------------------------------------------------------------------
 // The kernel
 // ---------------------------------------------------------------------------------------
-template <int kEpi, int kAMajor, int kBMajor, int kCtas, int BLOCK_N, int kStages>
+template <int kEpi, int kAMajor, int kBMajor, int kCtas, int BLOCK_N, int kStages, bool kSave = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, const GemmParams p) {
   using L = GemmSmem<BLOCK_N, kCtas, kStages>;
@@ -218,8 +276,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
   const uint32_t cta_rank = kCtas > 1 ? ptx::cluster_ctarank() : 0u;
   const bool leader = cta_rank == 0;
   const int cluster_id = blockIdx.x / kCtas, n_clusters = gridDim.x / kCtas;
-  const int n_items = p.m_blocks * p.n_splits;
-  const int num_kb = (p.K + GEMM_BLOCK_K - 1) / GEMM_BLOCK_K;
+  const int n_items = p.m_blocks * p.n_blocks * p.k_splits;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tm_a);
@@ -241,36 +298,33 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     // ===================== TMA producer =====================
     uint32_t stage = 0, phase = 0;
     for (int item = cluster_id; item < n_items; item += n_clusters) {
-      int m_blk, nb0, nb1;
-      item_range(p, item, m_blk, nb0, nb1);
-      const int m0 = (m_blk * kCtas + (int)cta_rank) * GEMM_BLOCK_M;
-      for (int nb = nb0; nb < nb1; ++nb) {
-        const int n0 = nb * BLOCK_N + (int)cta_rank * LOAD_N;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          ptx::mbar_wait(&empty_bar[stage], phase ^ 1, 1);
-          uint8_t* sa = smem + stage * L::STAGE_BYTES;
-          uint8_t* sb = sa + L::A_BYTES;
-          if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], L::STAGE_BYTES * kCtas);
-          else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
-          const int k0 = kb * GEMM_BLOCK_K;
-          auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
-            if constexpr (kCtas == 1) ptx::tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
-            else ptx::tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
-          };
-          if constexpr (kAMajor == MAJOR_K) {
-            load(sa, &tm_a, k0, m0);                                   // box {64 k, 128 rows}
-          } else {
+      const Item it = decode_item(p, item);
+      const int m0 = (it.m_blk * kCtas + (int)cta_rank) * GEMM_BLOCK_M;
+      const int n0 = it.nb * BLOCK_N + (int)cta_rank * LOAD_N;
+      for (int kb = it.kb0; kb < it.kb1; ++kb) {
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1, 1);
+        uint8_t* sa = smem + stage * L::STAGE_BYTES;
+        uint8_t* sb = sa + L::A_BYTES;
+        if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], L::STAGE_BYTES * kCtas);
+        else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
+        const int k0 = kb * GEMM_BLOCK_K;
+        auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
+          if constexpr (kCtas == 1) ptx::tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
+          else ptx::tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
+        };
+        if constexpr (kAMajor == MAJOR_K) {
+          load(sa, &tm_a, k0, m0);                                   // box {64 k, 128 rows}
+        } else {
 #pragma unroll
-            for (int a = 0; a < GEMM_BLOCK_M / 64; ++a) load(sa + a * 8192, &tm_a, m0 + a * 64, k0);  // box {64 m, 64 k}
-          }
-          if constexpr (kBMajor == MAJOR_K) {
-            load(sb, &tm_b, k0, n0);                                   // box {64 k, LOAD_N rows}
-          } else {
-#pragma unroll
-            for (int a = 0; a < LOAD_N / 64; ++a) load(sb + a * 8192, &tm_b, n0 + a * 64, k0);
-          }
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          for (int a = 0; a < GEMM_BLOCK_M / 64; ++a) load(sa + a * 8192, &tm_a, m0 + a * 64, k0);  // box {64 m, 64 k}
         }
+        if constexpr (kBMajor == MAJOR_K) {
+          load(sb, &tm_b, k0, n0);                                   // box {64 k, LOAD_N rows}
+        } else {
+#pragma unroll
+          for (int a = 0; a < LOAD_N / 64; ++a) load(sb + a * 8192, &tm_b, n0 + a * 64, k0);
+        }
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1 && lane == 0 && leader) {
@@ -280,26 +334,23 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     constexpr uint32_t A_KSTEP = (kAMajor == MAJOR_K ? GEMM_UMMA_K * 2 : GEMM_UMMA_K * 128) >> 4;
     constexpr uint32_t B_KSTEP = (kBMajor == MAJOR_K ? GEMM_UMMA_K * 2 : GEMM_UMMA_K * 128) >> 4;
     uint32_t stage = 0, phase = 0, tile_iter = 0;
-    for (int item = cluster_id; item < n_items; item += n_clusters) {
-      int m_blk, nb0, nb1;
-      item_range(p, item, m_blk, nb0, nb1);
-      for (int nb = nb0; nb < nb1; ++nb, ++tile_iter) {
-        const uint32_t as = tile_iter & 1, aphase = (tile_iter >> 1) & 1;
-        ptx::mbar_wait(&tmem_empty[as], aphase ^ 1, 2);
+    for (int item = cluster_id; item < n_items; item += n_clusters, ++tile_iter) {
+      const Item it = decode_item(p, item);
+      const uint32_t as = tile_iter & 1, aphase = (tile_iter >> 1) & 1;
+      ptx::mbar_wait(&tmem_empty[as], aphase ^ 1, 2);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+      for (int kb = it.kb0; kb < it.kb1; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase, 3);
         ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          ptx::mbar_wait(&full_bar[stage], phase, 3);
-          ptx::tc_fence_after();
-          const uint32_t sa = ptx::smem_u32(smem + stage * L::STAGE_BYTES), sb = sa + L::A_BYTES;
-          const uint64_t da = ptx::smem_desc_sw128(sa, A_LBO, 1024), db = ptx::smem_desc_sw128(sb, B_LBO, 1024);
+        const uint32_t sa = ptx::smem_u32(smem + stage * L::STAGE_BYTES), sb = sa + L::A_BYTES;
+        const uint64_t da = ptx::smem_desc_sw128(sa, A_LBO, 1024), db = ptx::smem_desc_sw128(sb, B_LBO, 1024);
 #pragma unroll
-          for (int k = 0; k < GEMM_BLOCK_K / GEMM_UMMA_K; ++k)
-            ptx::umma_bf16<kCtas>(d_tmem, da + (uint64_t)(k * A_KSTEP), db + (uint64_t)(k * B_KSTEP), idesc, (kb | k) != 0);
-          ptx::umma_commit<kCtas>(&empty_bar[stage]);              // frees the smem slot when the MMAs retire
-          if (kb == num_kb - 1) ptx::umma_commit<kCtas>(&tmem_full[as]);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
-        }
+        for (int k = 0; k < GEMM_BLOCK_K / GEMM_UMMA_K; ++k)
+          ptx::umma_bf16<kCtas>(d_tmem, da + (uint64_t)(k * A_KSTEP), db + (uint64_t)(k * B_KSTEP), idesc, (kb > it.kb0) || (k != 0));
+        ptx::umma_commit<kCtas>(&empty_bar[stage]);              // frees the smem slot when the MMAs retire
+        if (kb == it.kb1 - 1) ptx::umma_commit<kCtas>(&tmem_full[as]);
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
     }
     if (kCtas > 1 && tile_iter > 0) {  // drain: peer epilogue arrivals must land before teardown
@@ -314,17 +365,17 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     const float scale2 = p.inv_temp * LOG2E_F;
     uint32_t tile_iter = 0;
-    for (int item = cluster_id; item < n_items; item += n_clusters) {
-      int m_blk, nb0, nb1;
-      item_range(p, item, m_blk, nb0, nb1);
-      const int row = (m_blk * kCtas + (int)cta_rank) * GEMM_BLOCK_M + row_in_tile;
+    for (int item = cluster_id; item < n_items; item += n_clusters, ++tile_iter) {
+      const Item it = decode_item(p, item);
+      const int row = (it.m_blk * kCtas + (int)cta_rank) * GEMM_BLOCK_M + row_in_tile;
       const bool row_ok = row < p.M;
+      const int n0 = it.nb * BLOCK_N;
       FwdRowState fs;
       BwdRowConst bc;
       if constexpr (kEpi == EPI_FWD_STATS) {
         fs.m_raw = -INFINITY; fs.s = 0.f; fs.u = 0.f; fs.tgt = 0.f;
         const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
-        fs.tcol = (t >= 0 && t < p.N) ? (int)t : -1000000;
+        fs.tcol = (t >= n0 && t < min(p.N, n0 + BLOCK_N)) ? (int)t : -1000000;
       }
       if constexpr (kEpi == EPI_BWD_DLOGITS) {
         const float gs = (p.grad_scale ? *p.grad_scale : 1.0f) * p.inv_temp;
@@ -335,12 +386,11 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
         bc.tcol = (t >= 0 && t < p.N) ? (int)t : -1000000;
       }
-      for (int nb = nb0; nb < nb1; ++nb, ++tile_iter) {
-        const uint32_t as = tile_iter & 1, aphase = (tile_iter >> 1) & 1;
-        ptx::mbar_wait(&tmem_full[as], aphase, 6);
-        ptx::tc_fence_after();
-        const uint32_t t_addr = tmem_base + lane_addr + as * BLOCK_N;
-        const int n0 = nb * BLOCK_N;
+      const uint32_t as = tile_iter & 1, aphase = (tile_iter >> 1) & 1;
+      ptx::mbar_wait(&tmem_full[as], aphase, 6);
+      ptx::tc_fence_after();
+      const uint32_t t_addr = tmem_base + lane_addr + as * BLOCK_N;
+      if constexpr (kEpi == EPI_FWD_STATS) {   // pass 1: tile max per row
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N / 32; ++c) {
           const int col0 = n0 + c * 32;
@@ -349,19 +399,31 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
           __syncwarp();
           ptx::tmem_ld_32x32(t_addr + c * 32, v);
           ptx::tmem_ld_wait();
-          const int n_valid = min(32, p.N - col0);
-          if constexpr (kEpi == EPI_FWD_STATS) fwd_chunk(fs, v, col0, n_valid, scale2);
-          if constexpr (kEpi == EPI_BWD_DLOGITS) { if (row_ok) bwd_chunk(bc, v, col0, n_valid, scale2, p.dlogits + (long long)row * p.ldd); }
-          if constexpr (kEpi == EPI_STORE) { if (row_ok) store_chunk(p, v, row, col0, n_valid); }
+          fs.m_raw = fmaxf(fs.m_raw, chunk_max(v, min(32, p.N - col0)));
         }
-        ptx::tc_fence_before();
-        if (kCtas == 1) ptx::mbar_arrive(&tmem_empty[as]); else ptx::mbar_arrive_cluster(&tmem_empty[as], 0);
       }
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= p.N) break;                      // warp-uniform
+        uint32_t v[32];
+        __syncwarp();
+        ptx::tmem_ld_32x32(t_addr + c * 32, v);
+        ptx::tmem_ld_wait();
+        const int n_valid = min(32, p.N - col0);
+        if constexpr (kEpi == EPI_FWD_STATS) {
+          if (kSave && !row_ok) continue;
+          fwd_chunk<kSave>(fs, v, col0, n_valid, scale2, p.inv_temp, kSave ? p.zsave + (long long)row * p.ldz : nullptr);
+        }
+        if constexpr (kEpi == EPI_BWD_DLOGITS) { if (row_ok) bwd_chunk(bc, v, col0, n_valid, scale2, p.dlogits + (long long)row * p.ldd); }
+        if constexpr (kEpi == EPI_STORE) { if (row_ok) store_chunk(p, v, row, col0, n_valid, it.ks); }
+      }
+      ptx::tc_fence_before();
+      if (kCtas == 1) ptx::mbar_arrive(&tmem_empty[as]); else ptx::mbar_arrive_cluster(&tmem_empty[as], 0);
       if constexpr (kEpi == EPI_FWD_STATS) {
         if (row_ok) {
-          const int sp = item / p.m_blocks;
-          float4 o = make_float4(fs.m_raw * p.inv_temp, fs.s, fs.u * p.inv_temp, fs.tgt * p.inv_temp);
-          reinterpret_cast<float4*>(p.part)[(long long)sp * p.M + row] = o;
+          const float4 o = make_float4(fs.m_raw * p.inv_temp, fs.s, fs.u * p.inv_temp, fs.tgt * p.inv_temp);
+          reinterpret_cast<float4*>(p.part)[(long long)it.nb * p.M + row] = o;
         }
       }
     }

@@ -44,38 +44,40 @@ static int make_tmap(CUtensorMap* tm, const void* ptr, long long inner, long lon
   return 0;
 }
 
-// ---- work split: items = m_blocks x n_splits dealt round-robin to the resident clusters -----
-static int choose_splits(int m_blocks, int n_blocks, int n_clusters, int forced) {
-  if (forced > 0) return forced < n_blocks ? forced : n_blocks;
+// ---- tiling --------------------------------------------------------------------------------
+constexpr int BN = 256;
+constexpr int STAGES_1CTA = 4, STAGES_2CTA = 6;
+
+// k-splits for an EPI_STORE GEMM: smallest split count whose wave efficiency is within 1% of the
+// best reachable with <= 8 splits (each split costs an f32 slab round trip through HBM).
+static int choose_ksplits(int tiles, int clusters, int kb_total, int forced) {
+  if (forced > 0) return forced < kb_total ? forced : kb_total;
   int best = 1;
-  double best_eff = -1.0;
-  const int hi = n_blocks < 256 ? n_blocks : 256;
-  for (int s = 1; s <= hi; ++s) {
-    const long long items = (long long)m_blocks * s;
-    const long long waves = (items + n_clusters - 1) / n_clusters;
-    const int tiles_max = (n_blocks + s - 1) / s;
-    const double eff = (double)m_blocks * n_blocks / ((double)n_clusters * waves * tiles_max);
-    if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
+  double best_eff = 0.0;
+  for (int s = 1; s <= 8; ++s) {
+    if (s > 1 && kb_total / s < 64) break;
+    const long long items = (long long)tiles * s;
+    const long long waves = (items + clusters - 1) / clusters;
+    const double eff = (double)items / (double)(waves * clusters);
+    if (eff > best_eff + 0.01) { best_eff = eff; best = s; }
   }
   return best;
 }
 
-constexpr int BN = 256;
-constexpr int STAGES_1CTA = 4, STAGES_2CTA = 6;
-
-template <int kEpi, int kAMajor, int kBMajor, int kCtas>
+template <int kEpi, int kAMajor, int kBMajor, int kCtas, bool kSave>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
   constexpr int kStages = kCtas == 1 ? STAGES_1CTA : STAGES_2CTA;
   using L = GemmSmem<BN, kCtas, kStages>;
-  auto kern = gemm_sm100_kernel<kEpi, kAMajor, kBMajor, kCtas, BN, kStages>;
+  auto kern = gemm_sm100_kernel<kEpi, kAMajor, kBMajor, kCtas, BN, kStages, kSave>;
   static bool configured = false;
   if (!configured) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     configured = true;
   }
-  const int n_items = p.m_blocks * p.n_splits;
+  const long long n_items = (long long)p.m_blocks * p.n_blocks * p.k_splits;
+  B200_REQUIRE(n_items < (1ll << 30), "gemm: too many tiles");
   int clusters = sm_count() / kCtas;
-  if (clusters > n_items) clusters = n_items;
+  if (clusters > n_items) clusters = (int)n_items;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(clusters * kCtas);
   cfg.blockDim = dim3(GEMM_THREADS);
@@ -102,19 +104,25 @@ static int make_ab_maps(CUtensorMap* ta, CUtensorMap* tb, const void* A, long lo
   return e;
 }
 
-static void fill_tiling(GemmParams& p, int M, int N, int K, int ctas, int forced_splits) {
+static int clusters_for(int ctas) {
+  int c = sm_count() / ctas;
+  return c < 1 ? 1 : c;
+}
+
+// group_m <= 0: all row blocks in one group (row block fastest over the whole matrix)
+static void fill_tiling(GemmParams& p, int M, int N, int K, int ctas, int group_m, int k_splits) {
   p.M = M; p.N = N; p.K = K;
   p.m_blocks = ceil_div(M, GEMM_BLOCK_M * ctas);
   p.n_blocks = ceil_div(N, BN);
-  int clusters = sm_count() / ctas;
-  if (clusters < 1) clusters = 1;
-  p.n_splits = choose_splits(p.m_blocks, p.n_blocks, clusters, forced_splits);
+  p.kb_total = ceil_div(K, GEMM_BLOCK_K);
+  p.group_m = (group_m <= 0 || group_m > p.m_blocks) ? p.m_blocks : group_m;
+  p.k_splits = k_splits < 1 ? 1 : k_splits;
 }
 
-template <int kEpi>
+template <int kEpi, bool kSave = false>
 static int dispatch(int a_mn, int b_mn, int ctas, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
 #define B200_CASE(AM, BM, C) \
-  if (a_mn == AM && b_mn == BM && ctas == C) return launch_gemm<kEpi, AM, BM, C>(ta, tb, p, st);
+  if (a_mn == AM && b_mn == BM && ctas == C) return launch_gemm<kEpi, AM, BM, C, kSave>(ta, tb, p, st);
   if constexpr (kEpi == EPI_STORE) {
     B200_CASE(0, 0, 1) B200_CASE(0, 0, 2) B200_CASE(0, 1, 1) B200_CASE(0, 1, 2)
     B200_CASE(1, 0, 1) B200_CASE(1, 0, 2) B200_CASE(1, 1, 1) B200_CASE(1, 1, 2)
@@ -132,19 +140,42 @@ static int ctas_for(int M) {
 }
 
 // ---- small kernels around the GEMMs -----------------------------------------------------
-// merge per-split partials [S][M][4] -> stats [M][4]  (online-softmax merge; order fixed)
-__global__ void __launch_bounds__(256) fwd_merge_kernel(const float4* __restrict__ part, int S, int M, float4* __restrict__ stats) {
-  const int row = blockIdx.x * blockDim.x + threadIdx.x;
-  if (row >= M) return;
-  float m = -INFINITY;
-  for (int s = 0; s < S; ++s) m = fmaxf(m, part[(long long)s * M + row].x);
-  float sum = 0.f, dot = 0.f, tgt = 0.f;
-  for (int s = 0; s < S; ++s) {
-    const float4 q = part[(long long)s * M + row];
-    const float w = __expf(q.x - m);
-    sum = fmaf(q.y, w, sum); dot = fmaf(q.z, w, dot); tgt += q.w;
+// merge the per-tile partials [n_blocks][M][4] -> stats [M][4] (online-softmax merge, fixed order).
+// Block = 32 rows x 8 tile slices: a warp reads 512 contiguous bytes per tile, 4 loads in flight.
+constexpr int MG_SLICES = 8;
+__device__ __forceinline__ void merge_one(float& m, float& sum, float& dot, float& tgt, const float4 q) {
+  if (q.x > m) { const float r = __expf(m - q.x); sum *= r; dot *= r; m = q.x; }
+  const float w = __expf(q.x - m);
+  sum = fmaf(q.y, w, sum); dot = fmaf(q.z, w, dot); tgt += q.w;
+}
+__global__ void __launch_bounds__(32 * MG_SLICES) fwd_merge_kernel(const float4* __restrict__ part, int S, int M, float4* __restrict__ stats) {
+  const int rx = threadIdx.x & 31, sy = threadIdx.x >> 5;
+  const int row = blockIdx.x * 32 + rx;
+  float m = -INFINITY, sum = 0.f, dot = 0.f, tgt = 0.f;
+  if (row < M) {
+    int s = sy;
+    for (; s + 3 * MG_SLICES < S; s += 4 * MG_SLICES) {
+      float4 q[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) q[j] = __ldg(&part[(long long)(s + j * MG_SLICES) * M + row]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) merge_one(m, sum, dot, tgt, q[j]);
+    }
+    for (; s < S; s += MG_SLICES) merge_one(m, sum, dot, tgt, __ldg(&part[(long long)s * M + row]));
   }
-  stats[row] = make_float4(m, sum, dot, tgt);
+  __shared__ float4 sh[MG_SLICES][32];
+  sh[sy][rx] = make_float4(m, sum, dot, tgt);
+  __syncthreads();
+  if (sy == 0 && row < M) {
+    float M2 = -INFINITY, S2 = 0.f, D2 = 0.f, T2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < MG_SLICES; ++j) {
+      const float4 q = sh[j][rx];
+      if (q.x == -INFINITY) continue;  // slice saw no tile
+      merge_one(M2, S2, D2, T2, q);
+    }
+    stats[row] = make_float4(M2, S2, D2, T2);
+  }
 }
 
 // merge per-rank stats [R][M][4] and finish: lse, logprob, entropy  (rl/__init__.py:202-208)
@@ -166,38 +197,148 @@ __global__ void __launch_bounds__(256) finalize_kernel(const float4* __restrict_
   if (lse_out) lse_out[row] = lse;
 }
 
+// Saved forward logits -> dlogits, in place (the recompute-free backward).  z[t,j] holds
+// y = (logit - tile max)/T as bf16; the tile max lives in part[nb][t].x.  HBM-bound: 4 B/element
+// (bf16 in + bf16 out), 16-byte vectors, one block = 2048 consecutive columns of one row.
+constexpr int DL_THREADS = 256;
+__global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
+    __nv_bfloat16* __restrict__ z, long long ldz, const float4* __restrict__ part, int M, int N, const long long* __restrict__ targets,
+    long long v_offset, const float* __restrict__ lse, const float* __restrict__ entropy, const float* __restrict__ coef_lp,
+    const float* __restrict__ coef_ent, const float* __restrict__ grad_scale, float inv_temp) {
+  const int col = (blockIdx.x * DL_THREADS + threadIdx.x) * 8;
+  if (col >= N) return;
+  const int nb = col / BN;
+  const float gs = (grad_scale ? *grad_scale : 1.0f) * inv_temp;
+  for (int row = blockIdx.y; row < M; row += gridDim.y) {
+    const float lse_r = lse[row], a = coef_lp[row] * gs, e = coef_ent[row] * gs, ent = entropy[row];
+    const long long tl = targets[row] - v_offset;
+    const int t = (tl >= col && tl < col + 8) ? (int)(tl - col) : -1;
+    const float shift2 = (__ldg(&part[(long long)nb * M + row]).x - lse_r) * LOG2E_F;  // (tile max - lse) * log2 e
+    __nv_bfloat16* zr = z + (long long)row * ldz + col;
+    uint4 raw = *reinterpret_cast<const uint4*>(zr);
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 y = __bfloat1622float2(h[q]);
+      float d[2];
+#pragma unroll
+      for (int w = 0; w < 2; ++w) {
+        const float y2 = fmaf(w ? y.y : y.x, LOG2E_F, shift2);   // log2 p
+        const float pr = fast_exp2(y2);
+        float g = -pr * fmaf(e, fmaf(y2, LN2_F, ent), a);        // -p * (a + e*(logp + H))
+        if (2 * q + w == t) g += a;
+        d[w] = g;
+      }
+      h[q] = __floats2bfloat162_rn(d[0], d[1]);
+    }
+    if (col + 8 <= N) {
+      *reinterpret_cast<uint4*>(zr) = raw;
+    } else {
+      const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(&raw);
+      for (int j = 0; j < N - col; ++j) zr[j] = src[j];
+    }
+  }
+}
+
+// sum the k-split slabs [S][M][N] (f32) into C (bf16 or f32, optionally accumulating)
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ slab, int S, int M, int N, void* C,
+                                                            long long ldc, int c_is_f32, int accumulate) {
+  const long long quads = (long long)M * (N / 4);
+  const long long plane = (long long)M * N;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < quads; i += (long long)gridDim.x * blockDim.x) {
+    const int row = (int)(i / (N / 4)), c4 = (int)(i - (long long)row * (N / 4)) * 4;
+    float4 acc = __ldg(reinterpret_cast<const float4*>(slab + (long long)row * N + c4));
+    for (int s = 1; s < S; ++s) {
+      const float4 x = __ldg(reinterpret_cast<const float4*>(slab + s * plane + (long long)row * N + c4));
+      acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+    }
+    if (c_is_f32) {
+      float* o = reinterpret_cast<float*>(C) + (long long)row * ldc + c4;
+      if (accumulate) { acc.x += o[0]; acc.y += o[1]; acc.z += o[2]; acc.w += o[3]; }
+      o[0] = acc.x; o[1] = acc.y; o[2] = acc.z; o[3] = acc.w;
+    } else {
+      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(C) + (long long)row * ldc + c4;
+      o[0] = __float2bfloat16_rn(acc.x); o[1] = __float2bfloat16_rn(acc.y);
+      o[2] = __float2bfloat16_rn(acc.z); o[3] = __float2bfloat16_rn(acc.w);
+    }
+  }
+}
+
+// C[M,N] (+)= A . B^T with optional k-splits; slab workspace is needed when k_splits > 1.
+static size_t store_gemm_slab_bytes(int M, int N, int K, int ctas, int forced_ksplit) {
+  if (N % 4 != 0) return 0;
+  const int tiles = ceil_div(M, GEMM_BLOCK_M * ctas) * ceil_div(N, BN);
+  const int s = choose_ksplits(tiles, clusters_for(ctas), ceil_div(K, GEMM_BLOCK_K), forced_ksplit);
+  return s > 1 ? align_up((size_t)s * M * N * 4, 256) : 0;
+}
+
+static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* C, long long ldc,
+                          int c_is_f32, int accumulate, int M, int N, int K, int ctas, int group_m, int forced_ksplit,
+                          void* slab, size_t slab_bytes, cudaStream_t st) {
+  GemmParams p = {};
+  const int tiles = ceil_div(M, GEMM_BLOCK_M * ctas) * ceil_div(N, BN);
+  int ks = (N % 4 == 0 && slab) ? choose_ksplits(tiles, clusters_for(ctas), ceil_div(K, GEMM_BLOCK_K), forced_ksplit) : 1;
+  if (ks > 1 && slab_bytes < (size_t)ks * M * N * 4) ks = 1;
+  fill_tiling(p, M, N, K, ctas, group_m, ks);
+  p.C = C; p.ldc = ldc; p.c_is_f32 = c_is_f32; p.accumulate = accumulate; p.slab = (float*)slab;
+  CUtensorMap ta, tb;
+  if (int e = make_ab_maps(&ta, &tb, A, lda, a_mn, B, ldb, b_mn, M, N, K, ctas)) return e;
+  if (int e = dispatch<EPI_STORE>(a_mn ? 1 : 0, b_mn ? 1 : 0, ctas, ta, tb, p, st)) return e;
+  if (ks > 1) {
+    const long long quads = (long long)M * (N / 4);
+    long long grid = (quads + 255) / 256;
+    const long long cap = (long long)sm_count() * 16;
+    if (grid > cap) grid = cap;
+    splitk_reduce_kernel<<<(int)grid, 256, 0, st>>>((const float*)slab, ks, M, N, C, ldc, c_is_f32, accumulate);
+    B200_CUDA_OK(cudaGetLastError());
+  }
+  return 0;
+}
+
 }  // namespace b200grpo
 
 using namespace b200grpo;
 
 static size_t dlogits_ld(int Vloc) { return align_up((size_t)Vloc, 64); }
+static size_t part_bytes(int M, int Vloc) { return align_up((size_t)ceil_div(Vloc, BN) * M * 16, 256); }
 
 extern "C" size_t b200grpo_lmhead_fwd_workspace(int M, int H, int Vloc) {
   (void)H;
-  GemmParams p;
-  fill_tiling(p, M, Vloc, 64, ctas_for(M), get_tunable(TUNE_FWD_SPLITS));
-  return align_up((size_t)p.n_splits * M * 16, 256);
+  return part_bytes(M, Vloc);
+}
+
+// saved-forward state for the recompute-free backward: [per-tile partials][bf16 logits relative to the tile max]
+extern "C" size_t b200grpo_lmhead_saved_bytes(int M, int H, int Vloc) {
+  (void)H;
+  return part_bytes(M, Vloc) + align_up((size_t)M * dlogits_ld(Vloc) * 2, 256);
 }
 
 extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
-                                   int M, int H, int Vloc, int64_t v_offset, float inv_temperature, float* stats,
+                                   int M, int H, int Vloc, int64_t v_offset, float inv_temperature, float* stats, void* saved,
                                    void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_device_sm100()) return e;
-  B200_REQUIRE(hidden && weight && targets && stats && workspace, "lmhead_fwd: null pointer");
+  B200_REQUIRE(hidden && weight && targets && stats && (workspace || saved), "lmhead_fwd: null pointer");
   B200_REQUIRE(M >= 1 && H >= 8 && Vloc >= 1 && H % 8 == 0, "lmhead_fwd: M=%d H=%d Vloc=%d (H must be a multiple of 8)", M, H, Vloc);
   B200_REQUIRE(inv_temperature > 0.f, "lmhead_fwd: temperature must be positive");
+  B200_REQUIRE(!saved || ((uintptr_t)saved & 255) == 0, "lmhead_fwd: saved buffer must be 256-byte aligned");
   const int ctas = ctas_for(M);
   GemmParams p = {};
-  fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_SPLITS));
-  const size_t need = align_up((size_t)p.n_splits * M * 16, 256);
-  if (workspace_bytes < need) { set_error("lmhead_fwd: workspace %zu < %zu", workspace_bytes, need); return B200GRPO_EWORKSPACE; }
-  p.targets = (const long long*)targets; p.v_offset = v_offset; p.inv_temp = inv_temperature; p.part = (float*)workspace;
+  fill_tiling(p, M, Vloc, H, ctas, 0, 1);
+  const size_t need = part_bytes(M, Vloc);
+  if (!saved && workspace_bytes < need) { set_error("lmhead_fwd: workspace %zu < %zu", workspace_bytes, need); return B200GRPO_EWORKSPACE; }
+  p.targets = (const long long*)targets; p.v_offset = v_offset; p.inv_temp = inv_temperature;
+  p.part = (float*)(saved ? saved : workspace);
+  if (saved) { p.zsave = (__nv_bfloat16*)((char*)saved + need); p.ldz = (long long)dlogits_ld(Vloc); }
   CUtensorMap ta, tb;
   if (int e = make_ab_maps(&ta, &tb, hidden, ldh, 0, weight, ldw, 0, M, Vloc, H, ctas)) return e;
   cudaStream_t st = (cudaStream_t)stream;
-  { ProfScope ps(PROF_FWD_GEMM, st); if (int e = dispatch<EPI_FWD_STATS>(0, 0, ctas, ta, tb, p, st)) return e; }
+  {
+    ProfScope ps(PROF_FWD_GEMM, st);
+    const int e = saved ? dispatch<EPI_FWD_STATS, true>(0, 0, ctas, ta, tb, p, st) : dispatch<EPI_FWD_STATS, false>(0, 0, ctas, ta, tb, p, st);
+    if (e) return e;
+  }
   ProfScope ps(PROF_FWD_MERGE, st);
-  fwd_merge_kernel<<<ceil_div(M, 256), 256, 0, st>>>((const float4*)workspace, p.n_splits, M, (float4*)stats);
+  fwd_merge_kernel<<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, p.n_blocks, M, (float4*)stats);
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }
@@ -211,66 +352,73 @@ extern "C" int b200grpo_lmhead_finalize(const float* stats, int R, int M, float*
   return B200GRPO_OK;
 }
 
-extern "C" size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc) {
-  (void)H;
-  return align_up((size_t)M * dlogits_ld(Vloc) * 2, 256);
+extern "C" size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc, int with_saved) {
+  const int ctas = ctas_for(M);
+  const size_t slab = store_gemm_slab_bytes(M, H, Vloc, ctas, get_tunable(TUNE_DH_KSPLIT));
+  return (with_saved ? 0 : align_up((size_t)M * dlogits_ld(Vloc) * 2, 256)) + slab + 256;
 }
 
 extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
                                    const float* lse, const float* entropy, const float* coef_lp, const float* coef_ent,
                                    const float* grad_scale, int M, int H, int Vloc, int64_t v_offset, float inv_temperature,
-                                   void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw, int grad_weight_is_f32,
-                                   int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
+                                   void* saved, void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw,
+                                   int grad_weight_is_f32, int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_device_sm100()) return e;
   B200_REQUIRE(hidden && weight && targets && lse && entropy && coef_lp && coef_ent && workspace, "lmhead_bwd: null pointer");
   B200_REQUIRE(M >= 1 && H >= 8 && Vloc >= 1 && H % 8 == 0, "lmhead_bwd: M=%d H=%d Vloc=%d", M, H, Vloc);
   B200_REQUIRE(!accumulate || grad_weight_is_f32, "lmhead_bwd: accumulate needs an f32 grad_weight");
   const size_t ldd = dlogits_ld(Vloc);
-  const size_t need = align_up((size_t)M * ldd * 2, 256);
+  const size_t need = b200grpo_lmhead_bwd_workspace(M, H, Vloc, saved != nullptr);
   if (workspace_bytes < need) { set_error("lmhead_bwd: workspace %zu < %zu", workspace_bytes, need); return B200GRPO_EWORKSPACE; }
   const int ctas = ctas_for(M);
   cudaStream_t st = (cudaStream_t)stream;
-  CUtensorMap ta, tb;
-  {  // 1. recompute logits tile by tile -> bf16 dlogits
+  __nv_bfloat16* dlog;
+  char* slab;
+  if (saved) {  // 1a. saved logits -> dlogits in place (no recompute GEMM)
+    dlog = (__nv_bfloat16*)((char*)saved + part_bytes(M, Vloc));
+    slab = (char*)workspace;
+    ProfScope ps(PROF_DLOGITS_EW, st);
+    dim3 grid(ceil_div(Vloc, DL_THREADS * 8), M < 32768 ? M : 32768);
+    dlogits_from_saved_kernel<<<grid, DL_THREADS, 0, st>>>(dlog, (long long)ldd, (const float4*)saved, M, Vloc, (const long long*)targets,
+                                                           v_offset, lse, entropy, coef_lp, coef_ent, grad_scale, inv_temperature);
+    B200_CUDA_OK(cudaGetLastError());
+  } else {      // 1b. recompute logits tile by tile -> bf16 dlogits
+    dlog = (__nv_bfloat16*)workspace;
+    slab = (char*)workspace + align_up((size_t)M * ldd * 2, 256);
     GemmParams p = {};
-    fill_tiling(p, M, Vloc, H, ctas, 0);
+    fill_tiling(p, M, Vloc, H, ctas, 0, 1);
     p.targets = (const long long*)targets; p.v_offset = v_offset; p.inv_temp = inv_temperature;
     p.lse = lse; p.entropy = entropy; p.coef_lp = coef_lp; p.coef_ent = coef_ent; p.grad_scale = grad_scale;
-    p.dlogits = (__nv_bfloat16*)workspace; p.ldd = (long long)ldd;
+    p.dlogits = dlog; p.ldd = (long long)ldd;
+    CUtensorMap ta, tb;
     if (int e = make_ab_maps(&ta, &tb, hidden, ldh, 0, weight, ldw, 0, M, Vloc, H, ctas)) return e;
     ProfScope ps(PROF_BWD_DLOGITS, st);
     if (int e = dispatch<EPI_BWD_DLOGITS>(0, 0, ctas, ta, tb, p, st)) return e;
   }
+  const size_t slab_bytes = (char*)workspace + workspace_bytes - slab;
   if (grad_hidden) {  // 2. dH[M,H] = dlogits[M,V] . W[V,H]   (B is MN-major: vocab rows are the K axis)
-    GemmParams p = {};
-    fill_tiling(p, M, H, Vloc, ctas, 0);
-    p.C = grad_hidden; p.ldc = ldgh; p.c_is_f32 = 0; p.accumulate = 0;
-    if (int e = make_ab_maps(&ta, &tb, workspace, (long long)ldd, 0, weight, ldw, 1, M, H, Vloc, ctas)) return e;
     ProfScope ps(PROF_BWD_DH, st);
-    if (int e = dispatch<EPI_STORE>(0, 1, ctas, ta, tb, p, st)) return e;
+    if (int e = run_store_gemm(dlog, (long long)ldd, 0, weight, ldw, 1, grad_hidden, ldgh, 0, 0, M, H, Vloc, ctas,
+                               get_tunable(TUNE_DH_GROUP_M), get_tunable(TUNE_DH_KSPLIT), slab, slab_bytes, st)) return e;
   }
   if (grad_weight) {  // 3. dW[V,H] = dlogits^T[V,M] . hidden[M,H]   (both operands MN-major: tokens are the K axis)
-    GemmParams p = {};
-    fill_tiling(p, Vloc, H, M, ctas, 0);
-    p.C = grad_weight; p.ldc = ldgw; p.c_is_f32 = grad_weight_is_f32; p.accumulate = accumulate;
-    if (int e = make_ab_maps(&ta, &tb, workspace, (long long)ldd, 1, hidden, ldh, 1, Vloc, H, M, ctas)) return e;
     ProfScope ps(PROF_BWD_DW, st);
-    if (int e = dispatch<EPI_STORE>(1, 1, ctas, ta, tb, p, st)) return e;
+    if (int e = run_store_gemm(dlog, (long long)ldd, 1, hidden, ldh, 1, grad_weight, ldgw, grad_weight_is_f32, accumulate, Vloc, H, M,
+                               ctas, get_tunable(TUNE_DW_GROUP_M), 1, nullptr, 0, st)) return e;
   }
   return B200GRPO_OK;
 }
 
 extern "C" int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb, int b_mn_major, void* C,
-                                  int64_t ldc, int c_is_f32, int accumulate, int M, int N, int K, void* stream) {
+                                  int64_t ldc, int c_is_f32, int accumulate, int M, int N, int K, int group_m, int k_splits,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_device_sm100()) return e;
   B200_REQUIRE(A && B && C && M >= 1 && N >= 1 && K >= 1, "gemm: bad argument");
   B200_REQUIRE(!accumulate || c_is_f32, "gemm: accumulate needs f32 C");
+  B200_REQUIRE(k_splits <= 1 || (workspace && workspace_bytes >= (size_t)k_splits * M * N * 4 && N % 4 == 0),
+               "gemm: k_splits=%d needs a workspace of k_splits*M*N*4 bytes and N %% 4 == 0", k_splits);
   const int ctas = ctas_for(M);
-  GemmParams p = {};
-  fill_tiling(p, M, N, K, ctas, 0);
-  p.C = C; p.ldc = ldc; p.c_is_f32 = c_is_f32; p.accumulate = accumulate;
-  CUtensorMap ta, tb;
-  if (int e = make_ab_maps(&ta, &tb, A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, ctas)) return e;
   ProfScope ps(PROF_GEMM, (cudaStream_t)stream);
-  return dispatch<EPI_STORE>(a_mn_major ? 1 : 0, b_mn_major ? 1 : 0, ctas, ta, tb, p, (cudaStream_t)stream);
+  return run_store_gemm(A, lda, a_mn_major ? 1 : 0, B, ldb, b_mn_major ? 1 : 0, C, ldc, c_is_f32, accumulate, M, N, K, ctas, group_m,
+                        k_splits < 1 ? 1 : k_splits, k_splits > 1 ? workspace : nullptr, workspace_bytes, (cudaStream_t)stream);
 }

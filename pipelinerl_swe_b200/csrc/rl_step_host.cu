@@ -8,8 +8,9 @@ using namespace b200grpo;
 namespace {
 struct Layout {
   size_t hidden, ids, labels, pos, f32[7], stats, logprob, entropy, lse, coef_lp, coef_ent, metrics, loss, ghid, ws_fwd,
-      ws_loss, ws_bwd, total;
-  size_t n_fwd, n_loss, n_bwd;
+      ws_loss, ws_bwd, saved, total;
+  size_t n_fwd, n_loss, n_bwd, n_saved;
+  int save;
 };
 Layout make_layout(int L, int H, int V) {
   Layout o;
@@ -26,7 +27,9 @@ Layout make_layout(int L, int H, int V) {
   o.ghid = take((size_t)L * H * 2);
   o.n_fwd = b200grpo_lmhead_fwd_workspace(M, H, V); o.ws_fwd = take(o.n_fwd);
   o.n_loss = b200grpo_token_loss_workspace(1, L); o.ws_loss = take(o.n_loss);
-  o.n_bwd = b200grpo_lmhead_bwd_workspace(M, H, V); o.ws_bwd = take(o.n_bwd);
+  o.save = get_tunable(TUNE_SAVE_LOGITS) != 0;
+  o.n_bwd = b200grpo_lmhead_bwd_workspace(M, H, V, o.save); o.ws_bwd = take(o.n_bwd);
+  o.n_saved = o.save ? b200grpo_lmhead_saved_bytes(M, H, V) : 0; o.saved = take(o.n_saved);
   o.total = off;
   return o;
 }
@@ -59,7 +62,7 @@ extern "C" int b200grpo_rl_step_host(const b200grpo_host_batch* b, int L, int H,
   for (int i = 0; i < 7; ++i) B200_CUDA_OK(cudaMemcpyAsync(w + o.f32[i], f32_src[i], (size_t)L * 4, cudaMemcpyHostToDevice, st));
   const int64_t* targets = (const int64_t*)(w + o.ids) + 1;  // row t is scored against input_ids[t+1]
   int e = b200grpo_lmhead_fwd(w + o.hidden, H, weight, ldw, targets, M, H, V, 0, 1.0f / temperature, (float*)(w + o.stats),
-                              w + o.ws_fwd, o.n_fwd, stream);
+                              o.save ? (void*)(w + o.saved) : nullptr, w + o.ws_fwd, o.n_fwd, stream);
   if (e) return e;
   e = b200grpo_lmhead_finalize((const float*)(w + o.stats), 1, M, (float*)(w + o.logprob), (float*)(w + o.entropy),
                                (float*)(w + o.lse), stream);
@@ -74,7 +77,7 @@ extern "C" int b200grpo_rl_step_host(const b200grpo_host_batch* b, int L, int H,
   if (grad_weight || grad_hidden_host_bf16) {
     e = b200grpo_lmhead_bwd(w + o.hidden, H, weight, ldw, targets, (const float*)(w + o.lse), (const float*)(w + o.entropy),
                             (const float*)(w + o.coef_lp), (const float*)(w + o.coef_ent), nullptr, M, H, V, 0,
-                            1.0f / temperature, (void*)(w + o.ghid), H, grad_weight, H,
+                            1.0f / temperature, o.save ? (void*)(w + o.saved) : nullptr, (void*)(w + o.ghid), H, grad_weight, H,
                             grad_weight_is_f32, accumulate, w + o.ws_bwd, o.n_bwd, stream);
     if (e) return e;
     B200_CUDA_OK(cudaMemsetAsync(w + o.ghid + (size_t)M * H * 2, 0, (size_t)H * 2, st));  // last position has no target

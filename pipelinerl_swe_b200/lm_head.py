@@ -18,6 +18,20 @@ from . import ops
 from .vocab_parallel import exchange_stats, reduce_grad_hidden
 
 
+_SAVE_LOGITS = True
+
+
+def save_logits_enabled() -> bool:
+    return _SAVE_LOGITS
+
+
+def set_save_logits(flag: bool) -> None:
+    """True (default): forward keeps bf16 logits (2 B x tokens x vocab until backward), backward skips the
+    recompute GEMM.  False: nothing of size tokens x vocab is kept; backward recomputes the logits."""
+    global _SAVE_LOGITS
+    _SAVE_LOGITS = bool(flag)
+
+
 class LMHeadLogprobFunction(torch.autograd.Function):
     """(hidden [M,H] bf16, weight [Vloc,H] bf16, targets [M] i64) -> out f32 [M,2] = (logprob, entropy).
 
@@ -28,12 +42,17 @@ class LMHeadLogprobFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, hidden, weight, targets, inv_temperature: float, group=None, v_offset: int = 0):
-        stats = ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset)
+        # keep bf16 logits for a recompute-free backward when a backward will follow
+        need_bwd = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+        saved = ops.lmhead_saved_buffer(hidden.shape[0], hidden.shape[1], weight.shape[0], hidden.device) \
+            if (need_bwd and save_logits_enabled()) else None
+        stats = ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset, saved)
         if group is not None:
             stats = exchange_stats(stats, group)  # [R,M,4], 16 B/token/rank over NCCL
         logprob, entropy, lse = ops.lmhead_finalize(stats)
         ctx.save_for_backward(hidden, weight, targets, lse, entropy)
         ctx.inv_temperature, ctx.group, ctx.v_offset = inv_temperature, group, v_offset
+        ctx.saved = saved
         return torch.stack((logprob, entropy), dim=1)
 
     @staticmethod
@@ -42,8 +61,9 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         g = grad_out.float()
         coef_lp, coef_ent = g[:, 0].contiguous(), g[:, 1].contiguous()
         need_h, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        saved, ctx.saved = ctx.saved, None  # consumed in place by the backward; a second backward recomputes
         gh, gw = ops.lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, ctx.inv_temperature, ctx.v_offset,
-                                need_grad_hidden=need_h, need_grad_weight=need_w)
+                                need_grad_hidden=need_h, need_grad_weight=need_w, saved=saved)
         if gh is not None and ctx.group is not None:
             reduce_grad_hidden(gh, ctx.group)  # dH = sum over vocab shards
         return gh, gw, None, None, None, None

@@ -45,8 +45,14 @@ def _req(t: torch.Tensor, dtype: torch.dtype, name: str) -> torch.Tensor:
     return t
 
 
+def lmhead_saved_buffer(M: int, H: int, V: int, device) -> torch.Tensor:
+    """Scratch the forward fills for a recompute-free backward (bf16 logits relative to their tile max)."""
+    n = lib().b200grpo_lmhead_saved_bytes(M, H, V)
+    return torch.empty(n, dtype=torch.uint8, device=device)
+
+
 def lmhead_fwd_stats(hidden: torch.Tensor, weight: torch.Tensor, targets: torch.Tensor, inv_temperature: float,
-                     v_offset: int = 0) -> torch.Tensor:
+                     v_offset: int = 0, saved: torch.Tensor | None = None) -> torch.Tensor:
     """K1: per-row (max, sumexp, sum e*z, z_target) over this rank's vocab rows -> f32 [M,4]."""
     _req(hidden, torch.bfloat16, "hidden"); _req(weight, torch.bfloat16, "weight"); _req(targets, torch.int64, "targets")
     M, H = hidden.shape
@@ -56,7 +62,7 @@ def lmhead_fwd_stats(hidden: torch.Tensor, weight: torch.Tensor, targets: torch.
     n = lib().b200grpo_lmhead_fwd_workspace(M, H, V)
     ws = _workspace(hidden.device, n)
     check(lib().b200grpo_lmhead_fwd(hidden.data_ptr(), H, weight.data_ptr(), H, targets.data_ptr(), M, H, V, v_offset,
-                                    float(inv_temperature), stats.data_ptr(), ws.data_ptr(), ws.numel(), _stream()))
+                                    float(inv_temperature), stats.data_ptr(), _ptr(saved), ws.data_ptr(), ws.numel(), _stream()))
     return stats
 
 
@@ -73,8 +79,8 @@ def lmhead_finalize(stats: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, to
 
 def lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, inv_temperature, v_offset=0, grad_scale=None,
                need_grad_hidden=True, need_grad_weight=True, grad_weight_out: torch.Tensor | None = None,
-               accumulate: bool = False):
-    """K2: (grad_hidden bf16 [M,H] | None, grad_weight [V,H] | None)."""
+               accumulate: bool = False, saved: torch.Tensor | None = None):
+    """K2: (grad_hidden bf16 [M,H] | None, grad_weight [V,H] | None).  ``saved`` (from the forward) is consumed."""
     _req(hidden, torch.bfloat16, "hidden"); _req(weight, torch.bfloat16, "weight"); _req(targets, torch.int64, "targets")
     for name, t in (("lse", lse), ("entropy", entropy), ("coef_lp", coef_lp), ("coef_ent", coef_ent)):
         _req(t, torch.float32, name)
@@ -85,11 +91,11 @@ def lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, inv_tem
     if need_grad_weight:
         gw = grad_weight_out if grad_weight_out is not None else torch.empty(V, H, dtype=torch.bfloat16, device=hidden.device)
         assert gw.shape == (V, H) and gw.is_contiguous() and gw.dtype in (torch.bfloat16, torch.float32)
-    n = lib().b200grpo_lmhead_bwd_workspace(M, H, V)
+    n = lib().b200grpo_lmhead_bwd_workspace(M, H, V, int(saved is not None))
     ws = _workspace(hidden.device, n, "dlogits")
     check(lib().b200grpo_lmhead_bwd(hidden.data_ptr(), H, weight.data_ptr(), H, targets.data_ptr(), lse.data_ptr(),
                                     entropy.data_ptr(), coef_lp.data_ptr(), coef_ent.data_ptr(), _ptr(grad_scale), M, H, V,
-                                    v_offset, float(inv_temperature), _ptr(gh), H, _ptr(gw), H,
+                                    v_offset, float(inv_temperature), _ptr(saved), _ptr(gh), H, _ptr(gw), H,
                                     int(gw is not None and gw.dtype == torch.float32), int(accumulate), ws.data_ptr(),
                                     ws.numel(), _stream()))
     return gh, gw
@@ -135,7 +141,7 @@ def segment_bounds(position_ids: torch.Tensor) -> torch.Tensor:
 
 
 def gemm_bf16(A: torch.Tensor, B: torch.Tensor, a_mn_major=False, b_mn_major=False, out_dtype=torch.float32,
-              out: torch.Tensor | None = None, accumulate=False) -> torch.Tensor:
+              out: torch.Tensor | None = None, accumulate=False, group_m: int = 0, k_splits: int = 1) -> torch.Tensor:
     """C[M,N] = A.B^T on the tcgen05 mainloop (test surface).  MN-major operands are given as [K, M|N]."""
     _req(A, torch.bfloat16, "A"); _req(B, torch.bfloat16, "B")
     (K, M) = A.shape if a_mn_major else A.shape[::-1]
@@ -143,9 +149,10 @@ def gemm_bf16(A: torch.Tensor, B: torch.Tensor, a_mn_major=False, b_mn_major=Fal
     assert K == K2
     if out is None:
         out = torch.empty(M, N, dtype=out_dtype, device=A.device)
+    ws = _workspace(A.device, max(k_splits, 1) * M * N * 4 if k_splits > 1 else 256, "slab")
     check(lib().b200grpo_gemm_bf16(A.data_ptr(), A.stride(0), int(a_mn_major), B.data_ptr(), B.stride(0), int(b_mn_major),
                                    out.data_ptr(), out.stride(0), int(out.dtype == torch.float32), int(accumulate), M, N, K,
-                                   _stream()))
+                                   int(group_m), int(k_splits), ws.data_ptr(), ws.numel(), _stream()))
     return out
 
 

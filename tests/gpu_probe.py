@@ -78,6 +78,40 @@ def probe_bwd(two_cta, M, H, V, temp=1.0):
     return e1 < 2e-2 and e2 < 2e-2, f"rel dH={e1:.3e} rel dW={e2:.3e}"
 
 
+def probe_bwd_saved(two_cta, M, H, V, temp=1.0):
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", two_cta)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    h = torch.randn(M, H, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(V, H, device="cuda", generator=g) * 0.05).bfloat16()
+    tgt = torch.randint(0, V, (M,), device="cuda", generator=g)
+    c_lp = torch.randn(M, device="cuda", generator=g) * 0.1
+    c_ent = torch.randn(M, device="cuda", generator=g) * 0.01
+    saved = ops.lmhead_saved_buffer(M, H, V, h.device)
+    stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp, saved=saved)
+    lp, ent, lse = ops.lmhead_finalize(stats)
+    gh0, gw0 = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0 / temp)              # recompute path
+    gh1, gw1 = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0 / temp, saved=saved)  # saved-logits path
+    torch.cuda.synchronize()
+    e1, e2 = _rel(gh1, gh0), _rel(gw1, gw0)
+    return e1 < 1e-2 and e2 < 1e-2, f"saved vs recompute: rel dH={e1:.3e} rel dW={e2:.3e}"
+
+
+def probe_gemm_splitk(two_cta, M, N, K, ks, group_m):
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", two_cta)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    A = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    B = torch.randn(N, K, device="cuda", generator=g).bfloat16()
+    ref = A.float() @ B.float().t()
+    out = ops.gemm_bf16(A, B, out_dtype=torch.bfloat16, group_m=group_m, k_splits=ks)
+    acc = torch.ones(M, N, device="cuda")
+    ops.gemm_bf16(A, B, out=acc, accumulate=True, group_m=group_m, k_splits=ks)
+    torch.cuda.synchronize()
+    e1, e2 = _rel(out, ref), _rel(acc, ref + 1)
+    return e1 < 1e-2 and e2 < 1e-4, f"bf16 rel={e1:.3e} f32-accumulate rel={e2:.3e}"
+
+
 def probe_speed(two_cta, M, H, V):
     from pipelinerl_swe_b200 import _abi, ops
     _abi.set_tunable("two_cta", two_cta)
@@ -98,15 +132,32 @@ def probe_speed(two_cta, M, H, V):
         ms = t0.elapsed_time(t1) / 3
         out.append(f"{name} {ms:.3f} ms = {2 * M * H * V / ms / 1e9:.1f} TFLOP/s")
     lp, ent, lse = r
-    for _ in range(2):
-        ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0)
+    saved = ops.lmhead_saved_buffer(M, H, V, h.device)
+    for name, kw, nflop in (("bwd_recompute", {}, 6), ("bwd_saved", {"saved": saved}, 4)):
+        for _ in range(2):
+            ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0, **kw)
+        _abi.profile_enable(64)
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(3):
+            ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0, **kw)
+        t1.record(); torch.cuda.synchronize()
+        ms = t0.elapsed_time(t1) / 3
+        prof = {}
+        for tag, t in _abi.profile_read(64):
+            prof[tag] = prof.get(tag, 0.0) + t / 3
+        _abi.profile_enable(0)
+        out.append(f"{name} {ms:.3f} ms = {nflop * M * H * V / ms / 1e9:.1f} TFLOP/s executed " +
+                   " ".join(f"{k}={v:.3f}" for k, v in prof.items()))
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(2):
+        ops.lmhead_fwd_stats(h, w, tgt, 1.0, saved=saved)
     t0.record()
     for _ in range(3):
-        ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0)
+        ops.lmhead_fwd_stats(h, w, tgt, 1.0, saved=saved)
     t1.record(); torch.cuda.synchronize()
     ms = t0.elapsed_time(t1) / 3
-    out.append(f"bwd {ms:.3f} ms = {6 * M * H * V / ms / 1e9:.1f} TFLOP/s executed")
+    out.append(f"fwd_save {ms:.3f} ms = {2 * M * H * V / ms / 1e9:.1f} TFLOP/s")
     return True, "; ".join(out)
 
 
@@ -122,6 +173,9 @@ for ctas in (0, 1):
     PROBES[f"fwd_mid_split1_c{ctas + 1}"] = (probe_fwd, (ctas, 513, 256, 5000, 1.3, 1))
     PROBES[f"bwd_small_c{ctas + 1}"] = (probe_bwd, (ctas, 300, 128, 1000, 0.7))
     PROBES[f"bwd_mid_c{ctas + 1}"] = (probe_bwd, (ctas, 1023, 512, 9000, 1.0))
+    PROBES[f"bwdsaved_small_c{ctas + 1}"] = (probe_bwd_saved, (ctas, 300, 128, 1000, 0.7))
+    PROBES[f"bwdsaved_mid_c{ctas + 1}"] = (probe_bwd_saved, (ctas, 1023, 512, 9000 + 8, 1.0))
+    PROBES[f"gemm_splitk_c{ctas + 1}"] = (probe_gemm_splitk, (ctas, 1000, 776, 9000, 3, 2))
     PROBES[f"speed_c2shape_c{ctas + 1}"] = (probe_speed, (ctas, 8192, 1536, 151936))
     PROBES[f"speed_c3shape_c{ctas + 1}"] = (probe_speed, (ctas, 8192, 3584, 152064))
 

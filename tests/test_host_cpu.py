@@ -31,7 +31,7 @@ def test_library_exports_every_header_symbol():
     for n in names:
         assert hasattr(handle, n), f"libb200grpo.so does not export {n}"
     assert set(names) == set(_abi.SIGNATURES), set(names) ^ set(_abi.SIGNATURES)
-    assert _abi.lib().b200grpo_abi_version() == 1
+    assert _abi.lib().b200grpo_abi_version() == 2
 
 
 def test_struct_layouts_match_header():
