@@ -38,6 +38,7 @@ constexpr int GEMM_THREADS = 256;
 constexpr int GEMM_EPI_WARP0 = 4;
 constexpr float LOG2E_F = 1.4426950408889634f;
 constexpr float LN2_F = 0.6931471805599453f;
+constexpr int PANEL_W = 256;        // saved logits / dlogits are stored in [M x 256] column panels (== BLOCK_N)
 
 struct GemmParams {
   int M, N, K;
@@ -52,11 +53,9 @@ struct GemmParams {
   long long v_offset;
   float inv_temp;
   float* part;              // [n_blocks][M][4]  per-tile (max z, sum e, sum e*z, z_target|0)
-  __nv_bfloat16* zsave;     // optional [M][ldz]: (z - tile max) saved for a recompute-free backward
-  long long ldz;
+  __nv_bfloat16* zsave;     // optional panels [n_blocks][M][256]: (z - tile max)/T saved for a recompute-free backward
   const float *lse, *entropy, *coef_lp, *coef_ent, *grad_scale;
-  __nv_bfloat16* dlogits;   // [M][ldd]
-  long long ldd;
+  __nv_bfloat16* dlogits;   // panels [n_blocks][M][256]
 };
 
 template <int BLOCK_N, int kCtas, int kStages>
@@ -116,7 +115,7 @@ struct FwdRowState { float m_raw, s, u, tgt; int tcol; };
 // target logit, and (optionally) save y = (z - tile max)/T as bf16 for the backward.
 template <bool kSave>
 __device__ __forceinline__ void fwd_chunk(FwdRowState& st, const uint32_t (&v)[32], int col0, int n_valid, float scale2,
-                                          float inv_temp, __nv_bfloat16* zrow) {
+                                          float inv_temp, __nv_bfloat16* zout) {  // zout: this row's 32 columns in the panel
   const float neg = -st.m_raw * scale2;
   float s = 0.f, u = 0.f;
   if (n_valid >= 32) {
@@ -149,25 +148,21 @@ __device__ __forceinline__ void fwd_chunk(FwdRowState& st, const uint32_t (&v)[3
                                                      fmaf(__uint_as_float(v[j + 1]), inv_temp, negm));
       packed[j >> 1] = *reinterpret_cast<const uint32_t*>(&b);
     }
-    if (n_valid >= 32) {
-      uint4* o = reinterpret_cast<uint4*>(zrow + col0);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) o[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
-    } else {
+    if (n_valid < 32) {  // vocab tail: columns past N stay zero (they are K-padding of the dH GEMM)
 #pragma unroll
       for (int j = 0; j < 32; ++j)
-        if (j < n_valid) {
-          const uint32_t w = packed[j >> 1];
-          reinterpret_cast<unsigned short*>(zrow + col0)[j] = (j & 1) ? (unsigned short)(w >> 16) : (unsigned short)(w & 0xffffu);
-        }
+        if (j >= n_valid) packed[j >> 1] &= (j & 1) ? 0x0000ffffu : 0xffff0000u;
     }
+    uint4* o = reinterpret_cast<uint4*>(zout);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) o[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
   }
 }
 
 struct BwdRowConst { float lse2, a, e, ent; int tcol; };
 
 __device__ __forceinline__ void bwd_chunk(const BwdRowConst& rc, const uint32_t (&v)[32], int col0, int n_valid,
-                                          float scale2, __nv_bfloat16* out_row) {
+                                          float scale2, __nv_bfloat16* out) {  // out: this row's 32 columns in the panel
   uint32_t packed[16];
   const int t = rc.tcol - col0;
 #pragma unroll
@@ -184,19 +179,14 @@ __device__ __forceinline__ void bwd_chunk(const BwdRowConst& rc, const uint32_t 
     const __nv_bfloat162 b = __floats2bfloat162_rn(d[0], d[1]);
     packed[j >> 1] = *reinterpret_cast<const uint32_t*>(&b);
   }
-  if (n_valid >= 32) {
-    uint4* o = reinterpret_cast<uint4*>(out_row + col0);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) o[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
-  } else {
+  if (n_valid < 32) {  // vocab tail: columns past N stay zero (K-padding of the dH GEMM)
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-      if (j < n_valid) {
-        const uint32_t w = packed[j >> 1];
-        const unsigned short h = (j & 1) ? (unsigned short)(w >> 16) : (unsigned short)(w & 0xffffu);
-        reinterpret_cast<unsigned short*>(out_row + col0)[j] = h;
-      }
+      if (j >= n_valid) packed[j >> 1] &= (j & 1) ? 0x0000ffffu : 0xffff0000u;
   }
+  uint4* o = reinterpret_cast<uint4*>(out);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) o[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
 }
 
 __device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t (&v)[32], int row, int col0, int n_valid, int ks) {
@@ -252,7 +242,7 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t 
 // ---------------------------------------------------------------------------------------
 // The kernel
 // ---------------------------------------------------------------------------------------
-template <int kEpi, int kAMajor, int kBMajor, int kCtas, int BLOCK_N, int kStages, bool kSave = false>
+template <int kEpi, int kAMajor, int kBMajor, int kCtas, int BLOCK_N, int kStages, bool kSave = false, bool kAPanel = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, const GemmParams p) {
   using L = GemmSmem<BLOCK_N, kCtas, kStages>;
@@ -312,7 +302,19 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
           if constexpr (kCtas == 1) ptx::tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
           else ptx::tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
         };
-        if constexpr (kAMajor == MAJOR_K) {
+        auto load3 = [&](void* dst, const CUtensorMap* tm, int c0, int c1, int c2) {
+          if constexpr (kCtas == 1) ptx::tma_load_3d(dst, tm, &full_bar[stage], c0, c1, c2);
+          else ptx::tma_load_3d_pair(dst, tm, &full_bar[stage], c0, c1, c2);
+        };
+        if constexpr (kAPanel) {  // A lives in 256-column panels: element (r, c) at panel c/256, row r, column c%256
+          if constexpr (kAMajor == MAJOR_K) {
+            load3(sa, &tm_a, k0 % PANEL_W, m0, k0 / PANEL_W);        // box {64 k, 128 rows, 1}
+          } else {
+#pragma unroll
+            for (int a = 0; a < GEMM_BLOCK_M / 64; ++a)
+              load3(sa + a * 8192, &tm_a, (m0 + a * 64) % PANEL_W, k0, (m0 + a * 64) / PANEL_W);  // box {64 m, 64 k, 1}
+          }
+        } else if constexpr (kAMajor == MAJOR_K) {
           load(sa, &tm_a, k0, m0);                                   // box {64 k, 128 rows}
         } else {
 #pragma unroll
@@ -413,9 +415,12 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         const int n_valid = min(32, p.N - col0);
         if constexpr (kEpi == EPI_FWD_STATS) {
           if (kSave && !row_ok) continue;
-          fwd_chunk<kSave>(fs, v, col0, n_valid, scale2, p.inv_temp, kSave ? p.zsave + (long long)row * p.ldz : nullptr);
+          fwd_chunk<kSave>(fs, v, col0, n_valid, scale2, p.inv_temp,
+                           kSave ? p.zsave + ((long long)it.nb * p.M + row) * PANEL_W + c * 32 : nullptr);
         }
-        if constexpr (kEpi == EPI_BWD_DLOGITS) { if (row_ok) bwd_chunk(bc, v, col0, n_valid, scale2, p.dlogits + (long long)row * p.ldd); }
+        if constexpr (kEpi == EPI_BWD_DLOGITS) {
+          if (row_ok) bwd_chunk(bc, v, col0, n_valid, scale2, p.dlogits + ((long long)it.nb * p.M + row) * PANEL_W + c * 32);
+        }
         if constexpr (kEpi == EPI_STORE) { if (row_ok) store_chunk(p, v, row, col0, n_valid, it.ks); }
       }
       ptx::tc_fence_before();

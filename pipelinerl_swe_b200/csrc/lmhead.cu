@@ -44,6 +44,21 @@ static int make_tmap(CUtensorMap* tm, const void* ptr, long long inner, long lon
   return 0;
 }
 
+// bf16 panels [n_panels][rows][256]: dims {256, rows, n_panels}; box = {64, box_rows, 1}
+static int make_tmap_panel(CUtensorMap* tm, const void* ptr, long long rows, long long n_panels, int box_rows) {
+  if (int e = load_encode_fn()) return e;
+  B200_REQUIRE(((uintptr_t)ptr & 255) == 0, "panel operand must be 256-byte aligned");
+  cuuint64_t gdim[3] = {(cuuint64_t)PANEL_W, (cuuint64_t)rows, (cuuint64_t)n_panels};
+  cuuint64_t gstride[2] = {(cuuint64_t)PANEL_W * 2, (cuuint64_t)rows * PANEL_W * 2};
+  cuuint32_t box[3] = {64u, (cuuint32_t)box_rows, 1u};
+  cuuint32_t estr[3] = {1u, 1u, 1u};
+  const CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (panel) failed with %d (rows %lld panels %lld)", (int)r, rows, n_panels); return B200GRPO_ECUDA; }
+  return 0;
+}
+
 // ---- tiling --------------------------------------------------------------------------------
 constexpr int BN = 256;
 constexpr int STAGES_1CTA = 4, STAGES_2CTA = 6;
@@ -64,11 +79,12 @@ static int choose_ksplits(int tiles, int clusters, int kb_total, int forced) {
   return best;
 }
 
-template <int kEpi, int kAMajor, int kBMajor, int kCtas, bool kSave>
+template <int kEpi, int kAMajor, int kBMajor, int kCtas, bool kSave, bool kAPanel>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
   constexpr int kStages = kCtas == 1 ? STAGES_1CTA : STAGES_2CTA;
   using L = GemmSmem<BN, kCtas, kStages>;
-  auto kern = gemm_sm100_kernel<kEpi, kAMajor, kBMajor, kCtas, BN, kStages, kSave>;
+  static_assert(BN == PANEL_W, "panels are one N tile wide");
+  auto kern = gemm_sm100_kernel<kEpi, kAMajor, kBMajor, kCtas, BN, kStages, kSave, kAPanel>;
   static bool configured = false;
   if (!configured) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -119,11 +135,13 @@ static void fill_tiling(GemmParams& p, int M, int N, int K, int ctas, int group_
   p.k_splits = k_splits < 1 ? 1 : k_splits;
 }
 
-template <int kEpi, bool kSave = false>
+template <int kEpi, bool kSave = false, bool kAPanel = false>
 static int dispatch(int a_mn, int b_mn, int ctas, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
 #define B200_CASE(AM, BM, C) \
-  if (a_mn == AM && b_mn == BM && ctas == C) return launch_gemm<kEpi, AM, BM, C, kSave>(ta, tb, p, st);
-  if constexpr (kEpi == EPI_STORE) {
+  if (a_mn == AM && b_mn == BM && ctas == C) return launch_gemm<kEpi, AM, BM, C, kSave, kAPanel>(ta, tb, p, st);
+  if constexpr (kEpi == EPI_STORE && kAPanel) {   // the two backward GEMMs read dlogits panels
+    B200_CASE(0, 1, 1) B200_CASE(0, 1, 2) B200_CASE(1, 1, 1) B200_CASE(1, 1, 2)
+  } else if constexpr (kEpi == EPI_STORE) {
     B200_CASE(0, 0, 1) B200_CASE(0, 0, 2) B200_CASE(0, 1, 1) B200_CASE(0, 1, 2)
     B200_CASE(1, 0, 1) B200_CASE(1, 0, 2) B200_CASE(1, 1, 1) B200_CASE(1, 1, 2)
   } else {
@@ -197,45 +215,58 @@ __global__ void __launch_bounds__(256) finalize_kernel(const float4* __restrict_
   if (lse_out) lse_out[row] = lse;
 }
 
-// Saved forward logits -> dlogits, in place (the recompute-free backward).  z[t,j] holds
-// y = (logit - tile max)/T as bf16; the tile max lives in part[nb][t].x.  HBM-bound: 4 B/element
-// (bf16 in + bf16 out), 16-byte vectors, one block = 2048 consecutive columns of one row.
+// Saved forward logits -> dlogits, in place (the recompute-free backward).  z holds y = (logit - tile max)/T
+// as bf16 in [n_blocks][M][256] panels; the tile max lives in part[nb][t].x.  HBM-bound: 4 B/element
+// (bf16 in + bf16 out), 16-byte vectors, 32 threads per panel row, fully contiguous traversal.
 constexpr int DL_THREADS = 256;
+constexpr int DL_ROWS = 4;   // panel rows per warp iteration: 4 independent 16-byte loads in flight per thread
 __global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
-    __nv_bfloat16* __restrict__ z, long long ldz, const float4* __restrict__ part, int M, int N, const long long* __restrict__ targets,
+    __nv_bfloat16* __restrict__ z, const float4* __restrict__ part, int M, int N, int n_blocks, const long long* __restrict__ targets,
     long long v_offset, const float* __restrict__ lse, const float* __restrict__ entropy, const float* __restrict__ coef_lp,
     const float* __restrict__ coef_ent, const float* __restrict__ grad_scale, float inv_temp) {
-  const int col = (blockIdx.x * DL_THREADS + threadIdx.x) * 8;
-  if (col >= N) return;
-  const int nb = col / BN;
   const float gs = (grad_scale ? *grad_scale : 1.0f) * inv_temp;
-  for (int row = blockIdx.y; row < M; row += gridDim.y) {
-    const float lse_r = lse[row], a = coef_lp[row] * gs, e = coef_ent[row] * gs, ent = entropy[row];
-    const long long tl = targets[row] - v_offset;
-    const int t = (tl >= col && tl < col + 8) ? (int)(tl - col) : -1;
-    const float shift2 = (__ldg(&part[(long long)nb * M + row]).x - lse_r) * LOG2E_F;  // (tile max - lse) * log2 e
-    __nv_bfloat16* zr = z + (long long)row * ldz + col;
-    uint4 raw = *reinterpret_cast<const uint4*>(zr);
-    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+  const int sub = threadIdx.x & 31;                      // 8 columns each: 32 threads cover one 256-wide panel row
+  const long long n_rows = (long long)n_blocks * M;      // panel rows in storage order
+  const long long warp0 = ((long long)blockIdx.x * (DL_THREADS / 32) + (threadIdx.x >> 5)) * DL_ROWS;
+  const long long stride = (long long)gridDim.x * (DL_THREADS / 32) * DL_ROWS;
+  for (long long base = warp0; base < n_rows; base += stride) {
+    uint4 raw[DL_ROWS];
+    float shift2[DL_ROWS], a[DL_ROWS], e[DL_ROWS], ent[DL_ROWS];
+    int tcol[DL_ROWS], nval[DL_ROWS];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float2 y = __bfloat1622float2(h[q]);
-      float d[2];
-#pragma unroll
-      for (int w = 0; w < 2; ++w) {
-        const float y2 = fmaf(w ? y.y : y.x, LOG2E_F, shift2);   // log2 p
-        const float pr = fast_exp2(y2);
-        float g = -pr * fmaf(e, fmaf(y2, LN2_F, ent), a);        // -p * (a + e*(logp + H))
-        if (2 * q + w == t) g += a;
-        d[w] = g;
-      }
-      h[q] = __floats2bfloat162_rn(d[0], d[1]);
+    for (int r = 0; r < DL_ROWS; ++r) {
+      const long long pr = base + r;
+      nval[r] = 0;
+      if (pr >= n_rows) continue;
+      const int nb = (int)(pr / M), row = (int)(pr - (long long)nb * M);
+      const int col = nb * PANEL_W + sub * 8;
+      if (col >= N) continue;                            // tail columns stay zero
+      nval[r] = min(8, N - col);
+      raw[r] = *reinterpret_cast<const uint4*>(z + pr * PANEL_W + sub * 8);
+      a[r] = coef_lp[row] * gs; e[r] = coef_ent[row] * gs; ent[r] = entropy[row];
+      shift2[r] = (__ldg(&part[pr]).x - lse[row]) * LOG2E_F;   // (tile max - lse) * log2 e
+      const long long tl = targets[row] - v_offset;
+      tcol[r] = (tl >= col && tl < col + 8) ? (int)(tl - col) : -1;
     }
-    if (col + 8 <= N) {
-      *reinterpret_cast<uint4*>(zr) = raw;
-    } else {
-      const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(&raw);
-      for (int j = 0; j < N - col; ++j) zr[j] = src[j];
+#pragma unroll
+    for (int r = 0; r < DL_ROWS; ++r) {
+      if (nval[r] == 0) continue;
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw[r]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 y = __bfloat1622float2(h[q]);
+        float d[2];
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+          const float y2 = fmaf(w ? y.y : y.x, LOG2E_F, shift2[r]);   // log2 p
+          const float pr_ = fast_exp2(y2);
+          float g = -pr_ * fmaf(e[r], fmaf(y2, LN2_F, ent[r]), a[r]);  // -p * (a + e*(logp + H))
+          if (2 * q + w == tcol[r]) g += a[r];
+          d[w] = (2 * q + w < nval[r]) ? g : 0.f;
+        }
+        h[q] = __floats2bfloat162_rn(d[0], d[1]);
+      }
+      *reinterpret_cast<uint4*>(z + (base + r) * PANEL_W + sub * 8) = raw[r];
     }
   }
 }
@@ -272,9 +303,10 @@ static size_t store_gemm_slab_bytes(int M, int N, int K, int ctas, int forced_ks
   return s > 1 ? align_up((size_t)s * M * N * 4, 256) : 0;
 }
 
+// a_panel_rows > 0: A is a dlogits panel buffer [ceil(cols/256)][a_panel_rows][256] (lda unused)
 static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* C, long long ldc,
                           int c_is_f32, int accumulate, int M, int N, int K, int ctas, int group_m, int forced_ksplit,
-                          void* slab, size_t slab_bytes, cudaStream_t st) {
+                          void* slab, size_t slab_bytes, cudaStream_t st, int a_panel_rows = 0) {
   GemmParams p = {};
   const int tiles = ceil_div(M, GEMM_BLOCK_M * ctas) * ceil_div(N, BN);
   int ks = (N % 4 == 0 && slab) ? choose_ksplits(tiles, clusters_for(ctas), ceil_div(K, GEMM_BLOCK_K), forced_ksplit) : 1;
@@ -282,8 +314,15 @@ static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B,
   fill_tiling(p, M, N, K, ctas, group_m, ks);
   p.C = C; p.ldc = ldc; p.c_is_f32 = c_is_f32; p.accumulate = accumulate; p.slab = (float*)slab;
   CUtensorMap ta, tb;
-  if (int e = make_ab_maps(&ta, &tb, A, lda, a_mn, B, ldb, b_mn, M, N, K, ctas)) return e;
-  if (int e = dispatch<EPI_STORE>(a_mn ? 1 : 0, b_mn ? 1 : 0, ctas, ta, tb, p, st)) return e;
+  if (a_panel_rows > 0) {
+    const int cols = a_mn ? M : K;  // the panelled (vocab) axis
+    if (int e = make_tmap_panel(&ta, A, a_panel_rows, ceil_div(cols, PANEL_W), a_mn ? GEMM_BLOCK_K : GEMM_BLOCK_M)) return e;
+    if (int e = (!b_mn ? make_tmap(&tb, B, K, N, ldb, BN / ctas) : make_tmap(&tb, B, N, K, ldb, GEMM_BLOCK_K))) return e;
+    if (int e = dispatch<EPI_STORE, false, true>(a_mn ? 1 : 0, b_mn ? 1 : 0, ctas, ta, tb, p, st)) return e;
+  } else {
+    if (int e = make_ab_maps(&ta, &tb, A, lda, a_mn, B, ldb, b_mn, M, N, K, ctas)) return e;
+    if (int e = dispatch<EPI_STORE>(a_mn ? 1 : 0, b_mn ? 1 : 0, ctas, ta, tb, p, st)) return e;
+  }
   if (ks > 1) {
     const long long quads = (long long)M * (N / 4);
     long long grid = (quads + 255) / 256;
@@ -299,7 +338,14 @@ static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B,
 
 using namespace b200grpo;
 
-static size_t dlogits_ld(int Vloc) { return align_up((size_t)Vloc, 64); }
+static size_t panel_bytes(int M, int Vloc) { return align_up((size_t)ceil_div(Vloc, PANEL_W) * M * PANEL_W * 2, 256); }
+// zero the last panel when the vocab is not a multiple of 256: its unwritten tail columns are K-padding of dH
+static int clear_tail_panel(void* panels, int M, int Vloc, cudaStream_t st) {
+  if (Vloc % PANEL_W == 0) return 0;
+  const size_t one = (size_t)M * PANEL_W * 2;
+  B200_CUDA_OK(cudaMemsetAsync((char*)panels + (size_t)(ceil_div(Vloc, PANEL_W) - 1) * one, 0, one, st));
+  return 0;
+}
 static size_t part_bytes(int M, int Vloc) { return align_up((size_t)ceil_div(Vloc, BN) * M * 16, 256); }
 
 extern "C" size_t b200grpo_lmhead_fwd_workspace(int M, int H, int Vloc) {
@@ -310,7 +356,7 @@ extern "C" size_t b200grpo_lmhead_fwd_workspace(int M, int H, int Vloc) {
 // saved-forward state for the recompute-free backward: [per-tile partials][bf16 logits relative to the tile max]
 extern "C" size_t b200grpo_lmhead_saved_bytes(int M, int H, int Vloc) {
   (void)H;
-  return part_bytes(M, Vloc) + align_up((size_t)M * dlogits_ld(Vloc) * 2, 256);
+  return part_bytes(M, Vloc) + panel_bytes(M, Vloc);
 }
 
 extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
@@ -323,15 +369,18 @@ extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* 
   B200_REQUIRE(!saved || ((uintptr_t)saved & 255) == 0, "lmhead_fwd: saved buffer must be 256-byte aligned");
   const int ctas = ctas_for(M);
   GemmParams p = {};
-  fill_tiling(p, M, Vloc, H, ctas, 0, 1);
+  fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_GROUP_M), 1);
   const size_t need = part_bytes(M, Vloc);
   if (!saved && workspace_bytes < need) { set_error("lmhead_fwd: workspace %zu < %zu", workspace_bytes, need); return B200GRPO_EWORKSPACE; }
   p.targets = (const long long*)targets; p.v_offset = v_offset; p.inv_temp = inv_temperature;
   p.part = (float*)(saved ? saved : workspace);
-  if (saved) { p.zsave = (__nv_bfloat16*)((char*)saved + need); p.ldz = (long long)dlogits_ld(Vloc); }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (saved) {
+    p.zsave = (__nv_bfloat16*)((char*)saved + need);
+    if (int e = clear_tail_panel(p.zsave, M, Vloc, st)) return e;
+  }
   CUtensorMap ta, tb;
   if (int e = make_ab_maps(&ta, &tb, hidden, ldh, 0, weight, ldw, 0, M, Vloc, H, ctas)) return e;
-  cudaStream_t st = (cudaStream_t)stream;
   {
     ProfScope ps(PROF_FWD_GEMM, st);
     const int e = saved ? dispatch<EPI_FWD_STATS, true>(0, 0, ctas, ta, tb, p, st) : dispatch<EPI_FWD_STATS, false>(0, 0, ctas, ta, tb, p, st);
@@ -355,7 +404,7 @@ extern "C" int b200grpo_lmhead_finalize(const float* stats, int R, int M, float*
 extern "C" size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc, int with_saved) {
   const int ctas = ctas_for(M);
   const size_t slab = store_gemm_slab_bytes(M, H, Vloc, ctas, get_tunable(TUNE_DH_KSPLIT));
-  return (with_saved ? 0 : align_up((size_t)M * dlogits_ld(Vloc) * 2, 256)) + slab + 256;
+  return (with_saved ? 0 : panel_bytes(M, Vloc)) + slab + 256;
 }
 
 extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
@@ -367,7 +416,6 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
   B200_REQUIRE(hidden && weight && targets && lse && entropy && coef_lp && coef_ent && workspace, "lmhead_bwd: null pointer");
   B200_REQUIRE(M >= 1 && H >= 8 && Vloc >= 1 && H % 8 == 0, "lmhead_bwd: M=%d H=%d Vloc=%d", M, H, Vloc);
   B200_REQUIRE(!accumulate || grad_weight_is_f32, "lmhead_bwd: accumulate needs an f32 grad_weight");
-  const size_t ldd = dlogits_ld(Vloc);
   const size_t need = b200grpo_lmhead_bwd_workspace(M, H, Vloc, saved != nullptr);
   if (workspace_bytes < need) { set_error("lmhead_bwd: workspace %zu < %zu", workspace_bytes, need); return B200GRPO_EWORKSPACE; }
   const int ctas = ctas_for(M);
@@ -378,18 +426,23 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
     dlog = (__nv_bfloat16*)((char*)saved + part_bytes(M, Vloc));
     slab = (char*)workspace;
     ProfScope ps(PROF_DLOGITS_EW, st);
-    dim3 grid(ceil_div(Vloc, DL_THREADS * 8), M < 32768 ? M : 32768);
-    dlogits_from_saved_kernel<<<grid, DL_THREADS, 0, st>>>(dlog, (long long)ldd, (const float4*)saved, M, Vloc, (const long long*)targets,
-                                                           v_offset, lse, entropy, coef_lp, coef_ent, grad_scale, inv_temperature);
+    const int n_blocks = ceil_div(Vloc, PANEL_W);
+    const long long per_block = (DL_THREADS / 32) * DL_ROWS;
+    long long grid = ((long long)n_blocks * M + per_block - 1) / per_block;
+    const long long cap = (long long)sm_count() * 32;
+    if (grid > cap) grid = cap;
+    dlogits_from_saved_kernel<<<(int)grid, DL_THREADS, 0, st>>>(dlog, (const float4*)saved, M, Vloc, n_blocks, (const long long*)targets,
+                                                                v_offset, lse, entropy, coef_lp, coef_ent, grad_scale, inv_temperature);
     B200_CUDA_OK(cudaGetLastError());
   } else {      // 1b. recompute logits tile by tile -> bf16 dlogits
     dlog = (__nv_bfloat16*)workspace;
-    slab = (char*)workspace + align_up((size_t)M * ldd * 2, 256);
+    slab = (char*)workspace + panel_bytes(M, Vloc);
+    if (int e = clear_tail_panel(dlog, M, Vloc, st)) return e;
     GemmParams p = {};
-    fill_tiling(p, M, Vloc, H, ctas, 0, 1);
+    fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_GROUP_M), 1);
     p.targets = (const long long*)targets; p.v_offset = v_offset; p.inv_temp = inv_temperature;
     p.lse = lse; p.entropy = entropy; p.coef_lp = coef_lp; p.coef_ent = coef_ent; p.grad_scale = grad_scale;
-    p.dlogits = dlog; p.ldd = (long long)ldd;
+    p.dlogits = dlog;
     CUtensorMap ta, tb;
     if (int e = make_ab_maps(&ta, &tb, hidden, ldh, 0, weight, ldw, 0, M, Vloc, H, ctas)) return e;
     ProfScope ps(PROF_BWD_DLOGITS, st);
@@ -398,13 +451,13 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
   const size_t slab_bytes = (char*)workspace + workspace_bytes - slab;
   if (grad_hidden) {  // 2. dH[M,H] = dlogits[M,V] . W[V,H]   (B is MN-major: vocab rows are the K axis)
     ProfScope ps(PROF_BWD_DH, st);
-    if (int e = run_store_gemm(dlog, (long long)ldd, 0, weight, ldw, 1, grad_hidden, ldgh, 0, 0, M, H, Vloc, ctas,
-                               get_tunable(TUNE_DH_GROUP_M), get_tunable(TUNE_DH_KSPLIT), slab, slab_bytes, st)) return e;
+    if (int e = run_store_gemm(dlog, 0, 0, weight, ldw, 1, grad_hidden, ldgh, 0, 0, M, H, Vloc, ctas,
+                               get_tunable(TUNE_DH_GROUP_M), get_tunable(TUNE_DH_KSPLIT), slab, slab_bytes, st, M)) return e;
   }
   if (grad_weight) {  // 3. dW[V,H] = dlogits^T[V,M] . hidden[M,H]   (both operands MN-major: tokens are the K axis)
     ProfScope ps(PROF_BWD_DW, st);
-    if (int e = run_store_gemm(dlog, (long long)ldd, 1, hidden, ldh, 1, grad_weight, ldgw, grad_weight_is_f32, accumulate, Vloc, H, M,
-                               ctas, get_tunable(TUNE_DW_GROUP_M), 1, nullptr, 0, st)) return e;
+    if (int e = run_store_gemm(dlog, 0, 1, hidden, ldh, 1, grad_weight, ldgw, grad_weight_is_f32, accumulate, Vloc, H, M,
+                               ctas, get_tunable(TUNE_DW_GROUP_M), 1, nullptr, 0, st, M)) return e;
   }
   return B200GRPO_OK;
 }

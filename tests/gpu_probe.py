@@ -112,6 +112,114 @@ def probe_gemm_splitk(two_cta, M, N, K, ks, group_m):
     return e1 < 1e-2 and e2 < 1e-4, f"bf16 rel={e1:.3e} f32-accumulate rel={e2:.3e}"
 
 
+def probe_gemm_speed(two_cta, M, N, K, group_m, ks):
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", two_cta)
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = torch.randn(N, K, device="cuda").bfloat16()
+    At, Bt = A.t().contiguous(), B.t().contiguous()
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    res = []
+    for a_mn in (0, 1):
+        for b_mn in (0, 1):
+            Ain, Bin = (At if a_mn else A), (Bt if b_mn else B)
+            for _ in range(2):
+                ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out=out, group_m=group_m, k_splits=ks)
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
+            for _ in range(3):
+                ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out=out, group_m=group_m, k_splits=ks)
+            t1.record(); torch.cuda.synchronize()
+            ms = t0.elapsed_time(t1) / 3
+            res.append(f"a{a_mn}b{b_mn} {ms:.3f}ms {2 * M * N * K / ms / 1e9:.0f}TF")
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(2):
+        torch.matmul(A, Bt, out=out)
+    t0.record()
+    for _ in range(3):
+        torch.matmul(A, Bt, out=out)
+    t1.record(); torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1) / 3
+    res.append(f"cublas {ms:.3f}ms {2 * M * N * K / ms / 1e9:.0f}TF")
+    return True, " | ".join(res)
+
+
+def probe_sustained(two_cta, M, N, K, group_m, ks, secs=1.5):
+    """ours (a0b0 / a1b1) vs cuBLAS back to back for `secs` each: power-capped steady state."""
+    import subprocess
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", two_cta)
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = torch.randn(N, K, device="cuda").bfloat16()
+    At, Bt = A.t().contiguous(), B.t().contiguous()
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+
+    def clocks():
+        try:
+            r = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,power.draw", "--format=csv,noheader,nounits"],
+                               capture_output=True, text=True, timeout=10).stdout.strip().split(",")
+            return f"{r[0].strip()}MHz/{float(r[1]):.0f}W"
+        except Exception:  # noqa: BLE001
+            return "?"
+
+    def run(fn, name):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        n, t_start = 0, time.time()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        # warm into the power cap, then time the second half
+        while time.time() - t_start < secs * 0.5:
+            for _ in range(10):
+                fn()
+            torch.cuda.synchronize()
+        t0.record()
+        t_mid = time.time()
+        ck = ""
+        while time.time() - t_mid < secs * 0.5:
+            for _ in range(10):
+                fn()
+            n += 10
+            if not ck:
+                ck = clocks()
+            torch.cuda.synchronize()
+        t1.record(); torch.cuda.synchronize()
+        ms = t0.elapsed_time(t1) / n
+        return f"{name} {ms:.3f}ms {2 * M * N * K / ms / 1e9:.0f}TF @{ck}"
+
+    res = [run(lambda: ops.gemm_bf16(A, B, out=out, group_m=group_m, k_splits=ks), "a0b0"),
+           run(lambda: torch.matmul(A, Bt, out=out), "cublas"),
+           run(lambda: ops.gemm_bf16(At, Bt, a_mn_major=True, b_mn_major=True, out=out, group_m=group_m, k_splits=ks), "a1b1"),
+           run(lambda: torch.matmul(At.t(), Bt, out=out), "cublas_nn")]
+    return True, " | ".join(res)
+
+
+def probe_raster_sweep(which):
+    """One launch per (group_m, k_splits) config, meant to run under `ncu --metrics dram__bytes_read.sum,...`."""
+    from pipelinerl_swe_b200 import ops
+    if which == "dh":      # dH shape: A = dlogits [M,V] K-major, B = W [V,H] MN-major
+        M, N, K, b_mn = 8192, 3584, 152064, True
+        cfgs = [(8, 6), (8, 1), (4, 4), (16, 4), (32, 1), (2, 6), (1, 6), (8, 12)]
+    elif which == "dw":    # dW shape: both MN-major
+        M, N, K, b_mn = 152064, 3584, 8192, True
+        cfgs = [(1, 1), (2, 1), (4, 1), (8, 1), (0, 1)]
+    else:                  # fwd shape
+        M, N, K, b_mn = 8192, 152064, 3584, False
+        cfgs = [(0, 1), (16, 1), (8, 1), (4, 1)]
+    a_mn = which == "dw"
+    A = torch.randn(K if a_mn else M, M if a_mn else K, device="cuda").bfloat16()
+    B = torch.randn(K if b_mn else N, N if b_mn else K, device="cuda").bfloat16()
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    res = []
+    for g, ks in cfgs:
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        ops.gemm_bf16(A, B, a_mn_major=a_mn, b_mn_major=b_mn, out=out, group_m=g, k_splits=ks)
+        t1.record(); torch.cuda.synchronize()
+        res.append(f"g{g}/ks{ks}:{t0.elapsed_time(t1):.2f}ms")
+    return True, " ".join(res)
+
+
 def probe_speed(two_cta, M, H, V):
     from pipelinerl_swe_b200 import _abi, ops
     _abi.set_tunable("two_cta", two_cta)
@@ -176,6 +284,18 @@ for ctas in (0, 1):
     PROBES[f"bwdsaved_small_c{ctas + 1}"] = (probe_bwd_saved, (ctas, 300, 128, 1000, 0.7))
     PROBES[f"bwdsaved_mid_c{ctas + 1}"] = (probe_bwd_saved, (ctas, 1023, 512, 9000 + 8, 1.0))
     PROBES[f"gemm_splitk_c{ctas + 1}"] = (probe_gemm_splitk, (ctas, 1000, 776, 9000, 3, 2))
+    PROBES[f"gspeed_dh_c{ctas + 1}"] = (probe_gemm_speed, (ctas, 8192, 3584, 152064, 8, 4))
+    PROBES[f"gspeed_dh_nosplit_c{ctas + 1}"] = (probe_gemm_speed, (ctas, 8192, 3584, 152064, 8, 1))
+    PROBES[f"gspeed_dw_c{ctas + 1}"] = (probe_gemm_speed, (ctas, 152064, 3584, 8192, 1, 1))
+    PROBES[f"gspeed_dw_g4_c{ctas + 1}"] = (probe_gemm_speed, (ctas, 152064, 3584, 8192, 4, 1))
+    PROBES[f"gspeed_fwd_c{ctas + 1}"] = (probe_gemm_speed, (ctas, 8192, 152064, 3584, 0, 1))
+    PROBES[f"sweep_dh"] = (probe_raster_sweep, ("dh",))
+    PROBES[f"sweep_dw"] = (probe_raster_sweep, ("dw",))
+    PROBES[f"sweep_fwd"] = (probe_raster_sweep, ("fwd",))
+    PROBES[f"sust_fwd_c{ctas + 1}"] = (probe_sustained, (ctas, 8192, 152064, 3584, 0, 1))
+    PROBES[f"sust_dw_c{ctas + 1}"] = (probe_sustained, (ctas, 152064, 3584, 8192, 1, 1))
+    PROBES[f"sust_dh_c{ctas + 1}"] = (probe_sustained, (ctas, 8192, 3584, 152064, 8, 4))
+    PROBES[f"sust_sq_c{ctas + 1}"] = (probe_sustained, (ctas, 8192, 8192, 8192, 8, 1))
     PROBES[f"speed_c2shape_c{ctas + 1}"] = (probe_speed, (ctas, 8192, 1536, 151936))
     PROBES[f"speed_c3shape_c{ctas + 1}"] = (probe_speed, (ctas, 8192, 3584, 152064))
 
