@@ -219,55 +219,60 @@ __global__ void __launch_bounds__(256) finalize_kernel(const float4* __restrict_
 // as bf16 in [n_blocks][M][256] panels; the tile max lives in part[nb][t].x.  HBM-bound: 4 B/element
 // (bf16 in + bf16 out), 16-byte vectors, 32 threads per panel row, fully contiguous traversal.
 constexpr int DL_THREADS = 256;
-constexpr int DL_ROWS = 4;   // panel rows per warp iteration: 4 independent 16-byte loads in flight per thread
+constexpr int DL_ROWS = 32;   // panel rows per block: 32 rows x 256 columns = 16 KB in, 16 KB out
 __global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
-    __nv_bfloat16* __restrict__ z, const float4* __restrict__ part, int M, int N, int n_blocks, const long long* __restrict__ targets,
+    __nv_bfloat16* __restrict__ z, const float4* __restrict__ part, int M, int N, const long long* __restrict__ targets,
     long long v_offset, const float* __restrict__ lse, const float* __restrict__ entropy, const float* __restrict__ coef_lp,
     const float* __restrict__ coef_ent, const float* __restrict__ grad_scale, float inv_temp) {
-  const float gs = (grad_scale ? *grad_scale : 1.0f) * inv_temp;
-  const int sub = threadIdx.x & 31;                      // 8 columns each: 32 threads cover one 256-wide panel row
-  const long long n_rows = (long long)n_blocks * M;      // panel rows in storage order
-  const long long warp0 = ((long long)blockIdx.x * (DL_THREADS / 32) + (threadIdx.x >> 5)) * DL_ROWS;
-  const long long stride = (long long)gridDim.x * (DL_THREADS / 32) * DL_ROWS;
-  for (long long base = warp0; base < n_rows; base += stride) {
-    uint4 raw[DL_ROWS];
-    float shift2[DL_ROWS], a[DL_ROWS], e[DL_ROWS], ent[DL_ROWS];
-    int tcol[DL_ROWS], nval[DL_ROWS];
-#pragma unroll
-    for (int r = 0; r < DL_ROWS; ++r) {
-      const long long pr = base + r;
-      nval[r] = 0;
-      if (pr >= n_rows) continue;
-      const int nb = (int)(pr / M), row = (int)(pr - (long long)nb * M);
-      const int col = nb * PANEL_W + sub * 8;
-      if (col >= N) continue;                            // tail columns stay zero
-      nval[r] = min(8, N - col);
-      raw[r] = *reinterpret_cast<const uint4*>(z + pr * PANEL_W + sub * 8);
-      a[r] = coef_lp[row] * gs; e[r] = coef_ent[row] * gs; ent[r] = entropy[row];
-      shift2[r] = (__ldg(&part[pr]).x - lse[row]) * LOG2E_F;   // (tile max - lse) * log2 e
-      const long long tl = targets[row] - v_offset;
-      tcol[r] = (tl >= col && tl < col + 8) ? (int)(tl - col) : -1;
+  __shared__ float s_a[DL_ROWS], s_e[DL_ROWS], s_ent[DL_ROWS], s_shift[DL_ROWS];
+  __shared__ int s_t[DL_ROWS];
+  const int nb = blockIdx.y, row0 = blockIdx.x * DL_ROWS;
+  if (threadIdx.x < DL_ROWS) {   // per-row constants, loaded once per block
+    const int row = row0 + threadIdx.x;
+    if (row < M) {
+      const float gs = (grad_scale ? *grad_scale : 1.0f) * inv_temp;
+      s_a[threadIdx.x] = coef_lp[row] * gs;
+      s_e[threadIdx.x] = coef_ent[row] * gs;
+      s_ent[threadIdx.x] = entropy[row];
+      s_shift[threadIdx.x] = (__ldg(&part[(long long)nb * M + row]).x - lse[row]) * LOG2E_F;  // (tile max - lse) * log2 e
+      const long long tl = targets[row] - v_offset - (long long)nb * PANEL_W;
+      s_t[threadIdx.x] = (tl >= 0 && tl < PANEL_W) ? (int)tl : -1000;
     }
+  }
+  __syncthreads();
+  const int sub = threadIdx.x & 31, wr = threadIdx.x >> 5;   // 8 columns per thread; warp = one panel row
+  const int col = nb * PANEL_W + sub * 8;
+  if (col >= N) return;                                      // tail columns stay zero
+  const int n_valid = min(8, N - col);
+  __nv_bfloat16* base = z + ((long long)nb * M + row0) * PANEL_W + sub * 8;
+  uint4 raw[DL_ROWS / 8];
 #pragma unroll
-    for (int r = 0; r < DL_ROWS; ++r) {
-      if (nval[r] == 0) continue;
-      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw[r]);
+  for (int j = 0; j < DL_ROWS / 8; ++j) {                    // 4 independent 16-byte loads in flight
+    const int r = wr + 8 * j;
+    if (row0 + r < M) raw[j] = *reinterpret_cast<const uint4*>(base + (long long)r * PANEL_W);
+  }
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const float2 y = __bfloat1622float2(h[q]);
-        float d[2];
+  for (int j = 0; j < DL_ROWS / 8; ++j) {
+    const int r = wr + 8 * j;
+    if (row0 + r >= M) continue;
+    const float a = s_a[r], e = s_e[r], ent = s_ent[r], shift2 = s_shift[r];
+    const int t = s_t[r] - sub * 8;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw[j]);
 #pragma unroll
-        for (int w = 0; w < 2; ++w) {
-          const float y2 = fmaf(w ? y.y : y.x, LOG2E_F, shift2[r]);   // log2 p
-          const float pr_ = fast_exp2(y2);
-          float g = -pr_ * fmaf(e[r], fmaf(y2, LN2_F, ent[r]), a[r]);  // -p * (a + e*(logp + H))
-          if (2 * q + w == tcol[r]) g += a[r];
-          d[w] = (2 * q + w < nval[r]) ? g : 0.f;
-        }
-        h[q] = __floats2bfloat162_rn(d[0], d[1]);
+    for (int q = 0; q < 4; ++q) {
+      const float2 y = __bfloat1622float2(h[q]);
+      float d[2];
+#pragma unroll
+      for (int w = 0; w < 2; ++w) {
+        const float y2 = fmaf(w ? y.y : y.x, LOG2E_F, shift2);   // log2 p
+        const float pr = fast_exp2(y2);
+        float g = -pr * fmaf(e, fmaf(y2, LN2_F, ent), a);        // -p * (a + e*(logp + H))
+        if (2 * q + w == t) g += a;
+        d[w] = (2 * q + w < n_valid) ? g : 0.f;
       }
-      *reinterpret_cast<uint4*>(z + (base + r) * PANEL_W + sub * 8) = raw[r];
+      h[q] = __floats2bfloat162_rn(d[0], d[1]);
     }
+    *reinterpret_cast<uint4*>(base + (long long)r * PANEL_W) = raw[j];
   }
 }
 
@@ -426,13 +431,9 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
     dlog = (__nv_bfloat16*)((char*)saved + part_bytes(M, Vloc));
     slab = (char*)workspace;
     ProfScope ps(PROF_DLOGITS_EW, st);
-    const int n_blocks = ceil_div(Vloc, PANEL_W);
-    const long long per_block = (DL_THREADS / 32) * DL_ROWS;
-    long long grid = ((long long)n_blocks * M + per_block - 1) / per_block;
-    const long long cap = (long long)sm_count() * 32;
-    if (grid > cap) grid = cap;
-    dlogits_from_saved_kernel<<<(int)grid, DL_THREADS, 0, st>>>(dlog, (const float4*)saved, M, Vloc, n_blocks, (const long long*)targets,
-                                                                v_offset, lse, entropy, coef_lp, coef_ent, grad_scale, inv_temperature);
+    dim3 grid(ceil_div(M, DL_ROWS), ceil_div(Vloc, PANEL_W));
+    dlogits_from_saved_kernel<<<grid, DL_THREADS, 0, st>>>(dlog, (const float4*)saved, M, Vloc, (const long long*)targets, v_offset, lse,
+                                                           entropy, coef_lp, coef_ent, grad_scale, inv_temperature);
     B200_CUDA_OK(cudaGetLastError());
   } else {      // 1b. recompute logits tile by tile -> bf16 dlogits
     dlog = (__nv_bfloat16*)workspace;

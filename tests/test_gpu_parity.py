@@ -86,9 +86,11 @@ def test_rl_step_vs_reference_golden(name):
 # ---------------------------------------------------------------------------------------------
 # K1 / K2 at the real vocab size vs the oracle (fp32 math on the same bf16 values)
 # ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("save", [False, True])
 @pytest.mark.parametrize("two_cta", [0, 1])
-@pytest.mark.parametrize("T,H,V,temp", [(513, 896, 151936, 1.0), (300, 1536, 152064, 0.7)])
-def test_lmhead_fwd_bwd_vs_oracle(T, H, V, temp, two_cta):
+@pytest.mark.parametrize("T,H,V,temp", [(513, 896, 151936, 1.0), (300, 1536, 152064, 0.7), (260, 256, 1000 + 8, 1.3)])
+def test_lmhead_fwd_bwd_vs_oracle(T, H, V, temp, two_cta, save):
+    """save=False: backward recomputes the logits; save=True: forward keeps bf16 logits (tile-max relative)."""
     from pipelinerl_swe_b200 import _abi, ops
     _abi.set_tunable("two_cta", two_cta)
     try:
@@ -104,11 +106,12 @@ def test_lmhead_fwd_bwd_vs_oracle(T, H, V, temp, two_cta):
 
         d = _dev()
         h, w, tgt = hidden[:-1].contiguous().to(d), weight.to(d), ids[1:].contiguous().to(d)
-        stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp)
+        saved = ops.lmhead_saved_buffer(T - 1, H, V, d) if save else None
+        stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp, saved=saved)
         lp, ent, lse = ops.lmhead_finalize(stats)
-        assert float((lp.cpu() - lp_ref.detach()).abs().max()) <= LP_RTOL * float(lp_ref.abs().max())
-        assert float((ent.cpu() - ent_ref.detach()).abs().max()) <= LP_RTOL * float(ent_ref.abs().max())
-        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp.to(d), c_ent.to(d), 1.0 / temp)
+        assert float((lp.cpu() - lp_ref.detach()).abs().max()) <= LP_RTOL * float(lp_ref.detach().abs().max())
+        assert float((ent.cpu() - ent_ref.detach()).abs().max()) <= LP_RTOL * float(ent_ref.detach().abs().max())
+        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp.to(d), c_ent.to(d), 1.0 / temp, saved=saved)
         assert _rel(gh, hr.grad[:-1]) < GRAD_RTOL
         assert _rel(gw, wr.grad) < GRAD_RTOL
     finally:
@@ -175,3 +178,43 @@ def test_lmhead_properties_full_size():
     onehot = (tgt[:, None] == torch.arange(1000, 1256, device=d)[None]).float()
     dl = c[:, None] * (onehot - p)
     assert _rel(gw1[vs], dl.t() @ h.float()) < GRAD_RTOL
+
+
+def test_rl_step_recompute_mode_matches_saved_mode():
+    """set_save_logits(False): nothing of size tokens x vocab is kept between forward and backward."""
+    from pipelinerl_swe_b200 import RLConfig, rl_step
+    from pipelinerl_swe_b200.lm_head import set_save_logits
+    H, V, lens = 128, 3000, [70, 41, 90]
+    batch = synthetic_packed_batch(lens, V, seed=5)
+    cfg = RLConfig(policy_loss="ppo", batch_size=3, kl_coef=0.1, final_kl_coef=0.1, entropy_bonus=0.01, final_entropy_bonus=0.01)
+    grads = []
+    try:
+        for flag in (True, False):
+            set_save_logits(flag)
+            model = StubLM(H, V, sum(lens), seed=8).to(_dev())
+            loss, stats = rl_step(model, _to_dev(batch), 0, 1, cfg)
+            loss.backward()
+            grads.append((loss.item(), model.lm_head.weight.grad.float(), model.hidden.grad.float()))
+    finally:
+        set_save_logits(True)
+    assert grads[0][0] == grads[1][0]
+    assert _rel(grads[0][1], grads[1][1]) < 1e-2 and _rel(grads[0][2], grads[1][2]) < 1e-2
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1)])
+def test_gemm_splitk_and_raster(a_mn, b_mn):
+    from pipelinerl_swe_b200 import ops
+    d = _dev()
+    g = torch.Generator(device=d).manual_seed(1)
+    M, N, K = 777, 520, 9000
+    A = torch.randn(M, K, device=d, generator=g).bfloat16()
+    B = torch.randn(N, K, device=d, generator=g).bfloat16()
+    ref = A.float() @ B.float().t()
+    Ain = A.t().contiguous() if a_mn else A
+    Bin = B.t().contiguous() if b_mn else B
+    for group_m, ks in ((0, 1), (1, 1), (2, 3), (3, 5)):
+        out = ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), group_m=group_m, k_splits=ks)
+        assert _rel(out, ref) < 1e-4, (group_m, ks)
+        acc = torch.full((M, N), 2.0, device=d)
+        ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out=acc, accumulate=True, group_m=group_m, k_splits=ks)
+        assert _rel(acc, ref + 2.0) < 1e-4
