@@ -153,3 +153,16 @@ def test_plan_buckets():
         n = sum((int(np.prod(infos[i].shape)) + 7) // 8 * 8 for i in b)
         assert n <= cap or len(b) == 1
     assert plan_buckets(infos, 1 << 40) == [list(range(len(infos)))]
+
+
+def test_plan_transfers_covers_every_parameter_once():
+    from pipelinerl_swe_b200.weight_update import ParameterInfo, plan_transfers
+    infos = [ParameterInfo(name=f"p{i}", shape=s, dtype="torch.bfloat16") for i, s in
+             enumerate([[3584], [3584, 3584], [512, 3584], [152064, 3584], [18944, 3584], [7], [512]])]
+    plan = plan_transfers(infos, 64 << 20, direct_bytes=8 << 20)
+    seen = []
+    for kind, item in plan:
+        seen += item if kind == "bucket" else [item]
+    assert sorted(seen) == list(range(len(infos)))
+    assert ("direct", 1) in plan and ("direct", 3) in plan and ("direct", 4) in plan
+    assert [k for k, _ in plan].count("bucket") == 1 and plan[0] == ("bucket", [0, 2, 5, 6])

@@ -121,7 +121,7 @@ def main():
                 staging[0] = wu.receive_weight_update(request, None, load_weights, dev, bucket_bytes=mb << 20, staging=staging[0])
 
         ms = timed(run)
-        emit(f"bucketed_{mb}MB", ms, check(), {"bucket_MB": mb, "n_buckets": len(wu.plan_buckets(request.parameters_info, mb << 20))})
+        emit(f"bucketed_{mb}MB", ms, check(), {"bucket_MB": mb, "n_broadcasts": len(wu.plan_transfers(request.parameters_info, mb << 20))})
         staging[0] = None
         torch.cuda.empty_cache()
     dist.destroy_process_group()
