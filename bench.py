@@ -307,6 +307,7 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep rank 0's stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     _abi.set_tunable("save_logits", 0 if args.mode == "recompute" else 1)
 
