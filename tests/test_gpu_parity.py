@@ -206,7 +206,7 @@ def test_gemm_splitk_and_raster(a_mn, b_mn):
     from pipelinerl_swe_b200 import ops
     d = _dev()
     g = torch.Generator(device=d).manual_seed(1)
-    M, N, K = 777, 520, 9000
+    M, N, K = (776 if a_mn else 777), 520, 9000  # MN-major operands need a 16-byte aligned row pitch (TMA)
     A = torch.randn(M, K, device=d, generator=g).bfloat16()
     B = torch.randn(N, K, device=d, generator=g).bfloat16()
     ref = A.float() @ B.float().t()
