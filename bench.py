@@ -54,6 +54,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample-tokens", type=int, default=0, help="tokens per CPU-baseline call (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--tunable", action="append", default=[], metavar="NAME=VALUE", help="library tunable (experiments)")
     return ap.parse_args()
 
 
@@ -315,6 +316,9 @@ def run_b200(args):
         os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep rank 0's stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     _abi.set_tunable("save_logits", 0 if args.mode == "recompute" else 1)
+    for kv in args.tunable:
+        name, val = kv.split("=")
+        _abi.set_tunable(name, int(val))
 
     wl = DeviceWorkload(args, dev, rank, world)
     H, V, T = wl.H, wl.V, wl.T
@@ -427,7 +431,7 @@ def run_b200(args):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": wl.desc, "H": H, "V": V, "T": T, "parallelism": ("vocab" if wl.vocab_parallel else "dp") + str(world),
                        "grad_weight": "f32 accumulated across steps", "l2": "inputs exceed L2 (lm_head weight %.2f GB)" % (wl.weight.numel() * 2 / 1e9),
-                       "bwd_mode": args.mode, "tokens_per_gpu_per_sec": value / world if not wl.vocab_parallel else value},
+                       "bwd_mode": args.mode, "tunables": args.tunable, "tokens_per_gpu_per_sec": value / world if not wl.vocab_parallel else value},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(round(launches_per_step * K)),
             "gpu_launches_per_step": launches_per_step, "clocks": clocks.summary(),
         }

@@ -42,7 +42,8 @@ constexpr int PANEL_W = 256;        // saved logits / dlogits are stored in [M x
 
 struct GemmParams {
   int M, N, K;
-  int m_blocks, n_blocks, k_splits, group_m, kb_total;
+  int m_blocks, n_blocks, k_splits, group_m, group_n, kb_total;
+  unsigned long long hint_a, hint_b;   // L2 eviction policy of the A / B operand loads
   // EPI_STORE
   void* C;
   long long ldc;
@@ -58,10 +59,10 @@ struct GemmParams {
   __nv_bfloat16* dlogits;   // panels [n_blocks][M][256]
 };
 
-template <int BLOCK_N, int kCtas, int kStages>
+template <int BLOCK_N, int kCtas, int kStages, int kMRep = 1>
 struct GemmSmem {
   static constexpr int LOAD_N = BLOCK_N / kCtas;
-  static constexpr int A_BYTES = GEMM_BLOCK_M * GEMM_BLOCK_K * 2;
+  static constexpr int A_BYTES = GEMM_BLOCK_M * kMRep * GEMM_BLOCK_K * 2;
   static constexpr int B_BYTES = LOAD_N * GEMM_BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_OFFSET = kStages * STAGE_BYTES;
@@ -71,16 +72,24 @@ struct GemmSmem {
 struct Item { int m_blk, nb, ks, kb0, kb1; };
 
 __device__ __forceinline__ Item decode_item(const GemmParams& p, int item) {
+  // order: k-split (slowest) > column group of group_n tile columns > row group of group_m tile rows >
+  //        tile column inside the group > tile row (fastest)
   Item it;
   const int tiles = p.m_blocks * p.n_blocks;
   it.ks = item / tiles;
-  const int t = item - it.ks * tiles;
-  const int per_group = p.group_m * p.n_blocks;
+  int t = item - it.ks * tiles;
+  const int per_ngroup = p.m_blocks * p.group_n;
+  const int ng = t / per_ngroup;
+  t -= ng * per_ngroup;
+  const int n_first = ng * p.group_n;
+  const int gn = min(p.group_n, p.n_blocks - n_first);
+  const int per_group = p.group_m * gn;
   const int g = t / per_group, w = t - g * per_group;
   const int m_first = g * p.group_m;
   const int gm = min(p.group_m, p.m_blocks - m_first);
-  it.nb = w / gm;
-  it.m_blk = m_first + (w - it.nb * gm);
+  const int nb_local = w / gm;
+  it.nb = n_first + nb_local;
+  it.m_blk = m_first + (w - nb_local * gm);
   it.kb0 = (int)((long long)it.ks * p.kb_total / p.k_splits);
   it.kb1 = (int)((long long)(it.ks + 1) * p.kb_total / p.k_splits);
   return it;
@@ -240,18 +249,26 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t 
 }
 
 // ---------------------------------------------------------------------------------------
-// The kernel
+// The kernel.  kMRep = 1: 128 rows per CTA, two accumulator stages (epilogue overlaps the next
+// tile's MMAs).  kMRep = 2: 256 rows per CTA = two 128-row MMAs per k-step that share one B tile
+// in shared memory (25 % fewer operand bytes per FLOP from L2), one accumulator stage (all 512
+// TMEM columns); used where the K loop is long enough to make the un-overlapped epilogue cheap.
 // ---------------------------------------------------------------------------------------
-template <int kEpi, int kAMajor, int kBMajor, int kCtas, int BLOCK_N, int kStages, bool kSave = false, bool kAPanel = false>
+template <int kEpi, int kAMajor, int kBMajor, int kCtas, int BLOCK_N, int kStages, bool kSave = false, bool kAPanel = false,
+          int kMRep = 1>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, const GemmParams p) {
-  using L = GemmSmem<BLOCK_N, kCtas, kStages>;
+  using L = GemmSmem<BLOCK_N, kCtas, kStages, kMRep>;
   constexpr int LOAD_N = L::LOAD_N;
+  constexpr int CTA_M = GEMM_BLOCK_M * kMRep;                // rows of the output tile owned by one CTA
   constexpr int UMMA_M = GEMM_BLOCK_M * kCtas;
-  constexpr uint32_t TMEM_COLS = 2 * BLOCK_N <= 32 ? 32 : 2 * BLOCK_N <= 64 ? 64 : 2 * BLOCK_N <= 128 ? 128 : 2 * BLOCK_N <= 256 ? 256 : 512;
-  static_assert(2 * BLOCK_N <= 512, "two accumulator stages must fit the 512 TMEM columns");
+  constexpr int ACC_COLS = BLOCK_N * kMRep;                  // TMEM columns of one accumulator stage
+  constexpr int ACC_STAGES = 512 / ACC_COLS >= 2 ? 2 : 1;
+  constexpr uint32_t TMEM_COLS = ACC_STAGES * ACC_COLS <= 32 ? 32 : ACC_STAGES * ACC_COLS <= 64 ? 64 : ACC_STAGES * ACC_COLS <= 128 ? 128
+                                 : ACC_STAGES * ACC_COLS <= 256 ? 256 : 512;
+  static_assert(ACC_STAGES * ACC_COLS <= 512, "accumulators must fit the 512 TMEM columns");
   static_assert(BLOCK_N % 32 == 0 && LOAD_N % 64 == 0, "tile shape");
-  static_assert(kBMajor == MAJOR_K || LOAD_N % 64 == 0, "MN-major B is loaded in 64-wide atoms");
+  static_assert(kMRep == 1 || kMRep == 2, "one or two 128-row MMAs per CTA");
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t pad = (1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u;
@@ -289,7 +306,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     uint32_t stage = 0, phase = 0;
     for (int item = cluster_id; item < n_items; item += n_clusters) {
       const Item it = decode_item(p, item);
-      const int m0 = (it.m_blk * kCtas + (int)cta_rank) * GEMM_BLOCK_M;
+      const int m0 = (it.m_blk * kCtas + (int)cta_rank) * CTA_M;
       const int n0 = it.nb * BLOCK_N + (int)cta_rank * LOAD_N;
       for (int kb = it.kb0; kb < it.kb1; ++kb) {
         ptx::mbar_wait(&empty_bar[stage], phase ^ 1, 1);
@@ -299,26 +316,27 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
         const int k0 = kb * GEMM_BLOCK_K;
         auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
-          if constexpr (kCtas == 1) ptx::tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
-          else ptx::tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
+          const uint64_t pol = tm == &tm_a ? p.hint_a : p.hint_b;
+          if constexpr (kCtas == 1) ptx::tma_load_2d_hint(dst, tm, &full_bar[stage], c0, c1, pol);
+          else ptx::tma_load_2d_pair_hint(dst, tm, &full_bar[stage], c0, c1, pol);
         };
         auto load3 = [&](void* dst, const CUtensorMap* tm, int c0, int c1, int c2) {
-          if constexpr (kCtas == 1) ptx::tma_load_3d(dst, tm, &full_bar[stage], c0, c1, c2);
-          else ptx::tma_load_3d_pair(dst, tm, &full_bar[stage], c0, c1, c2);
+          if constexpr (kCtas == 1) ptx::tma_load_3d_hint(dst, tm, &full_bar[stage], c0, c1, c2, p.hint_a);
+          else ptx::tma_load_3d_pair_hint(dst, tm, &full_bar[stage], c0, c1, c2, p.hint_a);
         };
         if constexpr (kAPanel) {  // A lives in 256-column panels: element (r, c) at panel c/256, row r, column c%256
           if constexpr (kAMajor == MAJOR_K) {
-            load3(sa, &tm_a, k0 % PANEL_W, m0, k0 / PANEL_W);        // box {64 k, 128 rows, 1}
+            load3(sa, &tm_a, k0 % PANEL_W, m0, k0 / PANEL_W);        // box {64 k, CTA_M rows, 1}
           } else {
 #pragma unroll
-            for (int a = 0; a < GEMM_BLOCK_M / 64; ++a)
+            for (int a = 0; a < CTA_M / 64; ++a)
               load3(sa + a * 8192, &tm_a, (m0 + a * 64) % PANEL_W, k0, (m0 + a * 64) / PANEL_W);  // box {64 m, 64 k, 1}
           }
         } else if constexpr (kAMajor == MAJOR_K) {
-          load(sa, &tm_a, k0, m0);                                   // box {64 k, 128 rows}
+          load(sa, &tm_a, k0, m0);                                   // box {64 k, CTA_M rows}
         } else {
 #pragma unroll
-          for (int a = 0; a < GEMM_BLOCK_M / 64; ++a) load(sa + a * 8192, &tm_a, m0 + a * 64, k0);  // box {64 m, 64 k}
+          for (int a = 0; a < CTA_M / 64; ++a) load(sa + a * 8192, &tm_a, m0 + a * 64, k0);  // box {64 m, 64 k}
         }
         if constexpr (kBMajor == MAJOR_K) {
           load(sb, &tm_b, k0, n0);                                   // box {64 k, LOAD_N rows}
@@ -335,21 +353,26 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     constexpr uint32_t A_LBO = kAMajor == MAJOR_K ? 0 : GEMM_BLOCK_K * 128, B_LBO = kBMajor == MAJOR_K ? 0 : GEMM_BLOCK_K * 128;
     constexpr uint32_t A_KSTEP = (kAMajor == MAJOR_K ? GEMM_UMMA_K * 2 : GEMM_UMMA_K * 128) >> 4;
     constexpr uint32_t B_KSTEP = (kBMajor == MAJOR_K ? GEMM_UMMA_K * 2 : GEMM_UMMA_K * 128) >> 4;
+    constexpr uint32_t A_REP = (GEMM_BLOCK_M * GEMM_BLOCK_K * 2) >> 4;   // the second 128 rows start 16 KB further (both layouts)
     uint32_t stage = 0, phase = 0, tile_iter = 0;
     for (int item = cluster_id; item < n_items; item += n_clusters, ++tile_iter) {
       const Item it = decode_item(p, item);
-      const uint32_t as = tile_iter & 1, aphase = (tile_iter >> 1) & 1;
+      const uint32_t as = tile_iter % ACC_STAGES, aphase = (tile_iter / ACC_STAGES) & 1;
       ptx::mbar_wait(&tmem_empty[as], aphase ^ 1, 2);
       ptx::tc_fence_after();
-      const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+      const uint32_t d_tmem = tmem_base + as * ACC_COLS;
       for (int kb = it.kb0; kb < it.kb1; ++kb) {
         ptx::mbar_wait(&full_bar[stage], phase, 3);
         ptx::tc_fence_after();
         const uint32_t sa = ptx::smem_u32(smem + stage * L::STAGE_BYTES), sb = sa + L::A_BYTES;
         const uint64_t da = ptx::smem_desc_sw128(sa, A_LBO, 1024), db = ptx::smem_desc_sw128(sb, B_LBO, 1024);
 #pragma unroll
-        for (int k = 0; k < GEMM_BLOCK_K / GEMM_UMMA_K; ++k)
-          ptx::umma_bf16<kCtas>(d_tmem, da + (uint64_t)(k * A_KSTEP), db + (uint64_t)(k * B_KSTEP), idesc, (kb > it.kb0) || (k != 0));
+        for (int k = 0; k < GEMM_BLOCK_K / GEMM_UMMA_K; ++k) {
+#pragma unroll
+          for (int rep = 0; rep < kMRep; ++rep)
+            ptx::umma_bf16<kCtas>(d_tmem + rep * BLOCK_N, da + (uint64_t)(k * A_KSTEP + rep * A_REP), db + (uint64_t)(k * B_KSTEP), idesc,
+                                  (kb > it.kb0) || (k != 0));
+        }
         ptx::umma_commit<kCtas>(&empty_bar[stage]);              // frees the smem slot when the MMAs retire
         if (kb == it.kb1 - 1) ptx::umma_commit<kCtas>(&tmem_full[as]);
         if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -357,8 +380,8 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     }
     if (kCtas > 1 && tile_iter > 0) {  // drain: peer epilogue arrivals must land before teardown
       const uint32_t last = tile_iter - 1;
-      ptx::mbar_wait(&tmem_empty[last & 1], (last >> 1) & 1, 4);
-      if (tile_iter > 1) ptx::mbar_wait(&tmem_empty[(last - 1) & 1], ((last - 1) >> 1) & 1, 5);
+      ptx::mbar_wait(&tmem_empty[last % ACC_STAGES], (last / ACC_STAGES) & 1, 4);
+      if (ACC_STAGES > 1 && tile_iter > 1) ptx::mbar_wait(&tmem_empty[(last - 1) % ACC_STAGES], ((last - 1) / ACC_STAGES) & 1, 5);
     }
   } else if (warp >= GEMM_EPI_WARP0) {
     // ===================== epilogue (4 warps, thread == TMEM lane == tile row) ============
@@ -369,68 +392,75 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     uint32_t tile_iter = 0;
     for (int item = cluster_id; item < n_items; item += n_clusters, ++tile_iter) {
       const Item it = decode_item(p, item);
-      const int row = (it.m_blk * kCtas + (int)cta_rank) * GEMM_BLOCK_M + row_in_tile;
-      const bool row_ok = row < p.M;
       const int n0 = it.nb * BLOCK_N;
-      FwdRowState fs;
-      BwdRowConst bc;
-      if constexpr (kEpi == EPI_FWD_STATS) {
-        fs.m_raw = -INFINITY; fs.s = 0.f; fs.u = 0.f; fs.tgt = 0.f;
-        const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
-        fs.tcol = (t >= n0 && t < min(p.N, n0 + BLOCK_N)) ? (int)t : -1000000;
-      }
-      if constexpr (kEpi == EPI_BWD_DLOGITS) {
-        const float gs = (p.grad_scale ? *p.grad_scale : 1.0f) * p.inv_temp;
-        bc.lse2 = row_ok ? p.lse[row] * LOG2E_F : 0.f;
-        bc.a = row_ok ? p.coef_lp[row] * gs : 0.f;
-        bc.e = row_ok ? p.coef_ent[row] * gs : 0.f;
-        bc.ent = row_ok ? p.entropy[row] : 0.f;
-        const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
-        bc.tcol = (t >= 0 && t < p.N) ? (int)t : -1000000;
-      }
-      const uint32_t as = tile_iter & 1, aphase = (tile_iter >> 1) & 1;
-      ptx::mbar_wait(&tmem_full[as], aphase, 6);
-      ptx::tc_fence_after();
-      const uint32_t t_addr = tmem_base + lane_addr + as * BLOCK_N;
-      if constexpr (kEpi == EPI_FWD_STATS) {   // pass 1: tile max per row
+      const uint32_t as = tile_iter % ACC_STAGES, aphase = (tile_iter / ACC_STAGES) & 1;
+      bool waited = false;
+#pragma unroll 1
+      for (int rep = 0; rep < kMRep; ++rep) {
+        const int row = (it.m_blk * kCtas + (int)cta_rank) * CTA_M + rep * GEMM_BLOCK_M + row_in_tile;
+        const bool row_ok = row < p.M;
+        FwdRowState fs;
+        BwdRowConst bc;
+        if constexpr (kEpi == EPI_FWD_STATS) {
+          fs.m_raw = -INFINITY; fs.s = 0.f; fs.u = 0.f; fs.tgt = 0.f;
+          const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
+          fs.tcol = (t >= n0 && t < min(p.N, n0 + BLOCK_N)) ? (int)t : -1000000;
+        }
+        if constexpr (kEpi == EPI_BWD_DLOGITS) {
+          const float gs = (p.grad_scale ? *p.grad_scale : 1.0f) * p.inv_temp;
+          bc.lse2 = row_ok ? p.lse[row] * LOG2E_F : 0.f;
+          bc.a = row_ok ? p.coef_lp[row] * gs : 0.f;
+          bc.e = row_ok ? p.coef_ent[row] * gs : 0.f;
+          bc.ent = row_ok ? p.entropy[row] : 0.f;
+          const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
+          bc.tcol = (t >= 0 && t < p.N) ? (int)t : -1000000;
+        }
+        if (!waited) {
+          ptx::mbar_wait(&tmem_full[as], aphase, 6);
+          ptx::tc_fence_after();
+          waited = true;
+        }
+        const uint32_t t_addr = tmem_base + lane_addr + as * ACC_COLS + rep * BLOCK_N;
+        if constexpr (kEpi == EPI_FWD_STATS) {   // pass 1: tile max per row
+#pragma unroll 1
+          for (int c = 0; c < BLOCK_N / 32; ++c) {
+            const int col0 = n0 + c * 32;
+            if (col0 >= p.N) break;                    // warp-uniform
+            uint32_t v[32];
+            __syncwarp();
+            ptx::tmem_ld_32x32(t_addr + c * 32, v);
+            ptx::tmem_ld_wait();
+            fs.m_raw = fmaxf(fs.m_raw, chunk_max(v, min(32, p.N - col0)));
+          }
+        }
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N / 32; ++c) {
           const int col0 = n0 + c * 32;
-          if (col0 >= p.N) break;                    // warp-uniform
+          if (col0 >= p.N) break;                      // warp-uniform
           uint32_t v[32];
           __syncwarp();
           ptx::tmem_ld_32x32(t_addr + c * 32, v);
           ptx::tmem_ld_wait();
-          fs.m_raw = fmaxf(fs.m_raw, chunk_max(v, min(32, p.N - col0)));
+          const int n_valid = min(32, p.N - col0);
+          if constexpr (kEpi == EPI_FWD_STATS) {
+            if (kSave && !row_ok) continue;
+            fwd_chunk<kSave>(fs, v, col0, n_valid, scale2, p.inv_temp,
+                             kSave ? p.zsave + ((long long)it.nb * p.M + row) * PANEL_W + c * 32 : nullptr);
+          }
+          if constexpr (kEpi == EPI_BWD_DLOGITS) {
+            if (row_ok) bwd_chunk(bc, v, col0, n_valid, scale2, p.dlogits + ((long long)it.nb * p.M + row) * PANEL_W + c * 32);
+          }
+          if constexpr (kEpi == EPI_STORE) { if (row_ok) store_chunk(p, v, row, col0, n_valid, it.ks); }
         }
-      }
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        const int col0 = n0 + c * 32;
-        if (col0 >= p.N) break;                      // warp-uniform
-        uint32_t v[32];
-        __syncwarp();
-        ptx::tmem_ld_32x32(t_addr + c * 32, v);
-        ptx::tmem_ld_wait();
-        const int n_valid = min(32, p.N - col0);
         if constexpr (kEpi == EPI_FWD_STATS) {
-          if (kSave && !row_ok) continue;
-          fwd_chunk<kSave>(fs, v, col0, n_valid, scale2, p.inv_temp,
-                           kSave ? p.zsave + ((long long)it.nb * p.M + row) * PANEL_W + c * 32 : nullptr);
+          if (row_ok) {
+            const float4 o = make_float4(fs.m_raw * p.inv_temp, fs.s, fs.u * p.inv_temp, fs.tgt * p.inv_temp);
+            reinterpret_cast<float4*>(p.part)[(long long)it.nb * p.M + row] = o;
+          }
         }
-        if constexpr (kEpi == EPI_BWD_DLOGITS) {
-          if (row_ok) bwd_chunk(bc, v, col0, n_valid, scale2, p.dlogits + ((long long)it.nb * p.M + row) * PANEL_W + c * 32);
-        }
-        if constexpr (kEpi == EPI_STORE) { if (row_ok) store_chunk(p, v, row, col0, n_valid, it.ks); }
       }
       ptx::tc_fence_before();
       if (kCtas == 1) ptx::mbar_arrive(&tmem_empty[as]); else ptx::mbar_arrive_cluster(&tmem_empty[as], 0);
-      if constexpr (kEpi == EPI_FWD_STATS) {
-        if (row_ok) {
-          const float4 o = make_float4(fs.m_raw * p.inv_temp, fs.s, fs.u * p.inv_temp, fs.tgt * p.inv_temp);
-          reinterpret_cast<float4*>(p.part)[(long long)it.nb * p.M + row] = o;
-        }
-      }
     }
   }
 

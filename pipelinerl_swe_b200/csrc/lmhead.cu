@@ -126,13 +126,20 @@ static int clusters_for(int ctas) {
 }
 
 // group_m <= 0: all row blocks in one group (row block fastest over the whole matrix)
-static void fill_tiling(GemmParams& p, int M, int N, int K, int ctas, int group_m, int k_splits) {
+static unsigned long long hint_code(int h) {  // tunable encoding: 0 normal, 1 evict-first, 2 evict-last
+  return h == 1 ? ptx::L2_EVICT_FIRST : h == 2 ? ptx::L2_EVICT_LAST : ptx::L2_EVICT_NORMAL;
+}
+
+static void fill_tiling(GemmParams& p, int M, int N, int K, int ctas, int group_m, int k_splits, int group_n = 0,
+                        int hint_a = 0, int hint_b = 0) {
   p.M = M; p.N = N; p.K = K;
+  p.hint_a = hint_code(hint_a); p.hint_b = hint_code(hint_b);
   p.m_blocks = ceil_div(M, GEMM_BLOCK_M * ctas);
   p.n_blocks = ceil_div(N, BN);
   p.kb_total = ceil_div(K, GEMM_BLOCK_K);
   p.group_m = (group_m <= 0 || group_m > p.m_blocks) ? p.m_blocks : group_m;
   p.k_splits = k_splits < 1 ? 1 : k_splits;
+  p.group_n = (group_n <= 0 || group_n > p.n_blocks) ? p.n_blocks : group_n;
 }
 
 template <int kEpi, bool kSave = false, bool kAPanel = false>
@@ -311,12 +318,13 @@ static size_t store_gemm_slab_bytes(int M, int N, int K, int ctas, int forced_ks
 // a_panel_rows > 0: A is a dlogits panel buffer [ceil(cols/256)][a_panel_rows][256] (lda unused)
 static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* C, long long ldc,
                           int c_is_f32, int accumulate, int M, int N, int K, int ctas, int group_m, int forced_ksplit,
-                          void* slab, size_t slab_bytes, cudaStream_t st, int a_panel_rows = 0) {
+                          void* slab, size_t slab_bytes, cudaStream_t st, int a_panel_rows = 0, int group_n = 0,
+                          int hint_a = 0, int hint_b = 0) {
   GemmParams p = {};
   const int tiles = ceil_div(M, GEMM_BLOCK_M * ctas) * ceil_div(N, BN);
   int ks = (N % 4 == 0 && slab) ? choose_ksplits(tiles, clusters_for(ctas), ceil_div(K, GEMM_BLOCK_K), forced_ksplit) : 1;
   if (ks > 1 && slab_bytes < (size_t)ks * M * N * 4) ks = 1;
-  fill_tiling(p, M, N, K, ctas, group_m, ks);
+  fill_tiling(p, M, N, K, ctas, group_m, ks, group_n, hint_a, hint_b);
   p.C = C; p.ldc = ldc; p.c_is_f32 = c_is_f32; p.accumulate = accumulate; p.slab = (float*)slab;
   CUtensorMap ta, tb;
   if (a_panel_rows > 0) {
@@ -374,7 +382,7 @@ extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* 
   B200_REQUIRE(!saved || ((uintptr_t)saved & 255) == 0, "lmhead_fwd: saved buffer must be 256-byte aligned");
   const int ctas = ctas_for(M);
   GemmParams p = {};
-  fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_GROUP_M), 1);
+  fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_GROUP_M), 1, 0, get_tunable(TUNE_HINT_RESIDENT), get_tunable(TUNE_HINT_STREAM));
   const size_t need = part_bytes(M, Vloc);
   if (!saved && workspace_bytes < need) { set_error("lmhead_fwd: workspace %zu < %zu", workspace_bytes, need); return B200GRPO_EWORKSPACE; }
   p.targets = (const long long*)targets; p.v_offset = v_offset; p.inv_temp = inv_temperature;
@@ -440,7 +448,7 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
     slab = (char*)workspace + panel_bytes(M, Vloc);
     if (int e = clear_tail_panel(dlog, M, Vloc, st)) return e;
     GemmParams p = {};
-    fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_GROUP_M), 1);
+    fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_GROUP_M), 1, 0, get_tunable(TUNE_HINT_RESIDENT), get_tunable(TUNE_HINT_STREAM));
     p.targets = (const long long*)targets; p.v_offset = v_offset; p.inv_temp = inv_temperature;
     p.lse = lse; p.entropy = entropy; p.coef_lp = coef_lp; p.coef_ent = coef_ent; p.grad_scale = grad_scale;
     p.dlogits = dlog;
@@ -453,12 +461,14 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
   if (grad_hidden) {  // 2. dH[M,H] = dlogits[M,V] . W[V,H]   (B is MN-major: vocab rows are the K axis)
     ProfScope ps(PROF_BWD_DH, st);
     if (int e = run_store_gemm(dlog, 0, 0, weight, ldw, 1, grad_hidden, ldgh, 0, 0, M, H, Vloc, ctas,
-                               get_tunable(TUNE_DH_GROUP_M), get_tunable(TUNE_DH_KSPLIT), slab, slab_bytes, st, M)) return e;
+                               get_tunable(TUNE_DH_GROUP_M), get_tunable(TUNE_DH_KSPLIT), slab, slab_bytes, st, M, 0,
+                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_STREAM))) return e;
   }
   if (grad_weight) {  // 3. dW[V,H] = dlogits^T[V,M] . hidden[M,H]   (both operands MN-major: tokens are the K axis)
     ProfScope ps(PROF_BWD_DW, st);
     if (int e = run_store_gemm(dlog, 0, 1, hidden, ldh, 1, grad_weight, ldgw, grad_weight_is_f32, accumulate, Vloc, H, M,
-                               ctas, get_tunable(TUNE_DW_GROUP_M), 1, nullptr, 0, st, M)) return e;
+                               ctas, get_tunable(TUNE_DW_GROUP_M), 1, nullptr, 0, st, M, get_tunable(TUNE_DW_GROUP_N),
+                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT))) return e;
   }
   return B200GRPO_OK;
 }
