@@ -246,7 +246,9 @@ int b200grpo_rl_step_host(const b200grpo_host_batch* batch_host, int L, int H, i
  *   1: operand is [rows = K, cols = M or N] (M/N contiguous)
  * C is f32 (c_is_f32) or bf16, row-major [M, ldc]; accumulate adds into f32 C.
  * group_m: row blocks per raster group (0 = all); k_splits > 1 splits K into f32 partial slabs
- * (workspace >= k_splits*M*N*4 bytes, N % 4 == 0) reduced by a second kernel.
+ * (workspace >= k_splits*M*N*4 bytes, N % 4 == 0) reduced by a second kernel; k_splits == 0 cuts only the
+ * tiles of the last partial wave along K (workspace >= one f32 tile per cluster, 40 MB covers every case;
+ * a smaller workspace silently disables the cut).
  * ------------------------------------------------------------------------------------- */
 int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb,
                        int b_mn_major, void* C, int64_t ldc, int c_is_f32, int accumulate,

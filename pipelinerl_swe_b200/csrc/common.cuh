@@ -17,7 +17,7 @@ int check_device_sm100();  // 0 or B200GRPO_EARCH / ECUDA (cached per thread)
 int get_tunable(int id);
 enum { TUNE_FWD_SPLITS = 0, TUNE_TWO_CTA = 1, TUNE_GEMM_STAGES = 2, TUNE_WATCHDOG_MS = 3, TUNE_DH_KSPLIT = 4, TUNE_DH_GROUP_M = 5,
        TUNE_DW_GROUP_M = 6, TUNE_SAVE_LOGITS = 7, TUNE_FWD_GROUP_M = 8, TUNE_DW_GROUP_N = 9, TUNE_HINT_RESIDENT = 10,
-       TUNE_HINT_STREAM = 11, TUNE_COUNT = 12 };
+       TUNE_HINT_STREAM = 11, TUNE_DH_BIG_M = 12, TUNE_DW_BIG_M = 13, TUNE_GEMM_BIG_M = 14, TUNE_TAIL_SPLIT = 15, TUNE_DW_KSPLIT = 16, TUNE_COUNT = 17 };
 
 #define B200_CUDA_OK(expr)                                                              \
   do {                                                                                  \

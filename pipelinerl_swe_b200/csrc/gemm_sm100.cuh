@@ -43,12 +43,17 @@ constexpr int PANEL_W = 256;        // saved logits / dlogits are stored in [M x
 struct GemmParams {
   int M, N, K;
   int m_blocks, n_blocks, k_splits, group_m, group_n, kb_total;
+  int n_items;              // work items of the launch: full tiles x k_splits, or full-K tiles + tail pieces
+  int tail_first;           // tail split: items >= tail_first are K-pieces of the last (tiles % clusters) tiles
+  int tail_split;           //   pieces per tail tile (>= 2 when the tail split is on, else 0)
+  int tile_rows;            //   rows of one tile (all CTAs of the cluster)
   unsigned long long hint_a, hint_b;   // L2 eviction policy of the A / B operand loads
   // EPI_STORE
   void* C;
   long long ldc;
   int c_is_f32, accumulate;
-  float* slab;              // [k_splits][M][N] f32 partial sums when k_splits > 1
+  float* slab;              // [k_splits][M][N] f32 partial sums when k_splits > 1;
+                            // [tail piece][tile_rows][256] when the tail split is on
   // EPI_FWD_STATS / EPI_BWD_DLOGITS
   const long long* targets;
   long long v_offset;
@@ -69,27 +74,45 @@ struct GemmSmem {
   static constexpr int TOTAL = BAR_OFFSET + (2 * kStages + 4) * 8 + 16 + 1024;  // + alignment slack
 };
 
-struct Item { int m_blk, nb, ks, kb0, kb1; };
+struct Item { int m_blk, nb, ks, kb0, kb1, slot; };
 
-__device__ __forceinline__ Item decode_item(const GemmParams& p, int item) {
-  // order: k-split (slowest) > column group of group_n tile columns > row group of group_m tile rows >
-  //        tile column inside the group > tile row (fastest)
-  Item it;
-  const int tiles = p.m_blocks * p.n_blocks;
-  it.ks = item / tiles;
-  int t = item - it.ks * tiles;
+// tile number -> (row block, column block).  Order: column group of group_n tile columns (slowest) > row group of
+// group_m tile rows > tile column inside the group > tile row (fastest)
+__host__ __device__ __forceinline__ void decode_tile(const GemmParams& p, int t, int& m_blk, int& nb) {
   const int per_ngroup = p.m_blocks * p.group_n;
   const int ng = t / per_ngroup;
   t -= ng * per_ngroup;
   const int n_first = ng * p.group_n;
-  const int gn = min(p.group_n, p.n_blocks - n_first);
+  const int gn = p.group_n < p.n_blocks - n_first ? p.group_n : p.n_blocks - n_first;
   const int per_group = p.group_m * gn;
   const int g = t / per_group, w = t - g * per_group;
   const int m_first = g * p.group_m;
-  const int gm = min(p.group_m, p.m_blocks - m_first);
+  const int gm = p.group_m < p.m_blocks - m_first ? p.group_m : p.m_blocks - m_first;
   const int nb_local = w / gm;
-  it.nb = n_first + nb_local;
-  it.m_blk = m_first + (w - nb_local * gm);
+  nb = n_first + nb_local;
+  m_blk = m_first + (w - nb_local * gm);
+}
+
+// Work items: [0, tiles * k_splits) are (k-split, tile) pairs, k-split slowest.  With the tail split on
+// (k_splits == 1), items [0, tail_first) are full-K tiles -- whole waves of the persistent grid -- and item
+// tail_first + j is K-piece j % tail_split of tile tail_first + j / tail_split: the last partial wave is cut
+// along K so that every cluster gets an equal share; pieces land in the slab and tail_reduce_kernel sums them.
+__device__ __forceinline__ Item decode_item(const GemmParams& p, int item) {
+  Item it;
+  if (item >= p.tail_first) {
+    const int j = item - p.tail_first;
+    const int tt = j / p.tail_split, piece = j - tt * p.tail_split;
+    decode_tile(p, p.tail_first + tt, it.m_blk, it.nb);
+    it.ks = 0;
+    it.slot = j;
+    it.kb0 = (int)((long long)piece * p.kb_total / p.tail_split);
+    it.kb1 = (int)((long long)(piece + 1) * p.kb_total / p.tail_split);
+    return it;
+  }
+  const int tiles = p.m_blocks * p.n_blocks;
+  it.ks = item / tiles;
+  it.slot = -1;
+  decode_tile(p, item - it.ks * tiles, it.m_blk, it.nb);
   it.kb0 = (int)((long long)it.ks * p.kb_total / p.k_splits);
   it.kb1 = (int)((long long)(it.ks + 1) * p.kb_total / p.k_splits);
   return it;
@@ -198,8 +221,15 @@ __device__ __forceinline__ void bwd_chunk(const BwdRowConst& rc, const uint32_t 
   for (int q = 0; q < 4; ++q) o[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
 }
 
-__device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t (&v)[32], int row, int col0, int n_valid, int ks) {
-  if (p.k_splits > 1) {  // f32 partial of this k-split; reduced (and cast / accumulated) by splitk_reduce_kernel
+// slot >= 0: tail piece, written whole (32 columns) at tile-local coordinates (r_local, c_local)
+__device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t (&v)[32], int row, int col0, int n_valid, int ks,
+                                            int slot, int r_local, int c_local) {
+  if (slot >= 0) {
+    float4* o4 = reinterpret_cast<float4*>(p.slab + ((long long)slot * p.tile_rows + r_local) * PANEL_W + c_local);
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      o4[q] = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
+  } else if (p.k_splits > 1) {  // f32 partial of this k-split; reduced (and cast / accumulated) by splitk_reduce_kernel
     float* o = p.slab + ((long long)ks * p.M + row) * p.N + col0;
     if (n_valid >= 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
       float4* o4 = reinterpret_cast<float4*>(o);
@@ -283,7 +313,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
   const uint32_t cta_rank = kCtas > 1 ? ptx::cluster_ctarank() : 0u;
   const bool leader = cta_rank == 0;
   const int cluster_id = blockIdx.x / kCtas, n_clusters = gridDim.x / kCtas;
-  const int n_items = p.m_blocks * p.n_blocks * p.k_splits;
+  const int n_items = p.n_items;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tm_a);
@@ -450,7 +480,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
           if constexpr (kEpi == EPI_BWD_DLOGITS) {
             if (row_ok) bwd_chunk(bc, v, col0, n_valid, scale2, p.dlogits + ((long long)it.nb * p.M + row) * PANEL_W + c * 32);
           }
-          if constexpr (kEpi == EPI_STORE) { if (row_ok) store_chunk(p, v, row, col0, n_valid, it.ks); }
+          if constexpr (kEpi == EPI_STORE) {
+            if (row_ok) store_chunk(p, v, row, col0, n_valid, it.ks, it.slot, (int)cta_rank * CTA_M + rep * GEMM_BLOCK_M + row_in_tile, c * 32);
+          }
         }
         if constexpr (kEpi == EPI_FWD_STATS) {
           if (row_ok) {

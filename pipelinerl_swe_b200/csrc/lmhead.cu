@@ -61,7 +61,7 @@ static int make_tmap_panel(CUtensorMap* tm, const void* ptr, long long rows, lon
 
 // ---- tiling --------------------------------------------------------------------------------
 constexpr int BN = 256;
-constexpr int STAGES_1CTA = 4, STAGES_2CTA = 6;
+constexpr int STAGES_1CTA = 4, STAGES_2CTA = 6, STAGES_BIGM = 4;   // 32 KB, 32 KB(pair: 2 x 16+16) and 48 KB stages
 
 // k-splits for an EPI_STORE GEMM: smallest split count whose wave efficiency is within 1% of the
 // best reachable with <= 8 splits (each split costs an f32 slab round trip through HBM).
@@ -79,19 +79,20 @@ static int choose_ksplits(int tiles, int clusters, int kb_total, int forced) {
   return best;
 }
 
-template <int kEpi, int kAMajor, int kBMajor, int kCtas, bool kSave, bool kAPanel>
+template <int kEpi, int kAMajor, int kBMajor, int kCtas, bool kSave, bool kAPanel, int kMRep = 1>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
-  constexpr int kStages = kCtas == 1 ? STAGES_1CTA : STAGES_2CTA;
-  using L = GemmSmem<BN, kCtas, kStages>;
+  constexpr int kStages = kMRep == 2 ? STAGES_BIGM : kCtas == 1 ? STAGES_1CTA : STAGES_2CTA;
+  using L = GemmSmem<BN, kCtas, kStages, kMRep>;
   static_assert(BN == PANEL_W, "panels are one N tile wide");
-  auto kern = gemm_sm100_kernel<kEpi, kAMajor, kBMajor, kCtas, BN, kStages, kSave, kAPanel>;
+  static_assert(L::TOTAL <= 227 * 1024, "shared memory budget");
+  auto kern = gemm_sm100_kernel<kEpi, kAMajor, kBMajor, kCtas, BN, kStages, kSave, kAPanel, kMRep>;
   static bool configured = false;
   if (!configured) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     configured = true;
   }
-  const long long n_items = (long long)p.m_blocks * p.n_blocks * p.k_splits;
-  B200_REQUIRE(n_items < (1ll << 30), "gemm: too many tiles");
+  B200_REQUIRE((long long)p.m_blocks * p.n_blocks * p.k_splits < (1ll << 30), "gemm: too many tiles");
+  const long long n_items = p.n_items;
   int clusters = sm_count() / kCtas;
   if (clusters > n_items) clusters = (int)n_items;
   cudaLaunchConfig_t cfg = {};
@@ -110,9 +111,9 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
 
 // Operand maps for  D[M,N] = A . B^T  under the four layout combinations.
 static int make_ab_maps(CUtensorMap* ta, CUtensorMap* tb, const void* A, long long lda, int a_mn, const void* B, long long ldb,
-                        int b_mn, int M, int N, int K, int ctas) {
+                        int b_mn, int M, int N, int K, int ctas, int mrep = 1) {
   int e;
-  if (!a_mn) e = make_tmap(ta, A, K, M, lda, GEMM_BLOCK_M);       // [M rows, K cols]
+  if (!a_mn) e = make_tmap(ta, A, K, M, lda, GEMM_BLOCK_M * mrep);  // [M rows, K cols]
   else e = make_tmap(ta, A, M, K, lda, GEMM_BLOCK_K);             // [K rows, M cols], 64x64 atoms
   if (e) return e;
   if (!b_mn) e = make_tmap(tb, B, K, N, ldb, BN / ctas);
@@ -131,31 +132,55 @@ static unsigned long long hint_code(int h) {  // tunable encoding: 0 normal, 1 e
 }
 
 static void fill_tiling(GemmParams& p, int M, int N, int K, int ctas, int group_m, int k_splits, int group_n = 0,
-                        int hint_a = 0, int hint_b = 0) {
+                        int hint_a = 0, int hint_b = 0, int mrep = 1) {
   p.M = M; p.N = N; p.K = K;
   p.hint_a = hint_code(hint_a); p.hint_b = hint_code(hint_b);
-  p.m_blocks = ceil_div(M, GEMM_BLOCK_M * ctas);
+  p.m_blocks = ceil_div(M, GEMM_BLOCK_M * mrep * ctas);
   p.n_blocks = ceil_div(N, BN);
   p.kb_total = ceil_div(K, GEMM_BLOCK_K);
   p.group_m = (group_m <= 0 || group_m > p.m_blocks) ? p.m_blocks : group_m;
   p.k_splits = k_splits < 1 ? 1 : k_splits;
   p.group_n = (group_n <= 0 || group_n > p.n_blocks) ? p.n_blocks : group_n;
+  p.n_items = p.m_blocks * p.n_blocks * p.k_splits;
+  p.tail_first = 0x7fffffff; p.tail_split = 0;
+  p.tile_rows = GEMM_BLOCK_M * mrep * ctas;
+}
+
+// Tail split of an EPI_STORE GEMM: tiles = q * clusters + r; the r tiles of the last partial wave are cut into
+// s = clusters / r K-pieces each so that the last wave costs 1/s of a full one.  Returns s (0 = not worth it).
+constexpr int TAIL_MIN_KB = 8;   // fewest k-blocks in a piece
+static int tail_split_for(int tiles, int clusters, int kb_total) {
+  const int r = tiles % clusters;
+  if (r == 0) return 0;
+  int s = clusters / r;
+  if (s > kb_total / TAIL_MIN_KB) s = kb_total / TAIL_MIN_KB;
+  return s >= 2 ? s : 0;
+}
+static size_t tail_slab_bytes(int tiles, int clusters, int kb_total, int tile_rows) {
+  const int s = tail_split_for(tiles, clusters, kb_total);
+  return s ? align_up((size_t)(tiles % clusters) * s * tile_rows * PANEL_W * 4, 256) : 0;
 }
 
 template <int kEpi, bool kSave = false, bool kAPanel = false>
-static int dispatch(int a_mn, int b_mn, int ctas, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+static int dispatch(int a_mn, int b_mn, int ctas, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st,
+                    int mrep = 1) {
 #define B200_CASE(AM, BM, C) \
-  if (a_mn == AM && b_mn == BM && ctas == C) return launch_gemm<kEpi, AM, BM, C, kSave, kAPanel>(ta, tb, p, st);
+  if (a_mn == AM && b_mn == BM && ctas == C && mrep == 1) return launch_gemm<kEpi, AM, BM, C, kSave, kAPanel>(ta, tb, p, st);
+#define B200_BIG(AM, BM) \
+  if (a_mn == AM && b_mn == BM && ctas == 2 && mrep == 2) return launch_gemm<kEpi, AM, BM, 2, kSave, kAPanel, 2>(ta, tb, p, st);
   if constexpr (kEpi == EPI_STORE && kAPanel) {   // the two backward GEMMs read dlogits panels
     B200_CASE(0, 1, 1) B200_CASE(0, 1, 2) B200_CASE(1, 1, 1) B200_CASE(1, 1, 2)
+    B200_BIG(0, 1) B200_BIG(1, 1)
   } else if constexpr (kEpi == EPI_STORE) {
     B200_CASE(0, 0, 1) B200_CASE(0, 0, 2) B200_CASE(0, 1, 1) B200_CASE(0, 1, 2)
     B200_CASE(1, 0, 1) B200_CASE(1, 0, 2) B200_CASE(1, 1, 1) B200_CASE(1, 1, 2)
+    B200_BIG(0, 0) B200_BIG(0, 1) B200_BIG(1, 0) B200_BIG(1, 1)
   } else {
     B200_CASE(0, 0, 1) B200_CASE(0, 0, 2)
   }
 #undef B200_CASE
-  set_error("unsupported GEMM variant a_mn=%d b_mn=%d ctas=%d", a_mn, b_mn, ctas);
+#undef B200_BIG
+  set_error("unsupported GEMM variant a_mn=%d b_mn=%d ctas=%d rows/CTA=%d", a_mn, b_mn, ctas, 128 * mrep);
   return B200GRPO_EINVAL;
 }
 
@@ -163,6 +188,9 @@ static int ctas_for(int M) {
   (void)M;
   return get_tunable(TUNE_TWO_CTA) ? 2 : 1;
 }
+
+// 256 rows per CTA (pair tile 512 x 256) when the tunable asks for it and CTA pairs are in use
+static int mrep_for(int tunable, int ctas) { return (ctas == 2 && get_tunable(tunable)) ? 2 : 1; }
 
 // ---- small kernels around the GEMMs -----------------------------------------------------
 // merge the per-tile partials [n_blocks][M][4] -> stats [M][4] (online-softmax merge, fixed order).
@@ -307,10 +335,39 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
   }
 }
 
+// sum the K-pieces of the tail tiles: block = 4 tile rows x 64 float4 columns; grid (tail tiles, tile_rows / 4)
+constexpr int TAIL_RED_ROWS = 4;
+__global__ void __launch_bounds__(256) tail_reduce_kernel(const GemmParams p) {
+  int m_blk, nb;
+  decode_tile(p, p.tail_first + blockIdx.x, m_blk, nb);
+  const int r_local = blockIdx.y * TAIL_RED_ROWS + (threadIdx.x >> 6), c_local = (threadIdx.x & 63) * 4;
+  const int row = m_blk * p.tile_rows + r_local, col = nb * PANEL_W + c_local;
+  if (row >= p.M || col >= p.N) return;                // N % 4 == 0: a quad is inside or outside as a whole
+  const float* src = p.slab + ((long long)blockIdx.x * p.tail_split * p.tile_rows + r_local) * PANEL_W + c_local;
+  const long long piece = (long long)p.tile_rows * PANEL_W;
+  float4 acc = __ldg(reinterpret_cast<const float4*>(src));
+  for (int s = 1; s < p.tail_split; ++s) {
+    const float4 x = __ldg(reinterpret_cast<const float4*>(src + s * piece));
+    acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+  }
+  if (p.c_is_f32) {
+    float* o = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + col;
+    if (p.accumulate) { acc.x += o[0]; acc.y += o[1]; acc.z += o[2]; acc.w += o[3]; }
+    o[0] = acc.x; o[1] = acc.y; o[2] = acc.z; o[3] = acc.w;
+  } else {
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.C) + (long long)row * p.ldc + col;
+    o[0] = __float2bfloat16_rn(acc.x); o[1] = __float2bfloat16_rn(acc.y);
+    o[2] = __float2bfloat16_rn(acc.z); o[3] = __float2bfloat16_rn(acc.w);
+  }
+}
+
 // C[M,N] (+)= A . B^T with optional k-splits; slab workspace is needed when k_splits > 1.
-static size_t store_gemm_slab_bytes(int M, int N, int K, int ctas, int forced_ksplit) {
+static size_t store_gemm_slab_bytes(int M, int N, int K, int ctas, int forced_ksplit, int mrep = 1) {
   if (N % 4 != 0) return 0;
-  const int tiles = ceil_div(M, GEMM_BLOCK_M * ctas) * ceil_div(N, BN);
+  if (ctas != 2) mrep = 1;
+  const int tiles = ceil_div(M, GEMM_BLOCK_M * mrep * ctas) * ceil_div(N, BN);
+  if (forced_ksplit <= 0 && get_tunable(TUNE_TAIL_SPLIT))
+    return tail_slab_bytes(tiles, clusters_for(ctas), ceil_div(K, GEMM_BLOCK_K), GEMM_BLOCK_M * mrep * ctas);
   const int s = choose_ksplits(tiles, clusters_for(ctas), ceil_div(K, GEMM_BLOCK_K), forced_ksplit);
   return s > 1 ? align_up((size_t)s * M * N * 4, 256) : 0;
 }
@@ -319,22 +376,43 @@ static size_t store_gemm_slab_bytes(int M, int N, int K, int ctas, int forced_ks
 static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* C, long long ldc,
                           int c_is_f32, int accumulate, int M, int N, int K, int ctas, int group_m, int forced_ksplit,
                           void* slab, size_t slab_bytes, cudaStream_t st, int a_panel_rows = 0, int group_n = 0,
-                          int hint_a = 0, int hint_b = 0) {
+                          int hint_a = 0, int hint_b = 0, int mrep = 1) {
   GemmParams p = {};
-  const int tiles = ceil_div(M, GEMM_BLOCK_M * ctas) * ceil_div(N, BN);
-  int ks = (N % 4 == 0 && slab) ? choose_ksplits(tiles, clusters_for(ctas), ceil_div(K, GEMM_BLOCK_K), forced_ksplit) : 1;
+  if (ctas != 2) mrep = 1;   // the 256-row variant exists for CTA pairs only
+  const int tiles = ceil_div(M, GEMM_BLOCK_M * mrep * ctas) * ceil_div(N, BN);
+  // forced_ksplit >= 1: uniform k-splits (1 = none); <= 0: automatic = tail split of the last partial wave
+  // (or, with the tail_split tunable off, the uniform split count with the best wave efficiency)
+  const bool want_tail = forced_ksplit <= 0 && get_tunable(TUNE_TAIL_SPLIT);
+  int ks = (N % 4 == 0 && slab && !want_tail) ? choose_ksplits(tiles, clusters_for(ctas), ceil_div(K, GEMM_BLOCK_K), forced_ksplit) : 1;
   if (ks > 1 && slab_bytes < (size_t)ks * M * N * 4) ks = 1;
-  fill_tiling(p, M, N, K, ctas, group_m, ks, group_n, hint_a, hint_b);
+  fill_tiling(p, M, N, K, ctas, group_m, ks, group_n, hint_a, hint_b, mrep);
+  int tail = 0;
+  if (want_tail && slab && N % 4 == 0) {
+    const int clusters = clusters_for(ctas);
+    tail = tail_split_for(tiles, clusters, p.kb_total);
+    if (tail && slab_bytes < tail_slab_bytes(tiles, clusters, p.kb_total, p.tile_rows)) tail = 0;
+    if (tail) {
+      const int r = tiles % clusters;
+      p.tail_first = tiles - r;
+      p.tail_split = tail;
+      p.n_items = p.tail_first + r * tail;
+    }
+  }
   p.C = C; p.ldc = ldc; p.c_is_f32 = c_is_f32; p.accumulate = accumulate; p.slab = (float*)slab;
   CUtensorMap ta, tb;
   if (a_panel_rows > 0) {
     const int cols = a_mn ? M : K;  // the panelled (vocab) axis
-    if (int e = make_tmap_panel(&ta, A, a_panel_rows, ceil_div(cols, PANEL_W), a_mn ? GEMM_BLOCK_K : GEMM_BLOCK_M)) return e;
+    if (int e = make_tmap_panel(&ta, A, a_panel_rows, ceil_div(cols, PANEL_W), a_mn ? GEMM_BLOCK_K : GEMM_BLOCK_M * mrep)) return e;
     if (int e = (!b_mn ? make_tmap(&tb, B, K, N, ldb, BN / ctas) : make_tmap(&tb, B, N, K, ldb, GEMM_BLOCK_K))) return e;
-    if (int e = dispatch<EPI_STORE, false, true>(a_mn ? 1 : 0, b_mn ? 1 : 0, ctas, ta, tb, p, st)) return e;
+    if (int e = dispatch<EPI_STORE, false, true>(a_mn ? 1 : 0, b_mn ? 1 : 0, ctas, ta, tb, p, st, mrep)) return e;
   } else {
-    if (int e = make_ab_maps(&ta, &tb, A, lda, a_mn, B, ldb, b_mn, M, N, K, ctas)) return e;
-    if (int e = dispatch<EPI_STORE>(a_mn ? 1 : 0, b_mn ? 1 : 0, ctas, ta, tb, p, st)) return e;
+    if (int e = make_ab_maps(&ta, &tb, A, lda, a_mn, B, ldb, b_mn, M, N, K, ctas, mrep)) return e;
+    if (int e = dispatch<EPI_STORE>(a_mn ? 1 : 0, b_mn ? 1 : 0, ctas, ta, tb, p, st, mrep)) return e;
+  }
+  if (tail) {
+    dim3 grid((p.n_items - p.tail_first) / tail, p.tile_rows / TAIL_RED_ROWS);   // x: tail tiles
+    tail_reduce_kernel<<<grid, 256, 0, st>>>(p);
+    B200_CUDA_OK(cudaGetLastError());
   }
   if (ks > 1) {
     const long long quads = (long long)M * (N / 4);
@@ -416,7 +494,9 @@ extern "C" int b200grpo_lmhead_finalize(const float* stats, int R, int M, float*
 
 extern "C" size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc, int with_saved) {
   const int ctas = ctas_for(M);
-  const size_t slab = store_gemm_slab_bytes(M, H, Vloc, ctas, get_tunable(TUNE_DH_KSPLIT));
+  size_t slab = store_gemm_slab_bytes(M, H, Vloc, ctas, get_tunable(TUNE_DH_KSPLIT), mrep_for(TUNE_DH_BIG_M, ctas));
+  const size_t slab_dw = store_gemm_slab_bytes(Vloc, H, M, ctas, get_tunable(TUNE_DW_KSPLIT), mrep_for(TUNE_DW_BIG_M, ctas));
+  if (slab_dw > slab) slab = slab_dw;   // the two GEMMs run back to back on one stream and share it
   return (with_saved ? 0 : panel_bytes(M, Vloc)) + slab + 256;
 }
 
@@ -462,13 +542,13 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
     ProfScope ps(PROF_BWD_DH, st);
     if (int e = run_store_gemm(dlog, 0, 0, weight, ldw, 1, grad_hidden, ldgh, 0, 0, M, H, Vloc, ctas,
                                get_tunable(TUNE_DH_GROUP_M), get_tunable(TUNE_DH_KSPLIT), slab, slab_bytes, st, M, 0,
-                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_STREAM))) return e;
+                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_STREAM), mrep_for(TUNE_DH_BIG_M, ctas))) return e;
   }
   if (grad_weight) {  // 3. dW[V,H] = dlogits^T[V,M] . hidden[M,H]   (both operands MN-major: tokens are the K axis)
     ProfScope ps(PROF_BWD_DW, st);
     if (int e = run_store_gemm(dlog, 0, 1, hidden, ldh, 1, grad_weight, ldgw, grad_weight_is_f32, accumulate, Vloc, H, M,
-                               ctas, get_tunable(TUNE_DW_GROUP_M), 1, nullptr, 0, st, M, get_tunable(TUNE_DW_GROUP_N),
-                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT))) return e;
+                               ctas, get_tunable(TUNE_DW_GROUP_M), get_tunable(TUNE_DW_KSPLIT), slab, slab_bytes, st, M, get_tunable(TUNE_DW_GROUP_N),
+                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT), mrep_for(TUNE_DW_BIG_M, ctas))) return e;
   }
   return B200GRPO_OK;
 }
@@ -484,5 +564,6 @@ extern "C" int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, co
   const int ctas = ctas_for(M);
   ProfScope ps(PROF_GEMM, (cudaStream_t)stream);
   return run_store_gemm(A, lda, a_mn_major ? 1 : 0, B, ldb, b_mn_major ? 1 : 0, C, ldc, c_is_f32, accumulate, M, N, K, ctas, group_m,
-                        k_splits < 1 ? 1 : k_splits, k_splits > 1 ? workspace : nullptr, workspace_bytes, (cudaStream_t)stream);
+                        k_splits, k_splits != 1 ? workspace : nullptr, workspace_bytes, (cudaStream_t)stream, 0, 0, 0, 0,
+                        mrep_for(TUNE_GEMM_BIG_M, ctas));
 }

@@ -149,7 +149,8 @@ def gemm_bf16(A: torch.Tensor, B: torch.Tensor, a_mn_major=False, b_mn_major=Fal
     assert K == K2
     if out is None:
         out = torch.empty(M, N, dtype=out_dtype, device=A.device)
-    ws = _workspace(A.device, max(k_splits, 1) * M * N * 4 if k_splits > 1 else 256, "slab")
+    # k_splits == 0: tail split of the last partial wave, at most one f32 tile per cluster (<= 74 x 512 KB)
+    ws = _workspace(A.device, k_splits * M * N * 4 if k_splits > 1 else (40 << 20) if k_splits == 0 else 256, "slab")
     check(lib().b200grpo_gemm_bf16(A.data_ptr(), A.stride(0), int(a_mn_major), B.data_ptr(), B.stride(0), int(b_mn_major),
                                    out.data_ptr(), out.stride(0), int(out.dtype == torch.float32), int(accumulate), M, N, K,
                                    int(group_m), int(k_splits), ws.data_ptr(), ws.numel(), _stream()))

@@ -194,6 +194,94 @@ def probe_sustained(two_cta, M, N, K, group_m, ks, secs=1.5):
     return True, " | ".join(res)
 
 
+def probe_bigm_gemm(a_mn, b_mn, M, N, K, ks=1):
+    """256-rows-per-CTA variant (pair tile 512 x 256) against the fp32 product, and bit-equal to the 128-row variant."""
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", 1)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    A = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    B = torch.randn(N, K, device="cuda", generator=g).bfloat16()
+    ref = A.float() @ B.float().t()
+    Ain = A.t().contiguous() if a_mn else A
+    Bin = B.t().contiguous() if b_mn else B
+    _abi.set_tunable("gemm_big_m", 0)
+    small = ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out_dtype=torch.float32, k_splits=ks)
+    _abi.set_tunable("gemm_big_m", 1)
+    big = ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out_dtype=torch.float32, k_splits=ks)
+    torch.cuda.synchronize()
+    err = _rel(big, ref)
+    same = bool(torch.equal(big, small))
+    return err < 1e-4 and same, f"rel_err={err:.3e} bit_equal_to_128row={same}"
+
+
+def probe_tail_gemm(big, a_mn, b_mn, M, N, K):
+    """k_splits=0: the last partial wave is cut along K; f32 store, bf16 store and f32 accumulate against fp32 matmul."""
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", 1)
+    _abi.set_tunable("gemm_big_m", big)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    A = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    B = torch.randn(N, K, device="cuda", generator=g).bfloat16()
+    ref = A.float() @ B.float().t()
+    Ain = A.t().contiguous() if a_mn else A
+    Bin = B.t().contiguous() if b_mn else B
+    kw = dict(a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), k_splits=0, group_m=3)
+    f32 = ops.gemm_bf16(Ain, Bin, out_dtype=torch.float32, **kw)
+    b16 = ops.gemm_bf16(Ain, Bin, out_dtype=torch.bfloat16, **kw)
+    acc = torch.ones(M, N, device="cuda")
+    ops.gemm_bf16(Ain, Bin, out=acc, accumulate=True, **kw)
+    again = ops.gemm_bf16(Ain, Bin, out_dtype=torch.float32, **kw)
+    torch.cuda.synchronize()
+    e1, e2, e3 = _rel(f32, ref), _rel(b16, ref), _rel(acc, ref + 1)
+    det = bool(torch.equal(f32, again))
+    return e1 < 1e-4 and e2 < 1e-2 and e3 < 1e-4 and det, f"f32={e1:.2e} bf16={e2:.2e} acc={e3:.2e} deterministic={det}"
+
+
+def probe_bigm_sustained(a_mn, b_mn, M, N, K, group_m, ks_small, ks_big, secs=1.5):
+    """128-row vs 256-row CTA tiles vs cuBLAS, each held for `secs` (power-capped steady state)."""
+    from pipelinerl_swe_b200 import _abi, ops
+    _abi.set_tunable("two_cta", 1)
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = torch.randn(N, K, device="cuda").bfloat16()
+    Ain = A.t().contiguous() if a_mn else A
+    Bin = B.t().contiguous() if b_mn else B
+    Bt = B.t().contiguous()
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+
+    def run(fn, name):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        n, t_start = 0, time.time()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        while time.time() - t_start < secs * 0.5:
+            for _ in range(10):
+                fn()
+            torch.cuda.synchronize()
+        t0.record()
+        t_mid = time.time()
+        while time.time() - t_mid < secs * 0.5:
+            for _ in range(10):
+                fn()
+            n += 10
+            torch.cuda.synchronize()
+        t1.record(); torch.cuda.synchronize()
+        ms = t0.elapsed_time(t1) / n
+        return f"{name} {ms:.3f}ms {2 * M * N * K / ms / 1e9:.0f}TF"
+
+    def ours(big, ks, gm=group_m):
+        def f():
+            _abi.set_tunable("gemm_big_m", big)
+            ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out=out, group_m=gm, k_splits=ks)
+        return f
+
+    res = [run(ours(0, ks_small), f"128row/ks{ks_small}"), run(ours(1, ks_big), f"256row/ks{ks_big}"),
+           run(lambda: torch.matmul(A, Bt, out=out), "cublas"),
+           run(ours(1, ks_big, max(1, group_m // 2)), f"256row/ks{ks_big}/g{max(1, group_m // 2)}"),
+           run(ours(0, ks_small), f"128row/ks{ks_small}")]
+    return True, " | ".join(res)
+
+
 def probe_raster_sweep(which):
     """One launch per (group_m, k_splits) config, meant to run under `ncu --metrics dram__bytes_read.sum,...`."""
     from pipelinerl_swe_b200 import ops
@@ -270,6 +358,19 @@ def probe_speed(two_cta, M, H, V):
 
 
 PROBES = {}
+for _a in (0, 1):
+    for _b in (0, 1):
+        PROBES[f"bigm_gemm_a{_a}b{_b}"] = (probe_bigm_gemm, (_a, _b, 1024, 512, 320))
+        PROBES[f"bigm_gemm_a{_a}b{_b}_odd"] = (probe_bigm_gemm, (_a, _b, 1000, 776, 1192))
+for _big in (0, 1):
+    PROBES[f"tail_gemm_few_big{_big}"] = (probe_tail_gemm, (_big, 0, 0, 1000, 776, 1192))       # tiles < clusters
+    PROBES[f"tail_gemm_waves_big{_big}"] = (probe_tail_gemm, (_big, 0, 1, 4000, 2560, 2048))   # full waves + tail
+    PROBES[f"tail_gemm_mn_big{_big}"] = (probe_tail_gemm, (_big, 1, 1, 5000, 2056, 1536))
+PROBES["bigm_gemm_splitk"] = (probe_bigm_gemm, (0, 1, 1000, 776, 9000, 3))
+PROBES["sust_bigm_dw"] = (probe_bigm_sustained, (1, 1, 152064, 3584, 8192, 1, 1, 1))
+PROBES["sust_bigm_dh"] = (probe_bigm_sustained, (0, 1, 8192, 3584, 152064, 8, 4, 0))
+PROBES["sust_bigm_dw_tail"] = (probe_bigm_sustained, (1, 1, 152064, 3584, 8192, 1, 1, 0))
+PROBES["sust_bigm_fwdshape"] = (probe_bigm_sustained, (0, 0, 8192, 152064, 3584, 16, 1, 1))
 for ctas in (0, 1):
     for a_mn in (0, 1):
         for b_mn in (0, 1):

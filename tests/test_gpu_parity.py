@@ -218,3 +218,89 @@ def test_gemm_splitk_and_raster(a_mn, b_mn):
         acc = torch.full((M, N), 2.0, device=d)
         ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out=acc, accumulate=True, group_m=group_m, k_splits=ks)
         assert _rel(acc, ref + 2.0) < 1e-4
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 0), (1, 1)])
+def test_gemm_256_row_tiles_bit_equal_to_128_row_tiles(a_mn, b_mn):
+    """gemm_big_m: two 128-row MMAs per CTA share one B tile; same k order per output => identical bits."""
+    from pipelinerl_swe_b200 import _abi, ops
+    d = _dev()
+    g = torch.Generator(device=d).manual_seed(5)
+    M, N, K = 1000, 776, 1192
+    A = torch.randn(M, K, device=d, generator=g).bfloat16()
+    B = torch.randn(N, K, device=d, generator=g).bfloat16()
+    ref = A.float() @ B.float().t()
+    Ain = A.t().contiguous() if a_mn else A
+    Bin = B.t().contiguous() if b_mn else B
+    try:
+        outs = []
+        for big in (0, 1):
+            _abi.set_tunable("gemm_big_m", big)
+            outs.append(ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), group_m=2, k_splits=1))
+            outs.append(ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), group_m=2, k_splits=3))
+    finally:
+        _abi.set_tunable("gemm_big_m", 0)
+    assert _rel(outs[2], ref) < 1e-4
+    assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[3])
+
+
+@pytest.mark.parametrize("big", [0, 1])
+@pytest.mark.parametrize("a_mn,b_mn,M,N,K", [(0, 0, 1000, 776, 1192),      # fewer tiles than clusters: every tile is cut
+                                             (0, 1, 4000, 2560, 2048),     # whole waves + a cut tail
+                                             (1, 1, 5000, 2056, 1536)])
+def test_gemm_tail_split(a_mn, b_mn, M, N, K, big):
+    """k_splits=0: tiles of the last partial wave are cut along K and summed in a fixed order (deterministic)."""
+    from pipelinerl_swe_b200 import _abi, ops
+    d = _dev()
+    g = torch.Generator(device=d).manual_seed(6)
+    A = torch.randn(M, K, device=d, generator=g).bfloat16()
+    B = torch.randn(N, K, device=d, generator=g).bfloat16()
+    ref = A.float() @ B.float().t()
+    Ain = A.t().contiguous() if a_mn else A
+    Bin = B.t().contiguous() if b_mn else B
+    kw = dict(a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), k_splits=0, group_m=3)
+    try:
+        _abi.set_tunable("gemm_big_m", big)
+        f32 = ops.gemm_bf16(Ain, Bin, out_dtype=torch.float32, **kw)
+        b16 = ops.gemm_bf16(Ain, Bin, out_dtype=torch.bfloat16, **kw)
+        acc = torch.full((M, N), 2.0, device=d)
+        ops.gemm_bf16(Ain, Bin, out=acc, accumulate=True, **kw)
+        again = ops.gemm_bf16(Ain, Bin, out_dtype=torch.float32, **kw)
+    finally:
+        _abi.set_tunable("gemm_big_m", 0)
+    assert _rel(f32, ref) < 1e-4 and _rel(b16, ref) < 1e-2 and _rel(acc, ref + 2.0) < 1e-4
+    assert torch.equal(f32, again)
+
+
+@pytest.mark.parametrize("dh_big,dw_big,tail", [(0, 0, 0), (1, 1, 1), (0, 1, 1), (1, 0, 0)])
+def test_lmhead_bwd_tile_variants_agree(dh_big, dw_big, tail):
+    """dH / dW through 128- or 256-row tiles, with or without the tail split, against torch autograd in fp32."""
+    from pipelinerl_swe_b200 import _abi, ops
+    d = _dev()
+    M, H, V, temp = 1100, 768, 40000 + 8, 0.8
+    g = torch.Generator(device=d).manual_seed(9)
+    h = torch.randn(M, H, device=d, generator=g).bfloat16()
+    w = (torch.randn(V, H, device=d, generator=g) * 0.04).bfloat16()
+    tgt = torch.randint(0, V, (M,), device=d, generator=g)
+    c_lp = torch.randn(M, device=d, generator=g) * 0.1
+    c_ent = torch.randn(M, device=d, generator=g) * 0.01
+    hr, wr = h.float().requires_grad_(True), w.float().requires_grad_(True)
+    logp = torch.log_softmax((hr @ wr.t()) / temp, -1)
+    lp = logp.gather(1, tgt[:, None]).squeeze(1)
+    ent = -(logp.exp() * logp).sum(-1)
+    ((lp * c_lp).sum() + (ent * c_ent).sum()).backward()
+    try:
+        _abi.set_tunable("dh_big_m", dh_big)
+        _abi.set_tunable("dw_big_m", dw_big)
+        _abi.set_tunable("tail_split", tail)
+        saved = ops.lmhead_saved_buffer(M, H, V, d)
+        stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp, saved=saved)
+        lp2, ent2, lse = ops.lmhead_finalize(stats)
+        gw = torch.full((V, H), 0.5, device=d)
+        gh, _ = ops.lmhead_bwd(h, w, tgt, lse, ent2, c_lp, c_ent, 1.0 / temp, grad_weight_out=gw, accumulate=True, saved=saved)
+    finally:
+        _abi.set_tunable("dh_big_m", 1)
+        _abi.set_tunable("dw_big_m", 0)
+        _abi.set_tunable("tail_split", 1)
+    assert _rel(gh, hr.grad) < GRAD_RTOL
+    assert _rel(gw - 0.5, wr.grad) < GRAD_RTOL
