@@ -255,6 +255,30 @@ int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B
                        int M, int N, int K, int group_m, int k_splits, void* workspace,
                        size_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Step-metrics accumulator.  Replaces, per micro-batch, the python
+ * `rl_metrics[k].append(v)` of pipelinerl/finetune_loop.py:669-670 and, per optimizer step, the
+ * pickled all_gather_object of :62-87 + aggregate_rl_stats (rl/utils.py:8-22): every
+ * micro-batch folds its K3 metrics vector into acc on the device (no host sync); at the step
+ * boundary the caller exchanges acc (one fixed-size collective) and combines by kind.
+ *
+ * n_stats keys in the order of the reference's stats dict (rl/__init__.py:325-375).  Per key:
+ * slots[k] >= 0 is a B200GRPO_M_* index, < 0 one of B200GRPO_STAT_KL_COEF (= n_seq * kl_coef),
+ * B200GRPO_STAT_ENTROPY_COEF (= n_seq * entropy_coef), B200GRPO_STAT_INPUT_SIZE;
+ * kinds[k] is B200GRPO_STAT_SUM / _MIN / _MAX (chosen from the key NAME by the caller, as
+ * aggregate_rl_stats does).  Non-finite values are skipped (finetune_loop.py:85); a micro-batch
+ * without labels contributes input_size only (rl/__init__.py:195).  record == 0 (sentinel
+ * batch, finetune_loop.py:664-666) only advances the micro-batch / sample counters.
+ * acc: f64[2*n_stats + 4] = values | counts | flags, labelled micro-batches, micro-batches, samples.
+ * ------------------------------------------------------------------------------------- */
+enum { B200GRPO_STAT_SUM = 0, B200GRPO_STAT_MIN = 1, B200GRPO_STAT_MAX = 2 };
+enum { B200GRPO_STAT_KL_COEF = -1, B200GRPO_STAT_ENTROPY_COEF = -2, B200GRPO_STAT_INPUT_SIZE = -3 };
+#define B200GRPO_STATS_MAX 64
+int b200grpo_metrics_reset(const int* kinds, int n_stats, double* acc, void* stream);
+int b200grpo_metrics_accumulate(const double* metrics, const int* slots, const int* kinds, int n_stats,
+                                double kl_coef, double entropy_coef, double input_size,
+                                double n_samples, int record, double* acc, void* stream);
+
 /* Tunables (for experiments from the test/bench harness; defaults are the shipped ones).
  * name in {"two_cta","dh_ksplit","dh_group_m","dw_group_m","save_logits",...}; returns the previous value. */
 int b200grpo_set_tunable(const char* name, int value);

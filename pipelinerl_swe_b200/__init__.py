@@ -12,12 +12,13 @@ from .stats import aggregate_rl_stats  # noqa: F401
 from .data import collate_packed, create_sentinel_batch, create_sentinel_example  # noqa: F401
 from .advantage import filter_zero_advantage_groups, populate_rl_data, prepare_rl_fields  # noqa: F401
 from .lm_head import FusedLMHead, install_fused_lm_head, lmhead_logprobs  # noqa: F401
-from .rl import rl_step  # noqa: F401
+from .rl import rl_step, rl_step_async  # noqa: F401
+from .metrics import StepMetrics  # noqa: F401
 from . import weight_update  # noqa: F401
 from . import host_step  # noqa: F401
 
 __all__ = [
     "RLConfig", "RL_DATA_COLUMNS", "linear_decay_coef", "PipelineBatchEncoding", "aggregate_rl_stats", "collate_packed",
     "create_sentinel_batch", "create_sentinel_example", "populate_rl_data", "prepare_rl_fields",
-    "filter_zero_advantage_groups", "FusedLMHead", "install_fused_lm_head", "lmhead_logprobs", "rl_step", "weight_update", "host_step",
+    "filter_zero_advantage_groups", "FusedLMHead", "install_fused_lm_head", "lmhead_logprobs", "rl_step", "rl_step_async", "StepMetrics", "weight_update", "host_step",
 ]

@@ -21,6 +21,9 @@ M_COUNT = 40  # B200GRPO_M_COUNT
  M_CLAMP_NEW_OLD, M_TOKEN_WEIGHT, M_VALUE_MEAN, M_VALUE_LOSS, M_VALUE_MSE, M_MAX_REWARD, M_MIN_REWARD, M_MAX_ADV,
  M_MIN_ADV, M_MAX_KL, M_MIN_KL, M_MAX_TW, M_MIN_TW, M_MAX_VALUE, M_MIN_VALUE, M_FLAGS) = range(36)
 F_NEW_LP_NONFINITE, F_REF_NEW_NONFINITE, F_KL_NONFINITE, F_LOSS_NONFINITE, F_GROUP_TOKENS_LE0 = 1, 2, 4, 8, 16
+STAT_SUM, STAT_MIN, STAT_MAX = 0, 1, 2                                    # B200GRPO_STAT_*
+STAT_KL_COEF, STAT_ENTROPY_COEF, STAT_INPUT_SIZE = -1, -2, -3
+STATS_MAX = 64
 
 
 class B200GrpoError(RuntimeError):
@@ -45,7 +48,7 @@ class HostBatch(C.Structure):
         "group_tokens", "num_labels", "overflow")]
 
 
-_p, _i, _i64, _f, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
+_p, _i, _i64, _f, _sz, _d = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t, C.c_double
 
 # name -> (restype, argtypes); mirrors include/b200grpo.h one to one
 SIGNATURES = {
@@ -72,6 +75,8 @@ SIGNATURES = {
     "b200grpo_rl_step_host_grad_hidden": (_p, [_p, _i, _i, _i]),
     "b200grpo_rl_step_host": (_i, [C.POINTER(HostBatch), _i, _i, _i, _p, _i64, _f, C.POINTER(LossCfg), _p, _p, _i, _i, _p, _p,
                                    _sz, _p]),
+    "b200grpo_metrics_reset": (_i, [_p, _i, _p, _p]),
+    "b200grpo_metrics_accumulate": (_i, [_p, _p, _p, _i, _d, _d, _d, _d, _i, _p, _p]),
     "b200grpo_profile_enable": (_i, [_i]),
     "b200grpo_profile_read": (_i, [_p, _p, _i]),
     "b200grpo_gemm_bf16": (_i, [_p, _i64, _i, _p, _i64, _i, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),

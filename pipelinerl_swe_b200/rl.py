@@ -115,8 +115,8 @@ def grpo_loss_from_logprobs(lp_ent: torch.Tensor, b: dict, cfg: LossCfg, values:
     return loss, sink["metrics"]
 
 
-def rl_step(model, batch, current_step: int, max_step: int, config) -> tuple[torch.Tensor, dict[str, float]]:
-    """Perform a single RL step; see module docstring.  Handles packed and unpacked batches."""
+def _forward_loss(model, batch, current_step: int, max_step: int, config):
+    """Shared by rl_step / rl_step_async: model forward through the fused lm_head + K3.  No host sync."""
     b = _batch_dict(batch)
     has_value_head = hasattr(model, "value_head")
     cfg = make_loss_cfg(config, current_step, max_step, b["is_packed"], has_value_head)
@@ -138,8 +138,34 @@ def rl_step(model, batch, current_step: int, max_step: int, config) -> tuple[tor
     values = outputs.value.float().contiguous() if has_value_head else None
     tb = {k: (v.contiguous() if isinstance(v, torch.Tensor) else v) for k, v in b.items()}
     loss, metrics = grpo_loss_from_logprobs(lp_ent.float(), tb, cfg, values)
-    m = metrics.tolist()  # the one host sync of the step
     coefs = (linear_decay_coef(current_step, max_step, config.kl_coef, config.final_kl_coef),
              linear_decay_coef(current_step, max_step, config.entropy_bonus, config.final_entropy_bonus))
-    stats = stats_from_metrics(m, cfg, b["input_ids"].numel(), has_value_head, coefs)
+    return loss, metrics, cfg, coefs, b["input_ids"].numel(), has_value_head
+
+
+def rl_step(model, batch, current_step: int, max_step: int, config) -> tuple[torch.Tensor, dict[str, float]]:
+    """Perform a single RL step; see module docstring.  Handles packed and unpacked batches."""
+    loss, metrics, cfg, coefs, input_size, has_value_head = _forward_loss(model, batch, current_step, max_step, config)
+    m = metrics.tolist()  # the one host sync of the step
+    stats = stats_from_metrics(m, cfg, input_size, has_value_head, coefs)
     return loss, stats
+
+
+def batch_sequence_count(batch) -> int:
+    """finetune_loop.py:266-276 (``get_batch_sequence_count``)."""
+    get = (lambda k: batch.get(k)) if isinstance(batch, dict) else (lambda k: getattr(batch, k, None))
+    if get("position_ids") is not None and get("seq_boundaries") is not None:
+        return len(get("seq_boundaries")) - (1 if not get("padding") else 2)
+    return int(get("input_ids").shape[0])
+
+
+def rl_step_async(model, batch, current_step: int, max_step: int, config, step_metrics, record: bool = True) -> torch.Tensor:
+    """``rl_step`` without its host sync: the stats go into ``step_metrics`` (metrics.StepMetrics) on the device.
+
+    Replaces ``loss, m = rl_step(...); for k, v in m.items(): rl_metrics[k].append(v)`` of
+    finetune_loop.py:661-670; ``record=False`` is the sentinel-batch branch (:664-666) -- the caller still
+    multiplies the loss by 0.  The reference's asserts fire at ``step_metrics.reduce``.
+    """
+    loss, metrics, cfg, coefs, input_size, _ = _forward_loss(model, batch, current_step, max_step, config)
+    step_metrics.add(metrics, coefs[0], coefs[1], input_size, batch_sequence_count(batch), record)
+    return loss

@@ -225,3 +225,54 @@ def test_rl_step_host_entry_matches_piecewise():
     assert_stats_close(stats2, stats, rtol=1e-6, atol=1e-7)
     assert torch.equal(step.grad_weight, model.lm_head.weight.grad)
     assert torch.equal(step.grad_hidden_host.view(torch.int16)[:-1], model.hidden.grad[0].cpu().view(torch.int16)[:-1])
+
+
+# ---------------------------------------------------------------------------------------------
+# step metrics accumulator: device accumulation == list appends + aggregate_rl_stats
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("value_head", [False, True])
+def test_step_metrics_match_reference_aggregation(value_head):
+    from collections import defaultdict
+    from helpers import StubLM, near_policy_logprobs, synthetic_packed_batch
+    from pipelinerl_swe_b200 import RLConfig, StepMetrics, aggregate_rl_stats, rl_step, rl_step_async
+    d = torch.device("cuda:0")
+    H, V = 128, 2048 + 8
+    cfg = RLConfig(policy_loss="ppo", batch_size=4, kl_coef=0.05, final_kl_coef=0.02, entropy_bonus=0.01, final_entropy_bonus=0.01,
+                   temperature=0.9)
+    sm = StepMetrics(d, has_values=value_head)
+    lists, losses = defaultdict(list), []
+    micro = [([40, 25, 60], 3), ([30, 30], 4), ([17, 90, 11, 9], 5)]
+    for lens, seed in micro:
+        T = sum(lens)
+        model = StubLM(H, V, T, seed=seed, value_head=value_head).to(d)
+        batch = synthetic_packed_batch(lens, V, seed=seed)
+        batch = near_policy_logprobs(batch, model.hidden.detach().cpu()[0], model.lm_head.weight.detach().cpu(), cfg.temperature, seed)
+        batch["seq_boundaries"] = torch.tensor([0] + list(np.cumsum(lens)))
+        bd = {k: (v.to(d) if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+        loss, stats = rl_step(model, bd, 2, 10, cfg)
+        for k, v in stats.items():
+            lists[k].append(v)
+        loss2 = rl_step_async(model, bd, 2, 10, cfg, sm)
+        losses.append((loss.item(), loss2.item()))
+    # a sentinel batch advances the counters only; an unlabeled micro-batch contributes input_size only
+    model = StubLM(H, V, 50, seed=9, value_head=value_head).to(d)
+    batch = synthetic_packed_batch([50], V, seed=9)
+    batch["seq_boundaries"] = torch.tensor([0, 50])
+    bd = {k: (v.to(d) if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+    rl_step_async(model, bd, 2, 10, cfg, sm, record=False)
+    bd["labels"] = torch.full_like(bd["labels"], -100)
+    _, stats = rl_step(model, bd, 2, 10, cfg)
+    assert list(stats) == ["input_size"]
+    lists["input_size"].append(stats["input_size"])
+    rl_step_async(model, bd, 2, 10, cfg, sm)
+    want = aggregate_rl_stats(lists, num_samples=9)
+    got, counters = sm.reduce(9)
+    assert all(a == b for a, b in losses)
+    assert counters == {"labelled_micro_batches": 3, "micro_batches": 5, "samples": 3 + 2 + 4 + 1 + 1}
+    assert set(got) == set(want)
+    for k, w in want.items():
+        assert abs(got[k] - w) <= 1e-5 * max(1.0, abs(w)), (k, got[k], w)
+    # reduce() reset the accumulator
+    got2, counters2 = sm.reduce(9)
+    assert got2 == {} and counters2["micro_batches"] == 0

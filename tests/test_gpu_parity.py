@@ -304,3 +304,48 @@ def test_lmhead_bwd_tile_variants_agree(dh_big, dw_big, tail):
         _abi.set_tunable("tail_split", 1)
     assert _rel(gh, hr.grad) < GRAD_RTOL
     assert _rel(gw - 0.5, wr.grad) < GRAD_RTOL
+
+
+class _EmbedLM(torch.nn.Module):
+    """Token-wise 'trunk' (embedding lookup) + lm_head: hidden depends on the ids, so packing / offsets are exercised."""
+
+    def __init__(self, H, V, seed=0):
+        super().__init__()
+        g = torch.Generator().manual_seed(seed)
+        self.embed = torch.nn.Embedding(V, H, dtype=torch.bfloat16)
+        self.lm_head = torch.nn.Linear(H, V, bias=False, dtype=torch.bfloat16)
+        with torch.no_grad():
+            self.embed.weight.copy_(torch.randn(V, H, generator=g).bfloat16())
+            self.lm_head.weight.copy_((torch.randn(V, H, generator=g) * 0.05).bfloat16())
+        self.seen_rows = []
+
+    def forward(self, input_ids=None, attention_mask=None, position_ids=None, **kw):
+        import types
+        self.seen_rows.append((input_ids.shape[1], position_ids[0].tolist()))
+        return types.SimpleNamespace(logits=self.lm_head(self.embed(input_ids)))
+
+
+def test_ref_logprob_annotation_matches_fp32_log_softmax():
+    """preprocess.py:73-91 semantics: ref_logprobs[j] = log p(completion token j | everything before it), T = 1."""
+    from pipelinerl_swe_b200.ref_logprobs import annotate_traces_with_ref_logprobs
+    H, V = 256, 5000 + 8
+    model = _EmbedLM(H, V).to(_dev())
+    g = torch.Generator().manual_seed(4)
+    traces = []
+    for n, c in [(30, 10), (200, 199), (64, 1), (150, 70), (90, 33), (400, 20)]:
+        traces.append({"input_ids": torch.randint(0, V, (n,), generator=g).tolist(), "logprobs": [0.0] * c})
+    annotate_traces_with_ref_logprobs(model, traces, max_tokens=300)
+    assert [r[0] for r in model.seen_rows] == [294, 240, 400]          # 30+200+64 | 150+90 | 400 (alone, over the cap)
+    assert model.seen_rows[0][1][:31] == list(range(30)) + [0]          # position ids restart per trace
+    W, E = model.lm_head.weight.detach().float().cpu(), model.embed.weight.detach().float().cpu()
+    for tr in traces:
+        ids = torch.tensor(tr["input_ids"])
+        logp = torch.log_softmax(E[ids] @ W.t(), -1)
+        c = len(tr["logprobs"])
+        want = logp[len(ids) - c - 1: len(ids) - 1].gather(1, ids[len(ids) - c:, None]).squeeze(1)
+        got = torch.tensor(tr["ref_logprobs"])
+        assert got.shape == want.shape
+        assert float((got - want).abs().max()) <= LP_RTOL * float(want.abs().max())
+    assert isinstance(model.lm_head, torch.nn.Module) and model.training   # mode restored
+    with pytest.raises(ValueError):
+        annotate_traces_with_ref_logprobs(model, [{"input_ids": [1, 2], "logprobs": [0.0, 0.0]}])

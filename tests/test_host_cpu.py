@@ -166,3 +166,15 @@ def test_plan_transfers_covers_every_parameter_once():
     assert sorted(seen) == list(range(len(infos)))
     assert ("direct", 1) in plan and ("direct", 3) in plan and ("direct", 4) in plan
     assert [k for k, _ in plan].count("bucket") == 1 and plan[0] == ("bucket", [0, 2, 5, 6])
+
+
+def test_ref_logprob_pack_plan():
+    from pipelinerl_swe_b200.ref_logprobs import completion_spans, plan_packs
+    assert plan_packs([30, 200, 64, 150, 90, 400], 300) == [[0, 1, 2], [3, 4], [5]]
+    assert plan_packs([300, 1, 299], 300) == [[0], [1, 2]]
+    assert plan_packs([], 10) == []
+    with pytest.raises(ValueError):
+        plan_packs([3, 0], 10)
+    assert completion_spans([{"input_ids": [1, 2, 3], "logprobs": [0.1]}]) == [(3, 1)]
+    with pytest.raises(ValueError):
+        completion_spans([{"input_ids": [1, 2], "logprobs": [0.1, 0.2]}])

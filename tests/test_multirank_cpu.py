@@ -98,6 +98,71 @@ def _weight_update_worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
+def _fake_micro_batch_stats(rank, i, keys):
+    """One micro-batch's stats dict as rl_step would return it (values are arbitrary but rank/step specific)."""
+    g = torch.Generator().manual_seed(1000 * rank + i)
+    d = {k: float(torch.randn(1, generator=g)) * 3 for k in keys}
+    d["num_output_tokens_sum"] = float(100 + 7 * i + rank)
+    d["input_size"] = 4096.0
+    if rank == 1 and i == 1:
+        d["kl"] = float("nan")            # dropped by gather_rl_metrics (finetune_loop.py:85)
+        d["max_kl"] = float("inf")
+    if rank == 0 and i == 2:
+        d = {"input_size": 4096.0}        # micro-batch without labels (rl/__init__.py:195)
+    return d
+
+
+def _metrics_worker(rank, world, port, q):
+    """StepMetrics' exchange + combine + finalize == the reference's all_gather_object + aggregate_rl_stats."""
+    _init(rank, world, port)
+    from collections import defaultdict
+    from pipelinerl_swe_b200 import metrics as M
+    from pipelinerl_swe_b200.stats import aggregate_rl_stats
+    keys, _, kinds = M.stat_layout(has_values=True)
+    K = len(keys)
+    n_micro = 3 + rank                                  # ranks see different numbers of micro-batches
+    # what the reference does: dict of lists per rank, pickled all-gather, finite filter, substring-keyed reduction
+    lists = defaultdict(list)
+    for i in range(n_micro):
+        for k, v in _fake_micro_batch_stats(rank, i, keys).items():
+            lists[k].append(v)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, dict(lists))
+    merged = defaultdict(list)
+    for d in gathered:
+        for k, v in d.items():
+            merged[k].extend([x for x in v if torch.isfinite(torch.tensor(x))])
+    num_samples = 11
+    want = aggregate_rl_stats(merged, num_samples)
+    # the accumulator the device kernel maintains, built here on the host (the kernel itself is covered on the GPU)
+    acc = torch.zeros(2 * K + 4, dtype=torch.float64)
+    for j, kd in enumerate(kinds):
+        acc[j] = float("inf") if kd == M.KIND_MIN else float("-inf") if kd == M.KIND_MAX else 0.0
+    for i in range(n_micro):
+        d = _fake_micro_batch_stats(rank, i, keys)
+        for j, k in enumerate(keys):
+            if k in d and torch.isfinite(torch.tensor(d[k])):
+                acc[j] = min(acc[j], d[k]) if kinds[j] == M.KIND_MIN else max(acc[j], d[k]) if kinds[j] == M.KIND_MAX else acc[j] + d[k]
+                acc[K + j] += 1
+        acc[2 * K + 1] += float(len(d) > 1)
+        acc[2 * K + 2] += 1
+        acc[2 * K + 3] += 5
+    got, counters = M.reduce_accumulators(acc, keys, kinds, num_samples)
+    ok = set(got) == set(want)
+    for k in want:
+        ok = ok and abs(got[k] - want[k]) <= 1e-5 * max(1.0, abs(want[k]))
+    ok = ok and counters == {"labelled_micro_batches": 6, "micro_batches": 7, "samples": 35}
+    # a flag raised on one rank fires the reference's assert on every rank
+    acc[2 * K] = 8.0 if rank == 1 else 0.0
+    try:
+        M.reduce_accumulators(acc, keys, kinds, num_samples)
+        ok = False
+    except AssertionError as e:
+        ok = ok and "Non-finite loss" in str(e)
+    q.put((rank, ok, sorted(got.items())))
+    dist.destroy_process_group()
+
+
 def _guard(worker, rank, world, port, q):
     try:
         worker(rank, world, port, q)
@@ -132,6 +197,23 @@ def test_weight_update_plan_world2():
     res = _run(_weight_update_worker)
     assert all(ok for _, ok, _ in res)
     assert res[0][2] == res[1][2]
+
+
+def test_step_metrics_reduce_world2():
+    res = _run(_metrics_worker)
+    assert all(ok for _, ok, _ in res)
+    assert res[0][2] == res[1][2]            # every rank ends with the same averages
+
+
+def test_stat_kinds_follow_reference_substring_rule():
+    from pipelinerl_swe_b200 import metrics as M
+    keys, slots, kinds = M.stat_layout(True)
+    by = dict(zip(keys, kinds))
+    assert by["loss"] == M.KIND_SUM and by["max_loss"] == M.KIND_MAX and by["min_loss"] == M.KIND_MIN
+    assert by["ratio_new_old_sum"] == M.KIND_SUM and by["num_output_tokens_sum"] == M.KIND_SUM
+    assert by["value_min"] == M.KIND_MIN and by["value_max"] == M.KIND_MAX and by["value_loss"] == M.KIND_MEAN
+    assert by["policy_loss"] == M.KIND_MEAN and by["kl"] == M.KIND_MEAN and by["input_size"] == M.KIND_MEAN
+    assert len(keys) == 39 and len(M.stat_layout(False)[0]) == 34
 
 
 def test_shard_range_covers_vocab():
