@@ -256,6 +256,27 @@ int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B
                        size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------
+ * Packed-batch ingest.  Replaces pipelinerl/finetune/data.py:215-279
+ * (collate_packed materialising eleven [1,T] host tensors, 60 B per token) + their H2D copies
+ * (finetune_loop.py:109) + the per-token broadcast of the per-rollout advantage columns
+ * (rl/__init__.py:481-499).  Wire form, already on the device (one H2D copy of one pinned
+ * buffer): per token input_ids i32, labels i32 (-100 = masked, already masked at every rollout
+ * start after the first as data.py:260-261 does), old / ref log-probs f32; per rollout
+ * seq_boundaries i32[n_seq + 1] (token offsets, non-decreasing, [0] = 0, [n_seq] = T) and
+ * seq_scalars f32[5][n_seq] = rewards, advantages, group_tokens, num_labels, overflow.
+ * Output: the eleven tensors of the batch (i64 ids / labels / attention_mask (= 1) /
+ * position_ids (restart per rollout), f32 columns), each T long.
+ * ------------------------------------------------------------------------------------- */
+typedef struct b200grpo_packed_out {
+  int64_t *input_ids, *labels, *attention_mask, *position_ids;
+  float *rewards, *advantages, *ref_logprobs, *old_logprobs, *group_tokens, *num_labels, *overflow;
+} b200grpo_packed_out;
+int b200grpo_expand_packed(const int32_t* input_ids, const int32_t* labels, const float* old_logprobs,
+                           const float* ref_logprobs, const int32_t* seq_boundaries,
+                           const float* seq_scalars, int T, int n_seq, const b200grpo_packed_out* out,
+                           void* stream);
+
+/* ---------------------------------------------------------------------------------------
  * Step-metrics accumulator.  Replaces, per micro-batch, the python
  * `rl_metrics[k].append(v)` of pipelinerl/finetune_loop.py:669-670 and, per optimizer step, the
  * pickled all_gather_object of :62-87 + aggregate_rl_stats (rl/utils.py:8-22): every

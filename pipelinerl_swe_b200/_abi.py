@@ -48,6 +48,13 @@ class HostBatch(C.Structure):
         "group_tokens", "num_labels", "overflow")]
 
 
+class PackedOut(C.Structure):
+    """b200grpo_packed_out"""
+    _fields_ = [(n, C.c_void_p) for n in (
+        "input_ids", "labels", "attention_mask", "position_ids", "rewards", "advantages", "ref_logprobs", "old_logprobs",
+        "group_tokens", "num_labels", "overflow")]
+
+
 _p, _i, _i64, _f, _sz, _d = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t, C.c_double
 
 # name -> (restype, argtypes); mirrors include/b200grpo.h one to one
@@ -75,6 +82,7 @@ SIGNATURES = {
     "b200grpo_rl_step_host_grad_hidden": (_p, [_p, _i, _i, _i]),
     "b200grpo_rl_step_host": (_i, [C.POINTER(HostBatch), _i, _i, _i, _p, _i64, _f, C.POINTER(LossCfg), _p, _p, _i, _i, _p, _p,
                                    _sz, _p]),
+    "b200grpo_expand_packed": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, C.POINTER(PackedOut), _p]),
     "b200grpo_metrics_reset": (_i, [_p, _i, _p, _p]),
     "b200grpo_metrics_accumulate": (_i, [_p, _p, _p, _i, _d, _d, _d, _d, _i, _p, _p]),
     "b200grpo_profile_enable": (_i, [_i]),
@@ -113,7 +121,7 @@ def check(code: int) -> None:
 
 PROF_TAGS = {1: "fwd_gemm_stats", 2: "fwd_merge", 3: "finalize", 4: "token_loss", 5: "bwd_recompute_dlogits", 6: "bwd_dH_gemm",
              7: "bwd_dW_gemm", 8: "gemm", 9: "group_advantage", 10: "bucket", 11: "segments", 12: "fused_logits_gemm",
-             13: "dlogits_pass", 14: "splitk_reduce"}
+             13: "dlogits_pass", 14: "splitk_reduce", 15: "ingest_expand"}
 
 
 def profile_enable(capacity: int) -> None:

@@ -107,3 +107,29 @@ class StubLM(torch.nn.Module):
         if hasattr(self, "values"):
             out.value = self.values
         return out
+
+
+class StubTokenizer:
+    eos_token_id = 2
+    padding_side = "right"
+
+
+def synthetic_rollout_examples(lens, V, seed=0, n_prompt=3, per_token_rewards=False):
+    """Examples as populate_rl_data leaves them (per-token lists; per-rollout columns constant inside a rollout)."""
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for i, n in enumerate(lens):
+        ids = torch.randint(3, V, (n,), generator=g).tolist()
+        k = min(n_prompt, n)
+        labels = [-100] * k + ids[k:]
+        lp = lambda: [0.0] * k + (-(torch.rand(n - k, generator=g) * 3)).tolist()  # noqa: E731
+        rew = float(torch.randint(0, 2, (1,), generator=g))
+        rewards = [rew] * n
+        if per_token_rewards and n > 1:
+            rewards[-1] = rew + 0.5
+        out.append({
+            "input_ids": ids, "labels": labels, "attention_mask": [1] * n, "model_version": 3 + (i % 2),
+            "rewards": rewards, "advantages": [float(torch.randn(1, generator=g))] * n, "old_logprobs": lp(), "ref_logprobs": lp(),
+            "group_tokens": [float(37 + i)] * n, "num_labels": [float(n - k)] * n, "overflow": [float(i % 3 == 2)] * n,
+        })
+    return out

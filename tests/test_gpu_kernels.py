@@ -276,3 +276,45 @@ def test_step_metrics_match_reference_aggregation(value_head):
     # reduce() reset the accumulator
     got2, counters2 = sm.reduce(9)
     assert got2 == {} and counters2["micro_batches"] == 0
+
+
+# ---------------------------------------------------------------------------------------------
+# packed-batch ingest: wire form + device expansion == collate_packed + to_device, bit for bit
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("lens,sp", [([5, 1, 9, 0, 4], 1), ([5, 1, 9, 0, 4], 8), ([1], 1), ([700, 33, 1200, 2, 513], 4),
+                                      ([3] * 4000, 1)])
+def test_packed_ingest_bit_exact(lens, sp):
+    from helpers import StubTokenizer, synthetic_rollout_examples
+    from pipelinerl_swe_b200 import collate_packed
+    from pipelinerl_swe_b200.ingest import ingest_packed, pack_rollouts
+    ex = synthetic_rollout_examples(lens, 152064, seed=len(lens) + sp)
+    want = collate_packed(copy.deepcopy(ex), StubTokenizer(), sp).to_device(_dev())
+    wire = pack_rollouts(copy.deepcopy(ex), StubTokenizer(), sp)
+    got = wire.to_device(_dev())
+    torch.cuda.synchronize()
+    for k in ("input_ids", "labels", "attention_mask", "position_ids", "rewards", "advantages", "ref_logprobs", "old_logprobs",
+              "group_tokens", "num_labels", "overflow", "seq_boundaries"):
+        a, b = getattr(got, k), getattr(want, k)
+        assert a.dtype == b.dtype and a.shape == b.shape, k
+        assert torch.equal(a, b), k
+    assert (got.is_packed, got.padding, got.model_version) == (want.is_packed, want.padding, want.model_version)
+    T = want.input_ids.shape[1]
+    assert wire.nbytes < 0.3 * 60 * T + 30 * len(lens) + 200       # vs the reference's 60 B per token
+    # per-token rewards cannot take the wire form: same result through the fallback
+    ex2 = synthetic_rollout_examples(lens, 152064, seed=1, per_token_rewards=True)
+    want2 = collate_packed(copy.deepcopy(ex2), StubTokenizer(), sp).to_device(_dev())
+    got2 = ingest_packed(copy.deepcopy(ex2), StubTokenizer(), sp, _dev())
+    assert torch.equal(got2.rewards, want2.rewards) and torch.equal(got2.labels, want2.labels)
+
+
+def test_rl_step_on_ingested_batch_equals_collated_batch():
+    from helpers import StubTokenizer, synthetic_rollout_examples
+    from pipelinerl_swe_b200 import RLConfig, collate_packed, rl_step
+    from pipelinerl_swe_b200.ingest import ingest_packed
+    lens, H, V = [120, 64, 200, 77], 128, 4096
+    ex = synthetic_rollout_examples(lens, V, seed=8, n_prompt=10)
+    model = StubLM(H, V, sum(lens), seed=2).to(_dev())
+    cfg = RLConfig(batch_size=4, kl_coef=0.1, final_kl_coef=0.1)
+    l1, s1 = rl_step(model, collate_packed(copy.deepcopy(ex), StubTokenizer(), 1).to_device(_dev()), 0, 1, cfg)
+    l2, s2 = rl_step(model, ingest_packed(copy.deepcopy(ex), StubTokenizer(), 1, _dev()), 0, 1, cfg)
+    assert l1.item() == l2.item() and s1 == s2

@@ -178,3 +178,31 @@ def test_ref_logprob_pack_plan():
     assert completion_spans([{"input_ids": [1, 2, 3], "logprobs": [0.1]}]) == [(3, 1)]
     with pytest.raises(ValueError):
         completion_spans([{"input_ids": [1, 2], "logprobs": [0.1, 0.2]}])
+
+
+def test_packed_wire_layout_matches_collate_packed():
+    """Host side of the 8f-1 ingest: the wire sections hold what collate_packed would put in its tensors."""
+    from helpers import StubTokenizer, synthetic_rollout_examples
+    from pipelinerl_swe_b200 import collate_packed
+    from pipelinerl_swe_b200.ingest import SEQ_COLUMNS, NonUniformColumns, pack_rollouts
+    ex = synthetic_rollout_examples([5, 1, 9, 0, 4], 100, seed=3)
+    for sp in (1, 8):
+        want = collate_packed(copy.deepcopy(ex), StubTokenizer(), sp)
+        wire = pack_rollouts(copy.deepcopy(ex), StubTokenizer(), sp, pin=False)
+        T = want.input_ids.shape[1]
+        assert wire.T == T and wire.padding == want.padding and wire.model_version == want.model_version
+        assert wire.n_seq == len(want.seq_boundaries) - 1
+        assert torch.equal(wire.section("input_ids").long(), want.input_ids[0])
+        assert torch.equal(wire.section("labels").long(), want.labels[0])
+        assert torch.equal(wire.section("old_logprobs"), want.old_logprobs[0])
+        assert torch.equal(wire.section("ref_logprobs"), want.ref_logprobs[0])
+        assert torch.equal(wire.section("seq_boundaries"), want.seq_boundaries)
+        scal = wire.section("seq_scalars").reshape(5, wire.n_seq)
+        b = want.seq_boundaries.tolist()
+        for r, col in enumerate(SEQ_COLUMNS):
+            for s in range(wire.n_seq):
+                if b[s + 1] > b[s]:
+                    assert scal[r, s] == getattr(want, col)[0, b[s]]
+        assert wire.nbytes <= 16 * T + 24 * wire.n_seq + 6 * 16 + 4
+    with pytest.raises(NonUniformColumns):
+        pack_rollouts(synthetic_rollout_examples([5, 7], 100, per_token_rewards=True), StubTokenizer(), 1, pin=False)
