@@ -246,10 +246,11 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t 
       float4* o4 = reinterpret_cast<float4*>(o);
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
-        float4 x = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
-                               __uint_as_float(v[4 * q + 3]));
-        if (p.accumulate) { const float4 y = o4[q]; x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w; }
-        o4[q] = x;
+        const float4 x = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
+                                     __uint_as_float(v[4 * q + 3]));
+        // accumulate: the add happens in L2 (every element is touched once per launch, so the result does not
+        // depend on ordering); the SM never waits for the old gradient to come back
+        if (p.accumulate) ptx::red_add_v4_f32(o4 + q, x); else o4[q] = x;
       }
     } else {
 #pragma unroll

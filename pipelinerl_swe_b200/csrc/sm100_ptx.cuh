@@ -91,6 +91,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ta
   mbar_wait_timeout(bar, parity, tag);
 }
 
+// ---- global reductions -------------------------------------------------------------------
+// four f32 adds resolved in L2, no value returned (fire and forget)
+__device__ __forceinline__ void red_add_v4_f32(float4* addr, float4 x) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(x.x), "f"(x.y), "f"(x.z), "f"(x.w) : "memory");
+}
+
 // ---- TMA ------------------------------------------------------------------------------
 __device__ __forceinline__ void prefetch_tensormap(const void* desc) {
   asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)desc) : "memory");

@@ -278,6 +278,7 @@ def probe_bigm_sustained(a_mn, b_mn, M, N, K, group_m, ks_small, ks_big, secs=1.
     res = [run(ours(0, ks_small), f"128row/ks{ks_small}"), run(ours(1, ks_big), f"256row/ks{ks_big}"),
            run(lambda: torch.matmul(A, Bt, out=out), "cublas"),
            run(ours(1, ks_big, max(1, group_m // 2)), f"256row/ks{ks_big}/g{max(1, group_m // 2)}"),
+           run(ours(0, ks_big), f"128row/ks{ks_big}"),
            run(ours(0, ks_small), f"128row/ks{ks_small}")]
     return True, " | ".join(res)
 
