@@ -56,7 +56,11 @@ __global__ void __launch_bounds__(TL_THREADS) token_loss_kernel(const TokenLossA
     for (int u = 0; u < TL_UNROLL; ++u) {
       const long long i = base + u * stride;
       if (i >= n) break;
-      const int r = (int)(i / Ls), t = (int)(i - (long long)r * Ls);
+      int r = 0, t = (int)i;                         // packed rows (rows == 1) need no division
+      if (a.rows > 1) {
+        if (n < (1ll << 31)) { r = (int)((unsigned)i / (unsigned)Ls); t = (int)i - r * Ls; }
+        else { r = (int)(i / Ls); t = (int)(i - (long long)r * Ls); }
+      }
       const long long j = (long long)r * L + t + 1;  // shifted view [:,1:]
       const float lp = a.logprob[i], ent = a.entropy[i];
       const bool m = a.labels[j] != -100;
@@ -125,31 +129,33 @@ __global__ void __launch_bounds__(TL_THREADS) token_loss_kernel(const TokenLossA
         }
         if (m) { ext[8] = fmaxf(ext[8], v_pred); ext[9] = fminf(ext[9], v_pred); }
       }
-      if (m) {
+      if (m) {  // masked-out tokens contribute exact zeros to every sum below (masked_term): skip them
         s[B200GRPO_M_N_MASKED] += 1.0;
         ext[0] = fmaxf(ext[0], rew); ext[1] = fminf(ext[1], rew);
         ext[2] = fmaxf(ext[2], adv); ext[3] = fminf(ext[3], adv);
         ext[4] = fmaxf(ext[4], kl);  ext[5] = fminf(ext[5], kl);
         ext[6] = fmaxf(ext[6], tw);  ext[7] = fminf(ext[7], tw);
+        // x / num_labels as x * (1 / num_labels): one division per token instead of seventeen (<= 1 ulp apart)
+        const float inv_nl = 1.0f / nl;
+        s[B200GRPO_M_REWARD] += (double)masked_term(rew * inv_nl, true);
+        s[B200GRPO_M_ENTROPY] += (double)masked_term(ent * inv_nl, true);
+        s[B200GRPO_M_OLD_LP] += (double)masked_term(old * inv_nl, true);
+        s[B200GRPO_M_NEW_LP] += (double)masked_term(lp * inv_nl, true);
+        s[B200GRPO_M_REF_LP] += (double)masked_term(ref * inv_nl, true);
+        s[B200GRPO_M_ADVANTAGE] += (double)masked_term(adv * inv_nl, true);
+        s[B200GRPO_M_KL] += (double)masked_term(kl * inv_nl, true);
+        s[B200GRPO_M_POLICY] += (double)masked_term(policy * inv_nl, true);
+        s[B200GRPO_M_SURR1] += (double)masked_term(surr1 * inv_nl, true);
+        s[B200GRPO_M_SURR2] += (double)masked_term(surr2 * inv_nl, true);
+        s[B200GRPO_M_RATIO] += (double)masked_term(ratio * inv_nl, true);
+        s[B200GRPO_M_RATIO_SUM] += (double)masked_term(ratio, true);
+        s[B200GRPO_M_RATIO_SQ_SUM] += (double)masked_term(ratio * ratio, true);
+        s[B200GRPO_M_RATIO_REF_NEW] += (double)masked_term(expf(d_rn) * inv_nl, true);
+        s[B200GRPO_M_RATIO_REF_OLD] += (double)masked_term(expf(ref - old) * inv_nl, true);
+        s[B200GRPO_M_CLAMP_REF_NEW] += (double)masked_term(kl_clamped ? inv_nl : 0.f, true);
+        s[B200GRPO_M_CLAMP_NEW_OLD] += (double)masked_term(r_clamped ? inv_nl : 0.f, true);
+        s[B200GRPO_M_TOKEN_WEIGHT] += (double)masked_term(tw * inv_nl, true);
       }
-      s[B200GRPO_M_REWARD] += (double)masked_term(rew / nl, m);
-      s[B200GRPO_M_ENTROPY] += (double)masked_term(ent / nl, m);
-      s[B200GRPO_M_OLD_LP] += (double)masked_term(old / nl, m);
-      s[B200GRPO_M_NEW_LP] += (double)masked_term(lp / nl, m);
-      s[B200GRPO_M_REF_LP] += (double)masked_term(ref / nl, m);
-      s[B200GRPO_M_ADVANTAGE] += (double)masked_term(adv / nl, m);
-      s[B200GRPO_M_KL] += (double)masked_term(kl / nl, m);
-      s[B200GRPO_M_POLICY] += (double)masked_term(policy / nl, m);
-      s[B200GRPO_M_SURR1] += (double)masked_term(surr1 / nl, m);
-      s[B200GRPO_M_SURR2] += (double)masked_term(surr2 / nl, m);
-      s[B200GRPO_M_RATIO] += (double)masked_term(ratio / nl, m);
-      s[B200GRPO_M_RATIO_SUM] += (double)masked_term(ratio, m);
-      s[B200GRPO_M_RATIO_SQ_SUM] += (double)masked_term(ratio * ratio, m);
-      s[B200GRPO_M_RATIO_REF_NEW] += (double)masked_term(expf(d_rn) / nl, m);
-      s[B200GRPO_M_RATIO_REF_OLD] += (double)masked_term(expf(ref - old) / nl, m);
-      s[B200GRPO_M_CLAMP_REF_NEW] += (double)masked_term((kl_clamped ? 1.f : 0.f) / nl, m);
-      s[B200GRPO_M_CLAMP_NEW_OLD] += (double)masked_term((r_clamped ? 1.f : 0.f) / nl, m);
-      s[B200GRPO_M_TOKEN_WEIGHT] += (double)masked_term(tw / nl, m);
     }
   }
 

@@ -166,7 +166,8 @@ def group_advantage(row_reward: torch.Tensor, group_key: torch.Tensor, row_offse
         _req(token_rewards, torch.float64, "token_rewards")
     n_rows = row_reward.numel()
     total = int(row_offsets[-1].item()) if n_rows else 0
-    out = torch.empty(4, total, dtype=torch.float32, device=row_reward.device)
+    pitch = (total + 3) // 4 * 4  # 16-byte aligned columns -> vector stores in the expand kernel
+    out = torch.empty(4, pitch, dtype=torch.float32, device=row_reward.device)[:, :total]
     n = lib().b200grpo_group_advantage_workspace(n_rows, n_groups)
     ws = _workspace(row_reward.device, n)
     check(lib().b200grpo_group_advantage(row_reward.data_ptr(), group_key.data_ptr(), row_offsets.data_ptr(), n_labels.data_ptr(),
