@@ -377,9 +377,18 @@ def run_b200(args):
     algo_flops = 6.0 * (T - 1) * H * wl.Vloc
     achieved = algo_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     executed = 2.0 * (T - 1) * H * wl.Vloc * n_gemms / (gemm_only_ms * 1e-3) / 1e12 if gemm_only_ms > 0 else 0.0
+    traffic, traffic_note = None, "no ncu capture for this workload"
+    try:  # DRAM bytes of the step's kernels from the committed ncu capture (C3, saved mode, unsharded only)
+        tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01", "traffic.json")))
+        if tj["workload"] == f"{args.config}/{args.mode}/{args.parallelism}":
+            traffic = float(sum(tj["dram_bytes_per_launch"].values()))
+            traffic_note = ("dram__bytes_read+write summed over the step's four large kernels (one launch each per step), " + tj["source"]
+                            + "; algorithmic operand+output bytes of the same kernels: %.1f GB" % (sum(tj["algorithmic_bytes_per_launch"].values()) / 1e9))
+    except Exception:  # noqa: BLE001
+        pass
     roofline = {
         "bound": "tensor", "achieved": achieved, "peak": peaks["sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["sustained"],
-        "traffic": None, "peak_kind": f"bf16_tflops_sustained of {peaks['source']} (kernels timed inside a long step)",
+        "traffic": traffic, "traffic_note": traffic_note, "peak_kind": f"bf16_tflops_sustained of {peaks['source']} (kernels timed inside a long step)",
         "frac_of_burst_peak": achieved / peaks["burst"], "executed_tflops": executed, "gemm_ms_per_step": gemm_ms,
         "share_of_step": gemm_ms / ms_step if world == 1 else None,
         "kernels_ms_per_step": {k: round(v, 4) for k, v in sorted(per_tag.items())},
