@@ -304,6 +304,10 @@ int b200grpo_metrics_accumulate(const double* metrics, const int* slots, const i
  * name in {"two_cta","dh_ksplit","dh_group_m","dw_group_m","save_logits",...}; returns the previous value. */
 int b200grpo_set_tunable(const char* name, int value);
 
+/* Kernels launched by this library since it was loaded (every <<<>>> / cudaLaunchKernelEx it issues; copies
+ * and memsets are not counted).  bench.py differences it around the timed region for "gpu_launches". */
+uint64_t b200grpo_launch_count(void);
+
 /* Per-launch device timing (diagnostic, single-threaded): while enabled, every kernel group the
  * library launches is bracketed by CUDA events on its stream.  read() waits for the recorded
  * events, writes up to `capacity` (tag, milliseconds) pairs in launch order, clears the ring and

@@ -62,6 +62,7 @@ SIGNATURES = {
     "b200grpo_last_error": (C.c_char_p, []),
     "b200grpo_abi_version": (_i, []),
     "b200grpo_set_tunable": (_i, [C.c_char_p, _i]),
+    "b200grpo_launch_count": (C.c_uint64, []),
     "b200grpo_lmhead_fwd_workspace": (_sz, [_i, _i, _i]),
     "b200grpo_lmhead_saved_bytes": (_sz, [_i, _i, _i]),
     "b200grpo_lmhead_fwd": (_i, [_p, _i64, _p, _i64, _p, _i, _i, _i, _i64, _f, _p, _p, _p, _sz, _p]),
@@ -135,6 +136,10 @@ def profile_read(capacity: int = 4096) -> list[tuple[str, float]]:
     if n < 0:
         check(n)
     return [(PROF_TAGS.get(tags[i], str(tags[i])), float(ms[i])) for i in range(n)]
+
+
+def launch_count() -> int:
+    return int(lib().b200grpo_launch_count())
 
 
 def set_tunable(name: str, value: int) -> int:

@@ -14,6 +14,10 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static unsigned long long g_launches = 0;  // relaxed counter; exactness under concurrent host threads is not needed
+void count_launch(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
+unsigned long long launches_so_far() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
 static int g_sm_count = 0;
 
 int sm_count() {
@@ -102,6 +106,8 @@ extern "C" int b200grpo_profile_read(int32_t* tags_host, float* ms_host, int cap
 
 extern "C" const char* b200grpo_last_error(void) { return g_err; }
 extern "C" int b200grpo_abi_version(void) { return B200GRPO_ABI_VERSION; }
+
+extern "C" uint64_t b200grpo_launch_count(void) { return b200grpo::launches_so_far(); }
 
 extern "C" int b200grpo_set_tunable(const char* name, int value) {
   static const char* names[TUNE_COUNT] = {"fwd_splits", "two_cta", "gemm_stages", "watchdog_ms", "dh_ksplit", "dh_group_m", "dw_group_m", "save_logits", "fwd_group_m", "dw_group_n", "hint_resident", "hint_stream", "dh_big_m", "dw_big_m", "gemm_big_m", "tail_split", "dw_ksplit"};

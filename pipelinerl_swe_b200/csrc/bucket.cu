@@ -99,6 +99,7 @@ static int run_bucket(bool pack, void* const* ptrs, const int64_t* numel, const 
   const int64_t cap = (int64_t)sm_count() * 8;
   if (grid > cap) grid = cap;
   ProfScope ps(PROF_BUCKET, st);
+  count_launch();
   if (pack) bucket_kernel<true><<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
   else bucket_kernel<false><<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
   B200_CUDA_OK(cudaGetLastError());

@@ -40,6 +40,7 @@ enum { TUNE_FWD_SPLITS = 0, TUNE_TWO_CTA = 1, TUNE_GEMM_STAGES = 2, TUNE_WATCHDO
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 int sm_count();  // multiprocessors of the current device (cached)
+void count_launch(int n = 1);  // kernel launches issued by this library (b200grpo_launch_count)
 
 // ---- optional per-launch timing (b200grpo_profile_*): CUDA events on the launching stream ----
 enum { PROF_FWD_GEMM = 1, PROF_FWD_MERGE = 2, PROF_FINALIZE = 3, PROF_TOKEN_LOSS = 4, PROF_BWD_DLOGITS = 5,

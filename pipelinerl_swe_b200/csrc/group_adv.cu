@@ -133,6 +133,7 @@ extern "C" int b200grpo_group_advantage(const double* row_reward, const int32_t*
   cudaStream_t st = (cudaStream_t)stream;
   GroupStat* stats = (GroupStat*)workspace;
   ProfScope ps(PROF_ADVANTAGE, st);
+  if (n_groups > 0) count_launch();
   if (n_groups > 0)
     group_stats_kernel<<<ceil_div(n_groups, GS_WARPS), GS_WARPS * 32, 0, st>>>(row_reward, group_key, row_offsets, n_rows, n_groups, stats);
   const int vec_ok = (((uintptr_t)advantages | (uintptr_t)group_tokens | (uintptr_t)num_labels | (uintptr_t)overflow) & 15) == 0;
@@ -140,7 +141,7 @@ extern "C" int b200grpo_group_advantage(const double* row_reward, const int32_t*
   const int cap = sm_count() * 8;
   if (grid > cap) grid = cap;
   group_expand_kernel<<<grid, 256, 0, st>>>(row_reward, token_rewards, group_key, row_offsets, n_labels, has_eos, stats,
-                                            n_rows, divide_by_std, advantages, group_tokens, num_labels, overflow, vec_ok);
+                                            n_rows, divide_by_std, advantages, group_tokens, num_labels, overflow, vec_ok); count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }

@@ -55,7 +55,7 @@ extern "C" int b200grpo_expand_packed(const int32_t* input_ids, const int32_t* l
   if (T == 0) return B200GRPO_OK;
   ProfScope ps(PROF_INGEST, (cudaStream_t)stream);
   expand_packed_kernel<<<ceil_div(T, ING_THREADS), ING_THREADS, 0, (cudaStream_t)stream>>>(
-      input_ids, labels, old_logprobs, ref_logprobs, seq_boundaries, seq_scalars, T, n_seq, *out);
+      input_ids, labels, old_logprobs, ref_logprobs, seq_boundaries, seq_scalars, T, n_seq, *out); count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }

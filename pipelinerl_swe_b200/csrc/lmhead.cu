@@ -105,7 +105,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   attr[0].val.clusterDim.x = kCtas; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p)); count_launch();
   return 0;
 }
 
@@ -411,7 +411,7 @@ static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B,
   }
   if (tail) {
     dim3 grid((p.n_items - p.tail_first) / tail, p.tile_rows / TAIL_RED_ROWS);   // x: tail tiles
-    tail_reduce_kernel<<<grid, 256, 0, st>>>(p);
+    tail_reduce_kernel<<<grid, 256, 0, st>>>(p); count_launch();
     B200_CUDA_OK(cudaGetLastError());
   }
   if (ks > 1) {
@@ -419,7 +419,7 @@ static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B,
     long long grid = (quads + 255) / 256;
     const long long cap = (long long)sm_count() * 16;
     if (grid > cap) grid = cap;
-    splitk_reduce_kernel<<<(int)grid, 256, 0, st>>>((const float*)slab, ks, M, N, C, ldc, c_is_f32, accumulate);
+    splitk_reduce_kernel<<<(int)grid, 256, 0, st>>>((const float*)slab, ks, M, N, C, ldc, c_is_f32, accumulate); count_launch();
     B200_CUDA_OK(cudaGetLastError());
   }
   return 0;
@@ -478,7 +478,7 @@ extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* 
     if (e) return e;
   }
   ProfScope ps(PROF_FWD_MERGE, st);
-  fwd_merge_kernel<<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, p.n_blocks, M, (float4*)stats);
+  fwd_merge_kernel<<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, p.n_blocks, M, (float4*)stats); count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }
@@ -487,7 +487,7 @@ extern "C" int b200grpo_lmhead_finalize(const float* stats, int R, int M, float*
   if (int e = check_device_sm100()) return e;
   B200_REQUIRE(stats && logprob && entropy && R >= 1 && M >= 1, "lmhead_finalize: bad argument");
   ProfScope ps(PROF_FINALIZE, (cudaStream_t)stream);
-  finalize_kernel<<<ceil_div(M, 256), 256, 0, (cudaStream_t)stream>>>((const float4*)stats, R, M, logprob, entropy, lse);
+  finalize_kernel<<<ceil_div(M, 256), 256, 0, (cudaStream_t)stream>>>((const float4*)stats, R, M, logprob, entropy, lse); count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }
@@ -521,7 +521,7 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
     ProfScope ps(PROF_DLOGITS_EW, st);
     dim3 grid(ceil_div(M, DL_ROWS), ceil_div(Vloc, PANEL_W));
     dlogits_from_saved_kernel<<<grid, DL_THREADS, 0, st>>>(dlog, (const float4*)saved, M, Vloc, (const long long*)targets, v_offset, lse,
-                                                           entropy, coef_lp, coef_ent, grad_scale, inv_temperature);
+                                                           entropy, coef_lp, coef_ent, grad_scale, inv_temperature); count_launch();
     B200_CUDA_OK(cudaGetLastError());
   } else {      // 1b. recompute logits tile by tile -> bf16 dlogits
     dlog = (__nv_bfloat16*)workspace;

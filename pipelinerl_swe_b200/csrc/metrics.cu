@@ -57,7 +57,7 @@ using namespace b200grpo;
 extern "C" int b200grpo_metrics_reset(const int* kinds, int n_stats, double* acc, void* stream) {
   if (int e = check_device_sm100()) return e;
   B200_REQUIRE(kinds && acc && n_stats >= 1 && n_stats <= B200GRPO_STATS_MAX, "metrics_reset: bad argument (n_stats=%d)", n_stats);
-  metrics_reset_kernel<<<1, B200GRPO_STATS_MAX, 0, (cudaStream_t)stream>>>(kinds, n_stats, acc);
+  metrics_reset_kernel<<<1, B200GRPO_STATS_MAX, 0, (cudaStream_t)stream>>>(kinds, n_stats, acc); count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }
@@ -69,7 +69,7 @@ extern "C" int b200grpo_metrics_accumulate(const double* metrics, const int* slo
   B200_REQUIRE(metrics && slots && kinds && acc && n_stats >= 1 && n_stats <= B200GRPO_STATS_MAX,
                "metrics_accumulate: bad argument (n_stats=%d)", n_stats);
   metrics_accumulate_kernel<<<1, B200GRPO_STATS_MAX, 0, (cudaStream_t)stream>>>(metrics, slots, kinds, n_stats, kl_coef, entropy_coef,
-                                                                                input_size, n_samples, record, acc);
+                                                                                input_size, n_samples, record, acc); count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }

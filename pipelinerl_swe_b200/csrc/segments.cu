@@ -93,7 +93,7 @@ extern "C" int b200grpo_segment_bounds(const int64_t* position_ids, int T, int32
   ProfScope ps(PROF_SEGMENTS, st);
   seg_count_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts);
   seg_scan_kernel<<<1, 1024, 0, st>>>(counts, n_blocks, n_bounds);
-  seg_scatter_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts, n_bounds, bounds);
+  seg_scatter_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts, n_bounds, bounds); count_launch(3);
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }

@@ -305,7 +305,7 @@ extern "C" int b200grpo_token_loss(const float* logprob, const float* entropy, c
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA_OK(cudaMemsetAsync(a.ticket, 0, sizeof(unsigned), st));
   ProfScope ps(PROF_TOKEN_LOSS, st);
-  token_loss_kernel<<<grid, TL_THREADS, 0, st>>>(a);
+  token_loss_kernel<<<grid, TL_THREADS, 0, st>>>(a); count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }
