@@ -204,6 +204,14 @@ int b200grpo_bucket_pack(const void* const* src_ptrs_host, const int64_t* numel_
 int b200grpo_bucket_unpack(const void* bucket_bf16, void* const* dst_ptrs_host,
                            const int64_t* numel_host, const uint8_t* dst_is_f32_host,
                            int n_tensors, void* workspace, size_t workspace_bytes, void* stream);
+/* Pack + broadcast in one pass: bucket_multicast_bf16 is the NVSwitch multicast address of a symmetric
+ * buffer every rank of the update group owns (cuMulticast* / torch symmetric memory); the kernel reads the
+ * parameters once and stores with multimem.st, so the bytes land in every rank's copy of the bucket
+ * (the sender's included).  The caller orders it against the receivers with a barrier on the group. */
+int b200grpo_bucket_pack_multicast(const void* const* src_ptrs_host, const int64_t* numel_host,
+                                   const uint8_t* src_is_f32_host, int n_tensors,
+                                   void* bucket_multicast_bf16, int64_t bucket_capacity, void* workspace,
+                                   size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Host-buffer entry point (the end-to-end call): one GRPO logprob+loss forward/backward

@@ -5,6 +5,11 @@
 // 6 B/element when the source holds fp32 master weights (cast fused into the pack).
 // Every tensor starts on a 16-byte boundary inside the bucket (offsets rounded up to 8
 // elements) so both sides move 128-bit vectors.
+//
+// Multicast pack (b200grpo_bucket_pack_multicast): the bucket address is an NVSwitch multicast mapping of a
+// symmetric buffer that every rank of the update group owns, and the pack stores with multimem.st -- ONE kernel
+// reads the parameters once and the switch delivers the bf16 bytes into every receiver's copy: pack and
+// broadcast are the same pass, the sender's NVLink egress carries the payload once whatever the group size.
 #include "common.cuh"
 #include <vector>
 
@@ -29,6 +34,49 @@ __device__ __forceinline__ int find_entry(const BucketEntry* tab, int n, int64_t
     if (tab[mid].chunk_start <= chunk) lo = mid; else hi = mid - 1;
   }
   return lo;
+}
+
+// 16-byte store to an NVSwitch multicast address: lands in the buffer of every rank bound to the mapping
+__device__ __forceinline__ void multimem_st_16(void* mc_addr, uint4 v) {
+  asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w)) : "memory");
+}
+
+// multicast pack: every store is a whole 16-byte vector (tails are zero-padded: bucket offsets are multiples of 8)
+__global__ void __launch_bounds__(BK_THREADS) bucket_multicast_kernel(const BucketEntry* __restrict__ tab, int n,
+                                                                      int64_t total_chunks, __nv_bfloat16* mc_bucket) {
+  for (int64_t chunk = blockIdx.x; chunk < total_chunks; chunk += gridDim.x) {
+    const BucketEntry e = tab[find_entry(tab, n, chunk)];
+    const int64_t begin = (chunk - e.chunk_start) * BK_CHUNK;
+    const int64_t end = min(begin + (int64_t)BK_CHUNK, e.numel);
+    __nv_bfloat16* b = mc_bucket + e.bucket_off;
+    const bool vec_ok = ((uintptr_t)e.ptr & 15) == 0;
+    for (int64_t i = begin + threadIdx.x * 8LL; i < end; i += BK_THREADS * 8LL) {
+      uint4 out;
+      if (i + 8 <= end && vec_ok) {
+        if (!e.is_f32) {
+          out = __ldg((const uint4*)((const __nv_bfloat16*)e.ptr + i));
+        } else {
+          const float* p = (const float*)e.ptr;
+          const float4 x = __ldg((const float4*)(p + i)), y = __ldg((const float4*)(p + i + 4));
+          __nv_bfloat162 o[4] = {__floats2bfloat162_rn(x.x, x.y), __floats2bfloat162_rn(x.z, x.w),
+                                 __floats2bfloat162_rn(y.x, y.y), __floats2bfloat162_rn(y.z, y.w)};
+          out = *(uint4*)o;
+        }
+      } else {  // unaligned source or the last partial vector of the tensor
+        __nv_bfloat16 o[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int64_t j = i + k;
+          o[k] = j < end ? (e.is_f32 ? __float2bfloat16_rn(((const float*)e.ptr)[j]) : ((const __nv_bfloat16*)e.ptr)[j])
+                         : __float2bfloat16_rn(0.f);
+        }
+        out = *(uint4*)o;
+      }
+      multimem_st_16(b + i, out);
+    }
+  }
+  __threadfence_system();  // the stores are performed at every peer before the grid is reported complete
 }
 
 template <bool PACK>
@@ -75,7 +123,7 @@ __global__ void __launch_bounds__(BK_THREADS) bucket_kernel(const BucketEntry* _
   }
 }
 
-static int run_bucket(bool pack, void* const* ptrs, const int64_t* numel, const uint8_t* is_f32, int n, void* bucket,
+static int run_bucket(int mode, void* const* ptrs, const int64_t* numel, const uint8_t* is_f32, int n, void* bucket,
                       int64_t capacity, void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_device_sm100()) return e;
   B200_REQUIRE(n >= 0, "bucket: n_tensors < 0");
@@ -100,7 +148,8 @@ static int run_bucket(bool pack, void* const* ptrs, const int64_t* numel, const 
   if (grid > cap) grid = cap;
   ProfScope ps(PROF_BUCKET, st);
   count_launch();
-  if (pack) bucket_kernel<true><<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
+  if (mode == 2) bucket_multicast_kernel<<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
+  else if (mode == 1) bucket_kernel<true><<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
   else bucket_kernel<false><<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
@@ -123,13 +172,20 @@ extern "C" int64_t b200grpo_bucket_numel(const int64_t* numel_host, int n_tensor
 extern "C" int b200grpo_bucket_pack(const void* const* src_ptrs_host, const int64_t* numel_host,
                                     const uint8_t* src_is_f32_host, int n_tensors, void* bucket_bf16,
                                     int64_t bucket_capacity, void* workspace, size_t workspace_bytes, void* stream) {
-  return run_bucket(true, (void* const*)src_ptrs_host, numel_host, src_is_f32_host, n_tensors, bucket_bf16,
+  return run_bucket(1, (void* const*)src_ptrs_host, numel_host, src_is_f32_host, n_tensors, bucket_bf16,
                     bucket_capacity, workspace, workspace_bytes, stream);
 }
 
 extern "C" int b200grpo_bucket_unpack(const void* bucket_bf16, void* const* dst_ptrs_host, const int64_t* numel_host,
                                       const uint8_t* dst_is_f32_host, int n_tensors, void* workspace,
                                       size_t workspace_bytes, void* stream) {
-  return run_bucket(false, dst_ptrs_host, numel_host, dst_is_f32_host, n_tensors, (void*)bucket_bf16, -1, workspace,
+  return run_bucket(0, dst_ptrs_host, numel_host, dst_is_f32_host, n_tensors, (void*)bucket_bf16, -1, workspace,
                     workspace_bytes, stream);
+}
+
+extern "C" int b200grpo_bucket_pack_multicast(const void* const* src_ptrs_host, const int64_t* numel_host,
+                                              const uint8_t* src_is_f32_host, int n_tensors, void* bucket_multicast_bf16,
+                                              int64_t bucket_capacity, void* workspace, size_t workspace_bytes, void* stream) {
+  return run_bucket(2, (void* const*)src_ptrs_host, numel_host, src_is_f32_host, n_tensors, bucket_multicast_bf16,
+                    bucket_capacity, workspace, workspace_bytes, stream);
 }

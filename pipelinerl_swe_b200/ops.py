@@ -203,6 +203,14 @@ def bucket_pack(tensors: Sequence[torch.Tensor], bucket: torch.Tensor) -> None:
     check(lib().b200grpo_bucket_pack(ptrs, numel, is_f32, n, bucket.data_ptr(), bucket.numel(), ws.data_ptr(), ws.numel(), _stream()))
 
 
+def bucket_pack_multicast(tensors: Sequence[torch.Tensor], mc_ptr: int, capacity: int) -> None:
+    """K6 + broadcast in one pass: pack into the NVSwitch multicast mapping ``mc_ptr`` (bf16 elements, ``capacity`` of them)."""
+    ptrs, numel, is_f32 = _tensor_table(tensors)
+    n = len(tensors)
+    ws = _workspace(tensors[0].device, lib().b200grpo_bucket_workspace(n), "bucket")
+    check(lib().b200grpo_bucket_pack_multicast(ptrs, numel, is_f32, n, C.c_void_p(mc_ptr), int(capacity), ws.data_ptr(), ws.numel(), _stream()))
+
+
 def bucket_unpack(bucket: torch.Tensor, tensors: Sequence[torch.Tensor]) -> None:
     """K6 inverse: scatter a received bucket into the destination parameters."""
     _req(bucket, torch.bfloat16, "bucket")

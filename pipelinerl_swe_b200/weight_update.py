@@ -202,3 +202,78 @@ def reference_receive(request: WeightUpdateRequest, group, load_weights, device,
         dist.broadcast(buffer, src=src, group=group)
         load_weights([(info.name, buffer)])
     dist.barrier(group)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# NVSwitch multicast path: pack and broadcast are ONE kernel
+# ---------------------------------------------------------------------------------------------------------
+def plan_multicast(parameters_info: Sequence[ParameterInfo], bucket_bytes: int) -> list[list[int]]:
+    """Transfers of the multicast path: in-order groups of parameters, each at most ``bucket_bytes`` of bf16
+    (a larger tensor travels alone).  Both sides derive it from the request; identical to ``plan_buckets``."""
+    return plan_buckets(parameters_info, bucket_bytes)
+
+
+class MulticastChannel:
+    """Two symmetric staging slots mapped through an NVSwitch multicast address (torch symmetric memory is the
+    allocator / rendezvous; the data path is ``b200grpo_bucket_pack_multicast``).
+
+    Per transfer k (slot k % 2) the sender runs ONE kernel that reads the parameters (bf16, or fp32 masters cast
+    on the fly) and stores them to the multicast address -- the switch writes every receiver's copy of the slot --
+    then all ranks meet in one barrier; receivers hand ``load_weights`` zero-copy views of their local slot.  A
+    receiver reaches barrier k+1 only after its loads of transfer k were issued in stream order, so the sender's
+    pack of transfer k+2 (same slot) cannot overtake them: one barrier per transfer, pack k+1 overlaps load k.
+
+    Every rank of ``group`` must construct the channel collectively with the same ``slot_bytes``.
+    """
+
+    def __init__(self, group, device, slot_bytes: int):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.device = torch.device(device)
+        self.slot_elems = (int(slot_bytes) // 2 + 7) // 8 * 8
+        self.buf = symm.empty(2 * self.slot_elems, dtype=torch.bfloat16, device=self.device)
+        self.handle = symm.rendezvous(self.buf, self.group)
+        if not self.handle.has_multicast_support or not self.handle.multicast_ptr:
+            raise RuntimeError("MulticastChannel: this group has no NVSwitch multicast mapping; use send/receive_weight_update")
+        self.mc_ptr = int(self.handle.multicast_ptr)
+
+    @staticmethod
+    def slot_bytes_for(parameters_info: Sequence[ParameterInfo], bucket_bytes: int) -> int:
+        plan = plan_multicast(parameters_info, bucket_bytes)
+        return 2 * max(_bucket_elems(parameters_info, idxs) for idxs in plan)
+
+    def send(self, named_parameters: Sequence[tuple[str, torch.Tensor]], bucket_bytes: int = 256 << 20) -> int:
+        """Sender (finetune_loop.py:236-248).  Returns the number of transfers."""
+        params = [p.detach() for _, p in named_parameters]
+        params = [p if p.is_contiguous() else p.contiguous() for p in params]
+        infos = [ParameterInfo(name=n, shape=list(p.shape), dtype=str(torch.bfloat16)) for n, p in named_parameters]
+        plan = plan_multicast(infos, bucket_bytes)
+        for k, idxs in enumerate(plan):
+            n = _bucket_elems(infos, idxs)
+            if n > self.slot_elems:
+                raise ValueError(f"transfer {k} needs {2 * n} bytes, slots hold {2 * self.slot_elems}")
+            ops.bucket_pack_multicast([params[i] for i in idxs], self.mc_ptr + 2 * (k % 2) * self.slot_elems, n)
+            self.handle.barrier(channel=0)
+        self.handle.barrier(channel=0)  # receivers finished loading the last transfers
+        return len(plan)
+
+    def receive(self, request: WeightUpdateRequest, load_weights: Callable[[list[tuple[str, torch.Tensor]]], object],
+                model_dtype: torch.dtype = torch.bfloat16, bucket_bytes: int = 256 << 20) -> int:
+        """Receiver (vllm1.py:81-94): same checks as the reference, views into the local copy of the slot."""
+        infos = request.parameters_info
+        for info in infos:
+            assert info.dtype == str(model_dtype), f"mismatch dtype: src {info.dtype}, dst {model_dtype}"
+        plan = plan_multicast(infos, bucket_bytes)
+        for k, idxs in enumerate(plan):
+            self.handle.barrier(channel=0)      # transfer k has landed in this rank's slot
+            base = (k % 2) * self.slot_elems
+            off = 0
+            for i in idxs:
+                numel = _numel(infos[i].shape)
+                view = self.buf[base + off: base + off + numel].view(tuple(infos[i].shape))
+                loaded = load_weights([(infos[i].name, view)])
+                if loaded is not None and len(loaded) != 1:
+                    raise ValueError(f"model {infos[i].name} not found in model state dict")
+                off += (numel + 7) // 8 * 8
+        self.handle.barrier(channel=0)
+        return len(plan)

@@ -7,7 +7,7 @@
 Rank 0 plays the trainer (finetune_loop.py:236-248), ranks 1..N-1 the vLLM workers (vllm1.py:81-94) whose
 `load_weights` is modelled as a copy of each received tensor into the resident model parameter.  Times the
 reference's per-parameter loop (restated in weight_update.reference_send/receive) and the bucketed path for
-each bucket size; checks byte equality of every received parameter; prints one JSON line per variant with
+each bucket size, then the NVSwitch multicast path (pack + broadcast in one kernel); checks byte equality of every received parameter; prints one JSON line per variant with
 GB/s = bf16 parameter bytes delivered per receiver / max-over-ranks device time.
 """
 from __future__ import annotations
@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--fp32-masters", action="store_true", help="sender holds fp32 parameters (cast fused into the pack)")
     ap.add_argument("--layers", type=int, default=28)
+    ap.add_argument("--multicast-mb", default="64,256,1024", help="bucket sizes for the NVSwitch multicast path ('' to skip)")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -123,6 +124,26 @@ def main():
         ms = timed(run)
         emit(f"bucketed_{mb}MB", ms, check(), {"bucket_MB": mb, "n_broadcasts": len(wu.plan_transfers(request.parameters_info, mb << 20))})
         staging[0] = None
+        torch.cuda.empty_cache()
+    # NVSwitch multicast: pack + broadcast in one kernel (needs a multicast mapping for the group)
+    for mb in [int(x) for x in args.multicast_mb.split(",") if x]:
+        try:
+            ch = wu.MulticastChannel(None, dev, wu.MulticastChannel.slot_bytes_for(request.parameters_info, mb << 20))
+        except Exception as e:  # noqa: BLE001
+            if rank == 0:
+                print(json.dumps({"variant": f"multicast_{mb}MB", "unavailable": repr(e)[:200]}), flush=True)
+            break
+
+        def run_mc():
+            if rank == 0:
+                ch.send(params, bucket_bytes=mb << 20)
+            else:
+                ch.receive(request, load_weights, bucket_bytes=mb << 20)
+
+        ms = timed(run_mc)
+        emit(f"multicast_{mb}MB", ms, check(), {"bucket_MB": mb, "n_transfers": len(wu.plan_multicast(request.parameters_info, mb << 20)),
+                                                "slot_MB": ch.slot_elems * 2 / 2 ** 20})
+        del ch
         torch.cuda.empty_cache()
     dist.destroy_process_group()
 
