@@ -293,20 +293,26 @@ __global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
     const float a = s_a[r], e = s_e[r], ent = s_ent[r], shift2 = s_shift[r];
     const int t = s_t[r] - sub * 8;
     __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw[j]);
+    float d[8];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const float2 y = __bfloat1622float2(h[q]);
-      float d[2];
 #pragma unroll
       for (int w = 0; w < 2; ++w) {
         const float y2 = fmaf(w ? y.y : y.x, LOG2E_F, shift2);   // log2 p
         const float pr = fast_exp2(y2);
-        float g = -pr * fmaf(e, fmaf(y2, LN2_F, ent), a);        // -p * (a + e*(logp + H))
-        if (2 * q + w == t) g += a;
-        d[w] = (2 * q + w < n_valid) ? g : 0.f;
+        d[2 * q + w] = -pr * fmaf(e, fmaf(y2, LN2_F, ent), a);   // -p * (a + e*(logp + H))
       }
-      h[q] = __floats2bfloat162_rn(d[0], d[1]);
     }
+    if ((unsigned)t < 8u || n_valid < 8) {   // rare: the row's target column or the vocab tail is in this vector
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (k == t) d[k] += a;
+        if (k >= n_valid) d[k] = 0.f;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) h[q] = __floats2bfloat162_rn(d[2 * q], d[2 * q + 1]);
     *reinterpret_cast<uint4*>(base + (long long)r * PANEL_W) = raw[j];
   }
 }
