@@ -406,22 +406,39 @@ def run_b200(args):
         hs = [HostRLStep(T, H, V, wl.weight, wl.rlcfg, 0, 1, grad_weight_dtype=torch.float32) for _ in range(2)]
         for k, s in enumerate(hs):
             s.load_batch(wl.cpu_batches[k % wl.n_batches], wl.hidden[k % wl.n_batches].cpu())
+        # Two streams, two pinned buffer sets: step i+1 is submitted (its H2D copies included) before the host
+        # waits for step i's metrics -- the role of the reference's loader thread, which moves the next batch to the
+        # device while the current one trains (finetune_loop.py:92-115).  Every step still copies its own inputs
+        # from pinned memory and the host still reads every step's metrics before it looks at the next one.
+        streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
+
+        def submit(i):
+            with torch.cuda.stream(streams[i % 2]):
+                return hs[i % 2].run(accumulate=True)
+
         for i in range(W):
-            hs[i % 2].run(accumulate=True)
-            torch.cuda.synchronize()
+            submit(i)
+            streams[i % 2].synchronize()
         barrier()
-        t0 = time.perf_counter()
-        e0.record()
+        cur = torch.cuda.current_stream()
+        e0.record(cur)
+        for st in streams:
+            st.wait_stream(cur)
+        mh = submit(0)
         for i in range(K):
-            mh = hs[i % 2].run(accumulate=True)
-            torch.cuda.current_stream().synchronize()  # the trainer reads the step's metrics on the host every step
+            mh_next = submit(i + 1) if i + 1 < K else None
+            streams[i % 2].synchronize()               # the trainer reads the step's metrics on the host every step
             _ = float(mh[0])
-        e1.record()
+            mh = mh_next
+        for st in streams:
+            cur.wait_stream(st)
+        e1.record(cur)
         barrier()
         ms_e2e = max_over_ranks(e0.elapsed_time(e1))
         e2e = {"value": T * world * K / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hs[0].h2d_bytes,
                "d2h_bytes_per_step": hs[0].d2h_bytes, "ms_per_step": ms_e2e / K,
-               "api": "b200grpo_rl_step_host (pinned host hidden + batch fields in, f64 metrics out; weight/grad stay on device)"}
+               "api": "b200grpo_rl_step_host (pinned host hidden + batch fields in, f64 metrics out; weight/grad stay on device); "
+                      "two streams: step i+1 is submitted before the host waits for step i's metrics"}
         del hs
         torch.cuda.empty_cache()
 
