@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--mode", default="saved", choices=["saved", "recompute"],
                     help="backward: 'saved' = forward keeps bf16 logits (no third GEMM); 'recompute' = nothing [T x V] kept")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-torch-baseline", action="store_true", help="skip the torch-eager-on-this-GPU baseline (N=1 only)")
     ap.add_argument("--cpu-sample-tokens", type=int, default=0, help="tokens per CPU-baseline call (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--tunable", action="append", default=[], metavar="NAME=VALUE", help="library tunable (experiments)")
@@ -107,6 +108,59 @@ def reference_step_cpu(hidden, weight, batch, cfg, n_tokens):
     loss, stats = oracle.oracle_rl_step(h, w, sub, 0, 1, cfg)
     loss.backward()
     return float(loss.detach())
+
+
+def time_torch_eager_gpu(wl, dev, steps=8, warmup=2):
+    """The [T, V]-sized part of the reference's rl_step in plain torch on this GPU, bf16 like its HF model:
+    lm_head -> /temperature -> log_softmax -> softmax -> entropy -> gather (rl/__init__.py:197-208) and autograd
+    backward to hidden and lm_head.weight.  The O(T) per-token loss terms (:213-320) are replaced by one weighted sum,
+    so this slightly flatters the reference.  No library of this repo is involved."""
+    import torch
+    import torch.nn.functional as F
+    try:
+        hidden = wl.hidden[0].detach().clone().requires_grad_(True)            # bf16 [T-1 or T, H]
+        weight = wl.weight.detach().clone().requires_grad_(True)               # bf16 [V, H]
+        ids = wl.cpu_batches[0]["input_ids"].to(dev)
+        T = ids.shape[1]
+        h = None
+        tgt = ids[:, 1:].unsqueeze(2)
+        c_lp = torch.randn(1, T - 1, device=dev) * 1e-4
+        temperature = float(wl.rlcfg.temperature)
+        torch.cuda.reset_peak_memory_stats(dev)
+
+        def step():
+            logits = F.linear(hidden[None], weight)[:, :-1, :]        # [1, T-1, V]: the model's logits, last position dropped (:200)
+            logits = logits / temperature
+            logprobs = F.log_softmax(logits, dim=-1)
+            probs = F.softmax(logits, dim=-1)
+            entropy = -(probs * logprobs).sum(dim=-1)
+            del logits, probs
+            new_logprobs = torch.gather(logprobs, dim=2, index=tgt).squeeze(2)
+            loss = -(new_logprobs.float() * c_lp).sum() - 1e-3 * entropy.float().sum() / (T - 1)
+            loss.backward()
+            hidden.grad = None
+            return loss
+
+        for _ in range(warmup):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        out = {"value": T / (ms * 1e-3), "unit": "tokens/s", "ms_per_step": ms, "steps": steps,
+               "peak_mem_GB": torch.cuda.max_memory_allocated(dev) / 1e9,
+               "kind": "torch eager on the same B200, bf16: lm_head + rl/__init__.py:197-208 + autograd backward "
+                       "(weight.grad accumulated); O(T) loss terms omitted"}
+        del hidden, weight
+        torch.cuda.empty_cache()
+        return out
+    except Exception as e:  # noqa: BLE001  -- a baseline must never take the bench line down
+        torch.cuda.empty_cache()
+        return {"unavailable": repr(e)[:200]}
 
 
 def time_cpu_reference(hidden_cpu, weight_cpu, batch, ocfg, n_tokens, steps, warmup):
@@ -442,6 +496,11 @@ def run_b200(args):
         del hs
         torch.cuda.empty_cache()
 
+    # ---------------- the reference's torch ops on the SAME GPU (rank 0, N=1 only; SURVEY 8d "like-for-like") ----------------
+    torch_gpu = None
+    if rank == 0 and world == 1 and not args.no_torch_baseline:
+        torch_gpu = time_torch_eager_gpu(wl, dev)
+
     # ---------------- CPU baseline (rank 0, N=1 only) ----------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -460,7 +519,7 @@ def run_b200(args):
             "config": {"workload": wl.desc, "H": H, "V": V, "T": T, "parallelism": ("vocab" if wl.vocab_parallel else "dp") + str(world),
                        "grad_weight": "f32 accumulated across steps", "l2": "inputs exceed L2 (lm_head weight %.2f GB)" % (wl.weight.numel() * 2 / 1e9),
                        "bwd_mode": args.mode, "tunables": args.tunable, "tokens_per_gpu_per_sec": value / world if not wl.vocab_parallel else value},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(round(launches_per_step * K)),
+            "roofline": roofline, "cpu_baseline": cpu, "torch_gpu_baseline": torch_gpu, "e2e": e2e, "gpu_launches": int(round(launches_per_step * K)),
             "gpu_launches_per_step": launches_per_step, "clocks": clocks.summary(),
         }
         print(json.dumps(line), flush=True)

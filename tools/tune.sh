@@ -4,7 +4,7 @@
 mkdir -p gpurun_out
 for cfg in "$@"; do
   args=""; for kv in $cfg; do args="$args --tunable $kv"; done
-  python bench.py --steps 24 --warmup 3 --no-e2e --no-cpu-baseline $args 2>/dev/null | python -c "
+  python bench.py --steps 24 --warmup 3 --no-e2e --no-cpu-baseline --no-torch-baseline $args 2>/dev/null | python -c "
 import sys, json
 d = json.loads([l for l in sys.stdin if l.startswith('{')][-1])
 k = d['roofline']['kernels_ms_per_step']
