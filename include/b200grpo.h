@@ -309,7 +309,9 @@ int b200grpo_metrics_accumulate(const double* metrics, const int* slots, const i
                                 double n_samples, int record, double* acc, void* stream);
 
 /* Tunables (for experiments from the test/bench harness; defaults are the shipped ones).
- * name in {"two_cta","dh_ksplit","dh_group_m","dw_group_m","save_logits",...}; returns the previous value. */
+ * name in {"two_cta", "dh_ksplit", "dw_ksplit", "tail_split", "fwd_group_m", "dh_group_m", "dw_group_m", "dw_group_n",
+ * "save_logits", "hint_resident", "hint_stream", "dh_big_m", "dw_big_m", "gemm_big_m"} (meanings: csrc/abi.cu);
+ * returns the previous value, or a negative B200GRPO_E* code for an unknown name. */
 int b200grpo_set_tunable(const char* name, int value);
 
 /* Kernels launched by this library since it was loaded (every <<<>>> / cudaLaunchKernelEx it issues; copies

@@ -48,13 +48,18 @@ int check_device_sm100() {
   return 0;
 }
 
-// fwd_splits: 0 = auto; two_cta: 1 = cta_group::2 pairs (default); gemm_stages: 0 = auto; watchdog_ms
-// dh_ksplit / dw_ksplit: 0 = auto (tail split when tail_split = 1), >= 1 uniform k-splits;
-// dh_group_m / dw_group_m / fwd_group_m: row blocks per raster group; dw_group_n: column blocks per group (0 = all);
-// hint_resident / hint_stream: L2 eviction policy of reused / streamed operands (0 normal, 1 evict-first, 2 evict-last);
-// dh_big_m / dw_big_m / gemm_big_m: 256 rows per CTA (pair tile 512 x 256, one accumulator stage).  dH ships with it
-// (long K loop, plain store epilogue); dW does not: its f32 read-modify-write epilogue must overlap the next mainloop.
-static int g_tunables[TUNE_COUNT] = {0, 1, 0, 4000, 0, 4, 1, 1, 16, 0, 0, 0, 1, 0, 0, 1, 0};
+// Tunables, in the order of the TUNE_* enum (common.cuh); defaults are what ships.
+//   two_cta: 1 = cta_group::2 CTA pairs;  dh_ksplit / dw_ksplit: 0 = automatic (tail split when tail_split = 1, else the
+//   uniform split count with the best wave efficiency), >= 1 = that many uniform k-splits;
+//   fwd_group_m / dh_group_m / dw_group_m: row blocks per raster group; dw_group_n: column blocks per group (0 = all);
+//   save_logits: used by b200grpo_rl_step_host; hint_resident / hint_stream: L2 eviction policy of reused / streamed
+//   operands (0 normal, 1 evict-first, 2 evict-last);
+//   dh_big_m / dw_big_m / gemm_big_m: 256 rows per CTA (pair tile 512 x 256, one accumulator stage).  dH ships with it
+//   (long K loop, plain store epilogue); dW does not: its f32 accumulate epilogue must overlap the next mainloop.
+static const char* const g_tunable_names[TUNE_COUNT] = {"two_cta", "dh_ksplit", "dw_ksplit", "tail_split", "fwd_group_m", "dh_group_m",
+                                                        "dw_group_m", "dw_group_n", "save_logits", "hint_resident", "hint_stream",
+                                                        "dh_big_m", "dw_big_m", "gemm_big_m"};
+static int g_tunables[TUNE_COUNT] = {1, 0, 0, 1, 16, 4, 1, 0, 1, 0, 0, 1, 0, 0};
 int get_tunable(int id) { return g_tunables[id]; }
 
 // ---- profiling ring (diagnostic; single-threaded use) -------------------------------------
@@ -110,7 +115,7 @@ extern "C" int b200grpo_abi_version(void) { return B200GRPO_ABI_VERSION; }
 extern "C" uint64_t b200grpo_launch_count(void) { return b200grpo::launches_so_far(); }
 
 extern "C" int b200grpo_set_tunable(const char* name, int value) {
-  static const char* names[TUNE_COUNT] = {"fwd_splits", "two_cta", "gemm_stages", "watchdog_ms", "dh_ksplit", "dh_group_m", "dw_group_m", "save_logits", "fwd_group_m", "dw_group_n", "hint_resident", "hint_stream", "dh_big_m", "dw_big_m", "gemm_big_m", "tail_split", "dw_ksplit"};
+  const char* const* names = g_tunable_names;
   for (int i = 0; i < TUNE_COUNT; ++i)
     if (name && strcmp(name, names[i]) == 0) {
       const int prev = g_tunables[i];

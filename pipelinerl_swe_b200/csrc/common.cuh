@@ -15,9 +15,9 @@ namespace b200grpo {
 void set_error(const char* fmt, ...);
 int check_device_sm100();  // 0 or B200GRPO_EARCH / ECUDA (cached per thread)
 int get_tunable(int id);
-enum { TUNE_FWD_SPLITS = 0, TUNE_TWO_CTA = 1, TUNE_GEMM_STAGES = 2, TUNE_WATCHDOG_MS = 3, TUNE_DH_KSPLIT = 4, TUNE_DH_GROUP_M = 5,
-       TUNE_DW_GROUP_M = 6, TUNE_SAVE_LOGITS = 7, TUNE_FWD_GROUP_M = 8, TUNE_DW_GROUP_N = 9, TUNE_HINT_RESIDENT = 10,
-       TUNE_HINT_STREAM = 11, TUNE_DH_BIG_M = 12, TUNE_DW_BIG_M = 13, TUNE_GEMM_BIG_M = 14, TUNE_TAIL_SPLIT = 15, TUNE_DW_KSPLIT = 16, TUNE_COUNT = 17 };
+enum { TUNE_TWO_CTA = 0, TUNE_DH_KSPLIT, TUNE_DW_KSPLIT, TUNE_TAIL_SPLIT, TUNE_FWD_GROUP_M, TUNE_DH_GROUP_M, TUNE_DW_GROUP_M,
+       TUNE_DW_GROUP_N, TUNE_SAVE_LOGITS, TUNE_HINT_RESIDENT, TUNE_HINT_STREAM, TUNE_DH_BIG_M, TUNE_DW_BIG_M, TUNE_GEMM_BIG_M,
+       TUNE_COUNT };
 
 #define B200_CUDA_OK(expr)                                                              \
   do {                                                                                  \

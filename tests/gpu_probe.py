@@ -39,7 +39,6 @@ def probe_gemm(a_mn, b_mn, two_cta, M, N, K, dtype=torch.float32):
 def probe_fwd(two_cta, M, H, V, temp=1.0, splits=0):
     from pipelinerl_swe_b200 import _abi, ops
     _abi.set_tunable("two_cta", two_cta)
-    _abi.set_tunable("fwd_splits", splits)
     g = torch.Generator(device="cuda").manual_seed(2)
     h = torch.randn(M, H, device="cuda", generator=g).bfloat16()
     w = (torch.randn(V, H, device="cuda", generator=g) * 0.05).bfloat16()
