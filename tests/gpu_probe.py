@@ -236,6 +236,88 @@ def probe_tail_gemm(big, a_mn, b_mn, M, N, K):
     return e1 < 1e-4 and e2 < 1e-2 and e3 < 1e-4 and det, f"f32={e1:.2e} bf16={e2:.2e} acc={e3:.2e} deterministic={det}"
 
 
+def probe_gemm_fuzz(seed, n_cases=24):
+    """Random shapes / layouts / tile variants / split modes against the fp32 product (run under `timeout`)."""
+    import random
+    from pipelinerl_swe_b200 import _abi, ops
+    rnd = random.Random(seed)
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    worst, bad = 0.0, []
+    for case in range(n_cases):
+        a_mn, b_mn = rnd.randint(0, 1), rnd.randint(0, 1)
+        M = rnd.choice([1, 7, 8, 64, 129, 255, 256, 257, 511, 513, 1000, 2049, 4100]) if not a_mn else rnd.choice([8, 64, 136, 256, 520, 1000, 2056])
+        N = rnd.choice([8, 12, 100, 252, 256, 260, 516, 1000, 2052]) if not b_mn else rnd.choice([8, 64, 136, 256, 264, 1000, 2056])
+        K = rnd.choice([8, 16, 64, 72, 128, 200, 520, 1024, 4104, 9000])
+        big, two = rnd.randint(0, 1), rnd.randint(0, 1)
+        ks = rnd.choice([0, 1, 1, 2, 5])
+        gm = rnd.choice([0, 1, 3])
+        if ks > 1 and N % 4:
+            ks = 1
+        _abi.set_tunable("two_cta", two)
+        _abi.set_tunable("gemm_big_m", big)
+        A = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+        B = torch.randn(N, K, device="cuda", generator=g).bfloat16()
+        ref = A.float() @ B.float().t()
+        Ain = A.t().contiguous() if a_mn else A
+        Bin = B.t().contiguous() if b_mn else B
+        acc = rnd.randint(0, 1)
+        if acc:
+            out = torch.full((M, N), 3.0, device="cuda")
+            ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out=out, accumulate=True, group_m=gm, k_splits=ks)
+            ref = ref + 3.0
+        else:
+            out = ops.gemm_bf16(Ain, Bin, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), out_dtype=torch.float32, group_m=gm, k_splits=ks)
+        torch.cuda.synchronize()
+        err = _rel(out, ref)
+        worst = max(worst, err)
+        if not err < 2e-4:
+            bad.append((M, N, K, a_mn, b_mn, big, two, ks, gm, acc, err))
+    _abi.set_tunable("two_cta", 1)
+    _abi.set_tunable("gemm_big_m", 0)
+    return not bad, f"{n_cases} cases worst rel_err={worst:.2e} bad={bad[:3]}"
+
+
+def probe_lmhead_fuzz(seed, n_cases=16):
+    """Random (M, H, V, temperature, tile variant, saved / recompute) forward + backward against torch autograd in fp32."""
+    import random
+    from pipelinerl_swe_b200 import _abi, ops
+    rnd = random.Random(seed)
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    bad, worst = [], 0.0
+    for case in range(n_cases):
+        M = rnd.choice([1, 2, 31, 128, 129, 300, 513, 1030])
+        H = rnd.choice([8, 64, 136, 520, 1024])
+        V = rnd.choice([8, 100, 256, 264, 1000, 5000, 20008])
+        temp = rnd.choice([0.6, 1.0, 1.4])
+        save, two = rnd.randint(0, 1), rnd.randint(0, 1)
+        for name in ("dh_big_m", "dw_big_m", "tail_split"):
+            _abi.set_tunable(name, rnd.randint(0, 1))
+        _abi.set_tunable("two_cta", two)
+        h = torch.randn(M, H, device="cuda", generator=g).bfloat16()
+        w = (torch.randn(V, H, device="cuda", generator=g) * (1.0 / H ** 0.5)).bfloat16()
+        tgt = torch.randint(0, V, (M,), device="cuda", generator=g)
+        c_lp = torch.randn(M, device="cuda", generator=g) * 0.1
+        c_ent = torch.randn(M, device="cuda", generator=g) * 0.01
+        hr, wr = h.float().requires_grad_(True), w.float().requires_grad_(True)
+        logp = torch.log_softmax((hr @ wr.t()) / temp, -1)
+        lp = logp.gather(1, tgt[:, None]).squeeze(1)
+        ent = -(logp.exp() * logp).sum(-1)
+        ((lp * c_lp).sum() + (ent * c_ent).sum()).backward()
+        saved = ops.lmhead_saved_buffer(M, H, V, h.device) if save else None
+        stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp, saved=saved)
+        lp2, ent2, lse = ops.lmhead_finalize(stats)
+        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent2, c_lp, c_ent, 1.0 / temp, saved=saved)
+        torch.cuda.synchronize()
+        e = [float((lp2 - lp).abs().max() / (lp.abs().max() + 1e-9)), float((ent2 - ent).abs().max() / (ent.abs().max() + 1e-3)),
+             _rel(gh, hr.grad), _rel(gw, wr.grad)]
+        worst = max(worst, max(e))
+        if not (e[0] < 1e-3 and e[1] < 2e-3 and e[2] < 2e-2 and e[3] < 2e-2):
+            bad.append((M, H, V, temp, save, two, [round(x, 5) for x in e]))
+    for name, v in (("dh_big_m", 1), ("dw_big_m", 0), ("tail_split", 1), ("two_cta", 1)):
+        _abi.set_tunable(name, v)
+    return not bad, f"{n_cases} cases worst={worst:.2e} bad={bad[:3]}"
+
+
 def probe_bigm_sustained(a_mn, b_mn, M, N, K, group_m, ks_small, ks_big, secs=1.5):
     """128-row vs 256-row CTA tiles vs cuBLAS, each held for `secs` (power-capped steady state)."""
     from pipelinerl_swe_b200 import _abi, ops
@@ -366,6 +448,9 @@ for _big in (0, 1):
     PROBES[f"tail_gemm_few_big{_big}"] = (probe_tail_gemm, (_big, 0, 0, 1000, 776, 1192))       # tiles < clusters
     PROBES[f"tail_gemm_waves_big{_big}"] = (probe_tail_gemm, (_big, 0, 1, 4000, 2560, 2048))   # full waves + tail
     PROBES[f"tail_gemm_mn_big{_big}"] = (probe_tail_gemm, (_big, 1, 1, 5000, 2056, 1536))
+for _s in range(4):
+    PROBES[f"fuzz_gemm_{_s}"] = (probe_gemm_fuzz, (100 + _s,))
+    PROBES[f"fuzz_lmhead_{_s}"] = (probe_lmhead_fuzz, (200 + _s,))
 PROBES["bigm_gemm_splitk"] = (probe_bigm_gemm, (0, 1, 1000, 776, 9000, 3))
 PROBES["sust_bigm_dw"] = (probe_bigm_sustained, (1, 1, 152064, 3584, 8192, 1, 1, 1))
 PROBES["sust_bigm_dh"] = (probe_bigm_sustained, (0, 1, 8192, 3584, 152064, 8, 4, 0))

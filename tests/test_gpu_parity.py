@@ -349,3 +349,19 @@ def test_ref_logprob_annotation_matches_fp32_log_softmax():
     assert isinstance(model.lm_head, torch.nn.Module) and model.training   # mode restored
     with pytest.raises(ValueError):
         annotate_traces_with_ref_logprobs(model, [{"input_ids": [1, 2], "logprobs": [0.0, 0.0]}])
+
+
+@pytest.mark.parametrize("seed", [100, 101])
+def test_gemm_random_shapes_layouts_and_split_modes(seed):
+    """24 random (M, N, K, layout, 1/2-CTA, 128/256-row tiles, uniform / tail split, accumulate) cases vs fp32 matmul."""
+    from gpu_probe import probe_gemm_fuzz
+    ok, msg = probe_gemm_fuzz(seed)
+    assert ok, msg
+
+
+@pytest.mark.parametrize("seed", [200, 201])
+def test_lmhead_random_shapes_and_variants(seed):
+    """16 random (M, H, V, temperature, tile variant, saved / recompute) forward + backward cases vs torch autograd fp32."""
+    from gpu_probe import probe_lmhead_fuzz
+    ok, msg = probe_lmhead_fuzz(seed)
+    assert ok, msg
