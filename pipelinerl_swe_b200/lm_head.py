@@ -136,12 +136,18 @@ class FusedLMHead(nn.Module):
 
 
 def install_fused_lm_head(model: nn.Module) -> FusedLMHead:
-    """Idempotently replace ``model.lm_head`` (also through one ``.module`` / ``.model`` wrapper level)."""
+    """Idempotently replace ``model.lm_head``, looking through the usual wrappers: DeepSpeed / DDP ``.module``,
+    the reference's value-head wrapper ``.pretrained_model`` (finetune/value_model.py:60-66), PEFT ``.base_model`` / ``.model``."""
     owner = model
-    for _ in range(4):
+    for _ in range(6):
         if hasattr(owner, "lm_head"):
             break
-        nxt = getattr(owner, "module", None) or getattr(owner, "model", None)
+        nxt = None
+        for attr in ("module", "pretrained_model", "base_model", "model"):
+            cand = getattr(owner, attr, None)
+            if isinstance(cand, nn.Module) and cand is not owner:
+                nxt = cand
+                break
         if nxt is None:
             break
         owner = nxt

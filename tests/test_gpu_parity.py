@@ -365,3 +365,90 @@ def test_lmhead_random_shapes_and_variants(seed):
     from gpu_probe import probe_lmhead_fuzz
     ok, msg = probe_lmhead_fuzz(seed)
     assert ok, msg
+
+
+@pytest.mark.parametrize("tied", [False, True])
+def test_rl_step_through_a_real_hf_causal_lm(tied):
+    """Drop-in check on an unmodified transformers model (random tiny Qwen2): the lm_head swap inside HF's own forward,
+    autograd from the fused op back into the trunk, and tied embeddings, against the reference math on the plain logits."""
+    transformers = pytest.importorskip("transformers")
+    from pipelinerl_swe_b200 import FusedLMHead, RLConfig, rl_step
+    d = _dev()
+    V, lens = 2048 + 8, [60, 41, 100]
+    T = sum(lens)
+    cfg_m = transformers.Qwen2Config(vocab_size=V, hidden_size=128, intermediate_size=256, num_hidden_layers=2, num_attention_heads=4,
+                                     num_key_value_heads=2, max_position_embeddings=512, tie_word_embeddings=tied)
+    torch.manual_seed(3)
+    model = transformers.Qwen2ForCausalLM(cfg_m).to(torch.bfloat16).to(d)
+    batch = synthetic_packed_batch(lens, V, seed=5, n_prompt=6)
+    inputs = dict(input_ids=batch["input_ids"].to(d), attention_mask=batch["attention_mask"].to(d), position_ids=batch["position_ids"].to(d))
+    cfgkw = dict(policy_loss="ppo", batch_size=3, kl_coef=0.1, final_kl_coef=0.1, temperature=0.8, epsilon=0.2,
+                 entropy_bonus=0.01, final_entropy_bonus=0.01)
+
+    # reference math on the plain HF logits (what rl/__init__.py:197-208 does), old/ref log-probs near the policy
+    out = model(**inputs, output_hidden_states=True)
+    logits = out.logits.float()[0, :-1] / cfgkw["temperature"]
+    logp = torch.log_softmax(logits, -1)
+    new_lp = logp.gather(1, inputs["input_ids"][0, 1:, None]).squeeze(1)
+    ent = -(logp.exp() * logp).sum(-1)
+    g = torch.Generator().manual_seed(1)
+    m = (batch["labels"][:, 1:] != -100).float()
+    batch["old_logprobs"][:, 1:] = (new_lp.detach().cpu()[None] + 0.05 * torch.randn(1, T - 1, generator=g)) * m
+    batch["ref_logprobs"][:, 1:] = (new_lp.detach().cpu()[None] + 0.10 * torch.randn(1, T - 1, generator=g)) * m
+    bd = _to_dev(batch)
+    want_loss, want_stats = oracle.oracle_token_loss(new_lp[None], ent[None], bd, 1, 10, oracle.OracleRLConfig(**cfgkw))
+    want_loss.backward()
+    ref_grads = {n: p.grad.detach().float().clone() for n, p in model.named_parameters() if p.grad is not None}
+    model.zero_grad(set_to_none=True)
+
+    loss, stats = rl_step(model, bd, 1, 10, RLConfig(**cfgkw))
+    assert isinstance(model.lm_head, FusedLMHead)
+    if tied:
+        assert model.lm_head.weight is model.model.embed_tokens.weight
+    loss.backward()
+    assert abs(loss.item() - want_loss.item()) <= 5e-3 * abs(want_loss.item()) + 1e-5   # bf16 logits on the reference side
+    assert_stats_close(stats, want_stats, rtol=1e-2, atol=2e-3)
+    for name in ("lm_head.weight", "model.norm.weight", "model.layers.1.mlp.down_proj.weight", "model.layers.0.self_attn.q_proj.weight",
+                 "model.embed_tokens.weight"):
+        if name not in ref_grads:
+            continue
+        got = dict(model.named_parameters())[name].grad.float()
+        assert _rel(got, ref_grads[name]) < 5e-2, name   # both sides carry bf16 rounding through the trunk
+    # outside rl_step the swapped head is a plain projection again
+    plain = model(**inputs).logits
+    assert plain.shape == (1, T, V)
+
+
+def test_rl_step_through_the_value_head_wrapper():
+    """The reference's AutoModelForCausalLMWithValueHead shape (finetune/value_model.py:55-116): lm_head lives at
+    ``.pretrained_model.lm_head``, values come from ``Linear(H, 1)`` on the last hidden state."""
+    transformers = pytest.importorskip("transformers")
+    import types
+    from pipelinerl_swe_b200 import FusedLMHead, RLConfig, rl_step
+    d = _dev()
+    V, lens = 1024 + 8, [50, 33, 70]
+    cfg_m = transformers.Qwen2Config(vocab_size=V, hidden_size=64, intermediate_size=128, num_hidden_layers=1, num_attention_heads=4,
+                                     num_key_value_heads=2, max_position_embeddings=256, tie_word_embeddings=False)
+
+    class WithValueHead(torch.nn.Module):
+        def __init__(self, lm):
+            super().__init__()
+            self.pretrained_model = lm
+            self.value_head = torch.nn.Linear(lm.config.hidden_size, 1)
+
+        def forward(self, **kw):
+            out = self.pretrained_model(**kw, output_hidden_states=True)
+            value = self.value_head(out.hidden_states[-1].float()).squeeze(-1)
+            return types.SimpleNamespace(logits=out.logits, value=value)
+
+    torch.manual_seed(4)
+    model = WithValueHead(transformers.Qwen2ForCausalLM(cfg_m).to(torch.bfloat16)).to(d)
+    batch = _to_dev(synthetic_packed_batch(lens, V, seed=6, n_prompt=5))
+    cfg = RLConfig(batch_size=3, kl_coef=0.0, final_kl_coef=0.0, value_loss_coef=0.5, clamp_log_ratio_ref_new_value=5)
+    loss, stats = rl_step(model, batch, 0, 1, cfg)
+    assert isinstance(model.pretrained_model.lm_head, FusedLMHead)
+    assert {"value_mean", "value_loss", "value_mse", "value_max", "value_min"} <= set(stats)
+    loss.backward()
+    assert model.value_head.weight.grad is not None and float(model.value_head.weight.grad.abs().sum()) > 0
+    assert model.pretrained_model.lm_head.weight.grad is not None
+    assert torch.isfinite(loss).item()
