@@ -114,30 +114,44 @@ class logprob_request:
 
 
 class FusedLMHead(nn.Module):
-    """Swap-in for ``model.lm_head`` (an ``nn.Linear(H, V, bias=False)``).
+    """``model.lm_head`` (an ``nn.Linear(H, V, bias=False)``) with the fused forward.
 
     Outside ``rl_step`` it is the plain projection (generation / evaluation unchanged).
     Inside, ``forward(hidden)`` returns [B, L, 2] (logprob, entropy) in place of logits.
+
+    ``install_fused_lm_head`` does not build a new module: it re-classes the existing one IN PLACE to a subclass
+    of (FusedLMHead, its own class), so the module object, its ``weight`` Parameter, its name in the state dict and
+    every hook already registered on it (ZeRO-3 parameter gathering, FSDP, DDP, profilers) stay exactly as they were.
+    ``FusedLMHead(linear)`` builds a stand-alone wrapper around the same Parameter for code that wants one.
     """
 
     def __init__(self, linear: nn.Module):
         super().__init__()
-        if getattr(linear, "bias", None) is not None:
-            raise ValueError("FusedLMHead supports bias-free lm_head only (all Qwen2.5 / Llama heads)")
-        self.weight = linear.weight  # same Parameter object: tied embeddings and ZeRO/FSDP hooks stay valid
+        _check_fusable(linear)
+        self.weight = linear.weight  # same Parameter object: tied embeddings stay tied
         self.in_features = linear.weight.shape[1]
         self.out_features = linear.weight.shape[0]
 
     def forward(self, hidden: torch.Tensor) -> torch.Tensor:
         req = getattr(_tls, "req", None)
         if req is None:
-            return nn.functional.linear(hidden, self.weight)
+            if type(self) is FusedLMHead:
+                return nn.functional.linear(hidden, self.weight)
+            return super().forward(hidden)  # the original class's own forward (plain Linear, LoRA-wrapped, ...)
         return lmhead_logprobs(hidden, self.weight, req.input_ids, req.temperature, req.group, req.v_offset)
 
 
+def _check_fusable(linear: nn.Module) -> None:
+    if getattr(linear, "bias", None) is not None:
+        raise ValueError("FusedLMHead supports bias-free lm_head only (all Qwen2.5 / Llama heads)")
+    if not isinstance(getattr(linear, "weight", None), torch.Tensor) or linear.weight.dim() != 2:
+        raise ValueError("lm_head must own a 2-D `weight`")
+
+
 def install_fused_lm_head(model: nn.Module) -> FusedLMHead:
-    """Idempotently replace ``model.lm_head``, looking through the usual wrappers: DeepSpeed / DDP ``.module``,
-    the reference's value-head wrapper ``.pretrained_model`` (finetune/value_model.py:60-66), PEFT ``.base_model`` / ``.model``."""
+    """Idempotently give ``model.lm_head`` the fused forward, looking through the usual wrappers: DeepSpeed / DDP
+    ``.module``, the reference's value-head wrapper ``.pretrained_model`` (finetune/value_model.py:60-66), PEFT
+    ``.base_model`` / ``.model``."""
     owner = model
     for _ in range(6):
         if hasattr(owner, "lm_head"):
@@ -155,6 +169,7 @@ def install_fused_lm_head(model: nn.Module) -> FusedLMHead:
     if head is None:
         raise AttributeError("rl_step needs a model with an `lm_head` projection to fuse")
     if not isinstance(head, FusedLMHead):
-        head = FusedLMHead(head)
-        owner.lm_head = head
+        _check_fusable(head)
+        base = type(head)
+        head.__class__ = type("Fused" + base.__name__, (FusedLMHead, base), {"__module__": __name__})
     return head

@@ -206,3 +206,30 @@ def test_packed_wire_layout_matches_collate_packed():
         assert wire.nbytes <= 16 * T + 24 * wire.n_seq + 6 * 16 + 4
     with pytest.raises(NonUniformColumns):
         pack_rollouts(synthetic_rollout_examples([5, 7], 100, per_token_rewards=True), StubTokenizer(), 1, pin=False)
+
+
+def test_install_fused_lm_head_keeps_module_identity_and_hooks():
+    """The swap is an in-place re-class: same module object, same Parameter, hooks registered earlier still fire."""
+    from pipelinerl_swe_b200 import FusedLMHead, install_fused_lm_head
+
+    class Wrapper(torch.nn.Module):      # DeepSpeed-engine-like nesting
+        def __init__(self):
+            super().__init__()
+            self.module = torch.nn.Module()
+            self.module.lm_head = torch.nn.Linear(16, 40, bias=False)
+
+    w = Wrapper()
+    lin = w.module.lm_head
+    calls = []
+    lin.register_forward_pre_hook(lambda m, a: calls.append("pre"))
+    keys = list(w.state_dict().keys())
+    head = install_fused_lm_head(w)
+    assert head is lin and w.module.lm_head is lin and isinstance(lin, FusedLMHead) and isinstance(lin, torch.nn.Linear)
+    assert install_fused_lm_head(w) is lin and type(lin).__mro__.count(FusedLMHead) == 1   # idempotent
+    assert list(w.state_dict().keys()) == keys
+    x = torch.randn(2, 3, 16)
+    assert torch.equal(lin(x), torch.nn.functional.linear(x, lin.weight)) and calls == ["pre"]   # plain projection outside rl_step
+    with pytest.raises(ValueError):
+        install_fused_lm_head(torch.nn.ModuleDict({"lm_head": torch.nn.Linear(4, 4, bias=True)}))
+    standalone = FusedLMHead(torch.nn.Linear(16, 40, bias=False))
+    assert standalone(x).shape == (2, 3, 40)
