@@ -110,6 +110,53 @@ def reference_step_cpu(hidden, weight, batch, cfg, n_tokens):
     return float(loss.detach())
 
 
+def time_rl_step_api(wl, dev, steps, warmup=3):
+    """The drop-in call itself: ``rl_step(model, batch, ...)`` + ``loss.backward()`` through autograd on a model whose
+    forward ends in ``lm_head`` (hidden states fixed, as everywhere in this bench), batch already on the device like the
+    reference's (finetune_loop.py:109), host sync for the stats dict every step."""
+    import types
+    import torch
+    from pipelinerl_swe_b200 import rl_step
+    try:
+        class TrunkStub(torch.nn.Module):
+            def __init__(self, hidden, weight):
+                super().__init__()
+                self.hidden = torch.nn.Parameter(hidden[None].clone())
+                self.lm_head = torch.nn.Linear(weight.shape[1], weight.shape[0], bias=False, dtype=torch.bfloat16, device=dev)
+                self.lm_head.weight.data = weight  # shares the bench's weight storage
+
+            def forward(self, **kw):
+                return types.SimpleNamespace(logits=self.lm_head(self.hidden))
+
+        model = TrunkStub(wl.hidden[0], wl.weight)
+        batch = wl.batches[0]
+
+        def step():
+            loss, stats = rl_step(model, batch, 0, 1, wl.rlcfg)
+            loss.backward()
+            return stats
+
+        for _ in range(warmup):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            stats = step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        out = {"value": wl.T / (ms * 1e-3), "unit": "tokens/s", "ms_per_step": ms, "steps": steps, "loss": stats["loss"],
+               "api": "pipelinerl_swe_b200.rl_step(model, batch, step, max_step, config) + loss.backward(); "
+                      "bf16 lm_head.weight.grad accumulated by autograd, one host sync per step for the stats dict"}
+        del model
+        torch.cuda.empty_cache()
+        return out
+    except Exception as e:  # noqa: BLE001
+        torch.cuda.empty_cache()
+        return {"unavailable": repr(e)[:200]}
+
+
 def time_torch_eager_gpu(wl, dev, steps=8, warmup=2):
     """The [T, V]-sized part of the reference's rl_step in plain torch on this GPU, bf16 like its HF model:
     lm_head -> /temperature -> log_softmax -> softmax -> entropy -> gather (rl/__init__.py:197-208) and autograd
@@ -497,8 +544,9 @@ def run_b200(args):
         torch.cuda.empty_cache()
 
     # ---------------- the reference's torch ops on the SAME GPU (rank 0, N=1 only; SURVEY 8d "like-for-like") ----------------
-    torch_gpu = None
+    torch_gpu, api = None, None
     if rank == 0 and world == 1 and not args.no_torch_baseline:
+        api = time_rl_step_api(wl, dev, K)
         torch_gpu = time_torch_eager_gpu(wl, dev)
 
     # ---------------- CPU baseline (rank 0, N=1 only) ----------------
@@ -519,7 +567,7 @@ def run_b200(args):
             "config": {"workload": wl.desc, "H": H, "V": V, "T": T, "parallelism": ("vocab" if wl.vocab_parallel else "dp") + str(world),
                        "grad_weight": "f32 accumulated across steps", "l2": "inputs exceed L2 (lm_head weight %.2f GB)" % (wl.weight.numel() * 2 / 1e9),
                        "bwd_mode": args.mode, "tunables": args.tunable, "tokens_per_gpu_per_sec": value / world if not wl.vocab_parallel else value},
-            "roofline": roofline, "cpu_baseline": cpu, "torch_gpu_baseline": torch_gpu, "e2e": e2e, "gpu_launches": int(round(launches_per_step * K)),
+            "roofline": roofline, "cpu_baseline": cpu, "torch_gpu_baseline": torch_gpu, "rl_step_api": api, "e2e": e2e, "gpu_launches": int(round(launches_per_step * K)),
             "gpu_launches_per_step": launches_per_step, "clocks": clocks.summary(),
         }
         print(json.dumps(line), flush=True)

@@ -318,6 +318,37 @@ def probe_lmhead_fuzz(seed, n_cases=16):
     return not bad, f"{n_cases} cases worst={worst:.2e} bad={bad[:3]}"
 
 
+def probe_api_overhead(T, H, V, steps=24):
+    """Public drop-in path (rl_step + loss.backward() through autograd, StubLM) at the bench shape: ms/step and tok/s."""
+    from helpers import StubLM, synthetic_packed_batch
+    from pipelinerl_swe_b200 import RLConfig, rl_step
+    dev = torch.device("cuda:0")
+    n_seq = 16
+    lens = [T // n_seq] * n_seq
+    model = StubLM(H, V, T, seed=0, w_std=0.02).to(dev)
+    batch = synthetic_packed_batch(lens, V, seed=1)
+    bd = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+    bd["old_logprobs"] = bd["old_logprobs"].clamp(min=-12.0) * 0 - 11.9 * (bd["labels"] != -100).float()  # near ln(1/V): finite ratios
+    bd["ref_logprobs"] = bd["old_logprobs"].clone()
+    cfg = RLConfig(batch_size=4096, kl_coef=0.1, final_kl_coef=0.1, clamp_log_ratio_ref_new_value=5)
+
+    def step():
+        loss, stats = rl_step(model, bd, 0, 1, cfg)      # includes the host sync for the stats dict
+        loss.backward()
+        return stats
+
+    for _ in range(4):
+        step()
+    torch.cuda.synchronize()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(steps):
+        stats = step()
+    t1.record(); torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1) / steps
+    return True, f"rl_step+backward {ms:.3f} ms/step = {T / ms * 1e3:.0f} tok/s (grad dtype {model.lm_head.weight.grad.dtype}) loss={stats['loss']:.4f}"
+
+
 def probe_bigm_sustained(a_mn, b_mn, M, N, K, group_m, ks_small, ks_big, secs=1.5):
     """128-row vs 256-row CTA tiles vs cuBLAS, each held for `secs` (power-capped steady state)."""
     from pipelinerl_swe_b200 import _abi, ops
@@ -451,6 +482,7 @@ for _big in (0, 1):
 for _s in range(4):
     PROBES[f"fuzz_gemm_{_s}"] = (probe_gemm_fuzz, (100 + _s,))
     PROBES[f"fuzz_lmhead_{_s}"] = (probe_lmhead_fuzz, (200 + _s,))
+PROBES["api_overhead_c3"] = (probe_api_overhead, (8192, 3584, 152064))
 PROBES["bigm_gemm_splitk"] = (probe_bigm_gemm, (0, 1, 1000, 776, 9000, 3))
 PROBES["sust_bigm_dw"] = (probe_bigm_sustained, (1, 1, 152064, 3584, 8192, 1, 1, 1))
 PROBES["sust_bigm_dh"] = (probe_bigm_sustained, (0, 1, 8192, 3584, 152064, 8, 4, 0))
