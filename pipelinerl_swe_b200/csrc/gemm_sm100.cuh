@@ -287,7 +287,7 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t 
 // ---------------------------------------------------------------------------------------
 template <int kEpi, int kAMajor, int kBMajor, int kCtas, int BLOCK_N, int kStages, bool kSave = false, bool kAPanel = false,
           int kMRep = 1>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS + 128 * (kMRep - 1), 1)
 gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, const GemmParams p) {
   using L = GemmSmem<BLOCK_N, kCtas, kStages, kMRep>;
   constexpr int LOAD_N = L::LOAD_N;
@@ -322,7 +322,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) { ptx::mbar_init(&full_bar[i], kCtas); ptx::mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], 128 * kCtas); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], 128 * kCtas * kMRep); }
     ptx::fence_mbar_init();
   }
   if (kCtas > 1) ptx::cluster_sync();   // peer barriers initialised before anyone signals them
@@ -415,8 +415,11 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
       if (ACC_STAGES > 1 && tile_iter > 1) ptx::mbar_wait(&tmem_empty[(last - 1) % ACC_STAGES], ((last - 1) / ACC_STAGES) & 1, 5);
     }
   } else if (warp >= GEMM_EPI_WARP0) {
-    // ===================== epilogue (4 warps, thread == TMEM lane == tile row) ============
+    // ===================== epilogue (4 warps per 128-row accumulator, thread == TMEM lane == tile row) ============
+    // kMRep == 2: warps 4-7 drain the first 128 rows (TMEM columns [0, BLOCK_N)), warps 8-11 the second 128 rows
+    // concurrently -- the epilogue is not overlapped with the next tile's MMAs there, so its latency is what is exposed.
     const int quad = warp & 3;
+    const int rep = (warp - GEMM_EPI_WARP0) >> 2;
     const int row_in_tile = quad * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     const float scale2 = p.inv_temp * LOG2E_F;
@@ -425,9 +428,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
       const Item it = decode_item(p, item);
       const int n0 = it.nb * BLOCK_N;
       const uint32_t as = tile_iter % ACC_STAGES, aphase = (tile_iter / ACC_STAGES) & 1;
-      bool waited = false;
-#pragma unroll 1
-      for (int rep = 0; rep < kMRep; ++rep) {
+      {
         const int row = (it.m_blk * kCtas + (int)cta_rank) * CTA_M + rep * GEMM_BLOCK_M + row_in_tile;
         const bool row_ok = row < p.M;
         FwdRowState fs;
@@ -446,11 +447,8 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
           const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
           bc.tcol = (t >= 0 && t < p.N) ? (int)t : -1000000;
         }
-        if (!waited) {
-          ptx::mbar_wait(&tmem_full[as], aphase, 6);
-          ptx::tc_fence_after();
-          waited = true;
-        }
+        ptx::mbar_wait(&tmem_full[as], aphase, 6);
+        ptx::tc_fence_after();
         const uint32_t t_addr = tmem_base + lane_addr + as * ACC_COLS + rep * BLOCK_N;
         if constexpr (kEpi == EPI_FWD_STATS) {   // pass 1: tile max per row
 #pragma unroll 1

@@ -97,7 +97,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   if (clusters > n_items) clusters = (int)n_items;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(clusters * kCtas);
-  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.blockDim = dim3(GEMM_THREADS + 128 * (kMRep - 1));   // one more epilogue warpgroup per extra 128 rows
   cfg.dynamicSmemBytes = L::TOTAL;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -175,6 +175,8 @@ static int dispatch(int a_mn, int b_mn, int ctas, const CUtensorMap& ta, const C
     B200_CASE(0, 0, 1) B200_CASE(0, 0, 2) B200_CASE(0, 1, 1) B200_CASE(0, 1, 2)
     B200_CASE(1, 0, 1) B200_CASE(1, 0, 2) B200_CASE(1, 1, 1) B200_CASE(1, 1, 2)
     B200_BIG(0, 0) B200_BIG(0, 1) B200_BIG(1, 0) B200_BIG(1, 1)
+  } else if constexpr (kEpi == EPI_FWD_STATS) {
+    B200_CASE(0, 0, 1) B200_CASE(0, 0, 2) B200_BIG(0, 0)
   } else {
     B200_CASE(0, 0, 1) B200_CASE(0, 0, 2)
   }
@@ -465,8 +467,10 @@ extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* 
   B200_REQUIRE(inv_temperature > 0.f, "lmhead_fwd: temperature must be positive");
   B200_REQUIRE(!saved || ((uintptr_t)saved & 255) == 0, "lmhead_fwd: saved buffer must be 256-byte aligned");
   const int ctas = ctas_for(M);
+  const int mrep = mrep_for(TUNE_FWD_BIG_M, ctas);
   GemmParams p = {};
-  fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_GROUP_M), 1, 0, get_tunable(TUNE_HINT_RESIDENT), get_tunable(TUNE_HINT_STREAM));
+  fill_tiling(p, M, Vloc, H, ctas, max(1, get_tunable(TUNE_FWD_GROUP_M) / mrep), 1, 0, get_tunable(TUNE_HINT_RESIDENT),
+              get_tunable(TUNE_HINT_STREAM), mrep);
   const size_t need = part_bytes(M, Vloc);
   if (!saved && workspace_bytes < need) { set_error("lmhead_fwd: workspace %zu < %zu", workspace_bytes, need); return B200GRPO_EWORKSPACE; }
   p.targets = (const long long*)targets; p.v_offset = v_offset; p.inv_temp = inv_temperature;
@@ -477,10 +481,11 @@ extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* 
     if (int e = clear_tail_panel(p.zsave, M, Vloc, st)) return e;
   }
   CUtensorMap ta, tb;
-  if (int e = make_ab_maps(&ta, &tb, hidden, ldh, 0, weight, ldw, 0, M, Vloc, H, ctas)) return e;
+  if (int e = make_ab_maps(&ta, &tb, hidden, ldh, 0, weight, ldw, 0, M, Vloc, H, ctas, mrep)) return e;
   {
     ProfScope ps(PROF_FWD_GEMM, st);
-    const int e = saved ? dispatch<EPI_FWD_STATS, true>(0, 0, ctas, ta, tb, p, st) : dispatch<EPI_FWD_STATS, false>(0, 0, ctas, ta, tb, p, st);
+    const int e = saved ? dispatch<EPI_FWD_STATS, true>(0, 0, ctas, ta, tb, p, st, mrep)
+                        : dispatch<EPI_FWD_STATS, false>(0, 0, ctas, ta, tb, p, st, mrep);
     if (e) return e;
   }
   ProfScope ps(PROF_FWD_MERGE, st);
