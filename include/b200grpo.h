@@ -182,6 +182,13 @@ int b200grpo_group_advantage(const double* row_reward, const int32_t* group_key,
                              int n_groups, int divide_by_std, float* advantages,
                              float* group_tokens, float* num_labels, float* overflow,
                              void* workspace, size_t workspace_bytes, void* stream);
+/* Same statistics, one output value per ROLLOUT (f32[n_rows] each) instead of per token: what the list-of-dict
+ * contract of populate_rl_data needs when rewards are constant inside a rollout (the host repeats the value). */
+int b200grpo_group_advantage_rows(const double* row_reward, const int32_t* group_key,
+                                  const int64_t* row_offsets, const int32_t* n_labels,
+                                  const uint8_t* has_eos, int n_rows, int n_groups, int divide_by_std,
+                                  float* advantages, float* group_tokens, float* num_labels,
+                                  float* overflow, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * K6  weight-update buckets.  Replaces the per-parameter loop of

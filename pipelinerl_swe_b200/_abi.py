@@ -75,6 +75,7 @@ SIGNATURES = {
                                  _p, _sz, _p]),
     "b200grpo_group_advantage_workspace": (_sz, [_i, _i]),
     "b200grpo_group_advantage": (_i, [_p] * 6 + [_i, _i, _i] + [_p] * 5 + [_sz, _p]),
+    "b200grpo_group_advantage_rows": (_i, [_p] * 5 + [_i, _i, _i] + [_p] * 5 + [_sz, _p]),
     "b200grpo_bucket_workspace": (_sz, [_i]),
     "b200grpo_bucket_numel": (_i64, [_p, _i]),
     "b200grpo_bucket_pack": (_i, [_p, _p, _p, _i, _p, _i64, _p, _sz, _p]),

@@ -107,6 +107,24 @@ __global__ void __launch_bounds__(256) group_expand_kernel(const double* __restr
   }
 }
 
+// Per-ROLLOUT form of the expansion: one value per row and column (the list-of-dict contract of populate_rl_data
+// only needs these; the host repeats them per token with list multiplication).
+__global__ void __launch_bounds__(256) group_rows_kernel(const double* __restrict__ row_reward, const int32_t* __restrict__ group_key,
+                                                         const int32_t* __restrict__ n_labels, const uint8_t* __restrict__ has_eos,
+                                                         const GroupStat* __restrict__ stats, int n_rows, int divide_by_std,
+                                                         float* __restrict__ adv, float* __restrict__ gtok, float* __restrict__ nlab,
+                                                         float* __restrict__ ovf) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= n_rows) return;
+  const GroupStat s = stats[group_key[row]];
+  const double denom = (isnan(s.std) ? 0.0 : s.std) + 1e-4;  // np.nan_to_num(std) + 1e-4 (:466)
+  const double r0 = row_reward[row];
+  adv[row] = (float)(divide_by_std ? (r0 - s.mean) / denom : (r0 - s.mean));
+  gtok[row] = (float)s.gtok;
+  nlab[row] = (float)n_labels[row];
+  ovf[row] = has_eos[row] ? 0.f : 1.f;
+}
+
 }  // namespace b200grpo
 
 using namespace b200grpo;
@@ -142,6 +160,32 @@ extern "C" int b200grpo_group_advantage(const double* row_reward, const int32_t*
   if (grid > cap) grid = cap;
   group_expand_kernel<<<grid, 256, 0, st>>>(row_reward, token_rewards, group_key, row_offsets, n_labels, has_eos, stats,
                                             n_rows, divide_by_std, advantages, group_tokens, num_labels, overflow, vec_ok); count_launch();
+  B200_CUDA_OK(cudaGetLastError());
+  return B200GRPO_OK;
+}
+
+extern "C" int b200grpo_group_advantage_rows(const double* row_reward, const int32_t* group_key, const int64_t* row_offsets,
+                                             const int32_t* n_labels, const uint8_t* has_eos, int n_rows, int n_groups,
+                                             int divide_by_std, float* advantages, float* group_tokens, float* num_labels,
+                                             float* overflow, void* workspace, size_t workspace_bytes, void* stream) {
+  if (int e = check_device_sm100()) return e;
+  B200_REQUIRE(n_rows >= 0 && n_groups >= 0, "group_advantage_rows: negative size");
+  if (n_rows == 0) return B200GRPO_OK;
+  B200_REQUIRE(row_reward && group_key && row_offsets && n_labels && has_eos && advantages && group_tokens && num_labels &&
+               overflow && workspace, "group_advantage_rows: null pointer");
+  if (workspace_bytes < b200grpo_group_advantage_workspace(n_rows, n_groups)) {
+    set_error("group_advantage_rows: workspace too small");
+    return B200GRPO_EWORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  GroupStat* stats = (GroupStat*)workspace;
+  ProfScope ps(PROF_ADVANTAGE, st);
+  if (n_groups > 0) {
+    group_stats_kernel<<<ceil_div(n_groups, GS_WARPS), GS_WARPS * 32, 0, st>>>(row_reward, group_key, row_offsets, n_rows, n_groups, stats);
+    count_launch();
+  }
+  group_rows_kernel<<<ceil_div(n_rows, 256), 256, 0, st>>>(row_reward, group_key, n_labels, has_eos, stats, n_rows, divide_by_std,
+                                                           advantages, group_tokens, num_labels, overflow); count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }

@@ -177,6 +177,21 @@ def group_advantage(row_reward: torch.Tensor, group_key: torch.Tensor, row_offse
     return out
 
 
+def group_advantage_rows(row_reward: torch.Tensor, group_key: torch.Tensor, row_offsets: torch.Tensor, n_labels: torch.Tensor,
+                         has_eos: torch.Tensor, n_groups: int, divide_by_std: bool) -> torch.Tensor:
+    """K4, per-rollout form -> f32 [4, n_rows]: advantage, group_tokens, num_labels, overflow of every rollout."""
+    _req(row_reward, torch.float64, "row_reward"); _req(group_key, torch.int32, "group_key")
+    _req(row_offsets, torch.int64, "row_offsets"); _req(n_labels, torch.int32, "n_labels"); _req(has_eos, torch.uint8, "has_eos")
+    n_rows = row_reward.numel()
+    out = torch.empty(4, n_rows, dtype=torch.float32, device=row_reward.device)
+    ws = _workspace(row_reward.device, lib().b200grpo_group_advantage_workspace(n_rows, n_groups))
+    check(lib().b200grpo_group_advantage_rows(row_reward.data_ptr(), group_key.data_ptr(), row_offsets.data_ptr(), n_labels.data_ptr(),
+                                              has_eos.data_ptr(), n_rows, n_groups, int(divide_by_std), out[0].data_ptr(),
+                                              out[1].data_ptr(), out[2].data_ptr(), out[3].data_ptr(), ws.data_ptr(), ws.numel(),
+                                              _stream()))
+    return out
+
+
 def _tensor_table(tensors: Sequence[torch.Tensor]):
     n = len(tensors)
     ptrs = (C.c_void_p * n)(*[t.data_ptr() for t in tensors])
