@@ -22,7 +22,8 @@ IGNORE = -100
 def prepare_rl_fields(encoding: dict[str, Any], reward: float, old_logprobs: list[float], ref_logprobs: list[float]) -> dict[str, Any]:
     """rl/__init__.py:504-525 (pure host list bookkeeping; nothing to accelerate)."""
     n = len(encoding["labels"])
-    n_target = sum(1 for t in encoding["labels"] if t != IGNORE)
+    labels = encoding["labels"]
+    n_target = (len(labels) - labels.count(IGNORE)) if isinstance(labels, list) else sum(1 for t in labels if t != IGNORE)
     assert n_target == len(old_logprobs), f"Target tokens: {n_target}, old logprobs: {len(old_logprobs)}"
     encoding["rewards"] = [reward] * n
     encoding["advantages"] = [0.0] * n

@@ -92,15 +92,17 @@ class PackedWire:
 
 def _seq_scalar(example: dict[str, Any], col: str, n_tokens: int) -> float:
     v = example[col]
-    if isinstance(v, (list, tuple, np.ndarray)):
-        a = np.asarray(v, dtype=np.float64).reshape(-1)
-        if a.size == 0:
+    if isinstance(v, np.ndarray):
+        v = v.reshape(-1).tolist()
+    if isinstance(v, (list, tuple)):
+        n = len(v)
+        if n == 0:
             return 0.0
-        if a.size != n_tokens:
-            raise NonUniformColumns(f"column {col}: {a.size} values for {n_tokens} tokens")
-        if not (a == a[0]).all():
+        if n != n_tokens:
+            raise NonUniformColumns(f"column {col}: {n} values for {n_tokens} tokens")
+        if v.count(v[0]) != n:       # C-speed scan, no array conversion
             raise NonUniformColumns(f"column {col} varies inside a rollout")
-        return float(a[0])
+        return float(v[0])
     return float(v)
 
 
