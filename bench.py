@@ -394,11 +394,18 @@ class DeviceWorkload:
         saved = self.saved if self.save_logits else None
         lp, ent, lse = ops.lmhead_finalize(self.fwd_stats(h, tgt, saved))
         loss, metrics, coef_lp, coef_ent, _ = ops.token_loss(lp[None], ent[None], b, self.cfg)
-        gh, _ = ops.lmhead_bwd(h, self.weight, tgt, lse, ent, coef_lp[0], coef_ent[0], 1.0, self.v_offset,
-                               grad_weight_out=self.grad_weight, accumulate=True, saved=saved)
-        if self.vocab_parallel:
-            from pipelinerl_swe_b200.vocab_parallel import reduce_grad_hidden
-            reduce_grad_hidden(gh)
+        args = (h, self.weight, tgt, lse, ent, coef_lp[0], coef_ent[0], 1.0, self.v_offset)
+        if self.vocab_parallel:   # as LMHeadLogprobFunction.backward: the dH all-reduce runs while dW is computed
+            from pipelinerl_swe_b200 import _abi
+            from pipelinerl_swe_b200.vocab_parallel import reduce_grad_hidden_async
+            gh, _ = ops.lmhead_bwd(*args, need_grad_weight=False, saved=saved, stages=_abi.BWD_DLOGITS | _abi.BWD_DH)
+            pending = reduce_grad_hidden_async(gh)
+            ops.lmhead_bwd(*args, need_grad_hidden=False, grad_weight_out=self.grad_weight, accumulate=True, saved=saved,
+                           stages=_abi.BWD_DW)
+            if pending is not None:
+                pending.wait()
+        else:
+            ops.lmhead_bwd(*args, grad_weight_out=self.grad_weight, accumulate=True, saved=saved)
         return metrics
 
 

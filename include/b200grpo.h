@@ -165,6 +165,21 @@ int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* weight, int
                         int grad_weight_is_f32, int accumulate, void* workspace,
                         size_t workspace_bytes, void* stream);
 
+/* The same backward in stages, for callers that put something between the two gradient GEMMs -- the
+ * vocab-parallel path all-reduces grad_hidden over NCCL while grad_weight is still being computed:
+ *   call 1: stages = B200GRPO_BWD_DLOGITS | B200GRPO_BWD_DH   (forms dlogits, writes grad_hidden)
+ *   call 2: stages = B200GRPO_BWD_DW                          (reuses the dlogits of call 1)
+ * with the same saved / workspace buffers in both.  The per-token inputs may be NULL when
+ * B200GRPO_BWD_DLOGITS is not requested. */
+enum { B200GRPO_BWD_DLOGITS = 1, B200GRPO_BWD_DH = 2, B200GRPO_BWD_DW = 4 };
+int b200grpo_lmhead_bwd_staged(const void* hidden, int64_t ldh, const void* weight, int64_t ldw,
+                        const int64_t* targets, const float* lse, const float* entropy,
+                        const float* coef_lp, const float* coef_ent, const float* grad_scale,
+                        int M, int H, int Vloc, int64_t v_offset, float inv_temperature,
+                        void* saved, void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw,
+                        int grad_weight_is_f32, int accumulate, int stages, void* workspace,
+                        size_t workspace_bytes, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * K4  group-normalised advantages.  Replaces the pandas path rl/__init__.py:394-499.
  * Per rollout row i (n_rows): reward f64 (rewards[0] of the row, :402), group_key i32

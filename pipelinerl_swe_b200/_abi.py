@@ -21,6 +21,7 @@ M_COUNT = 40  # B200GRPO_M_COUNT
  M_CLAMP_NEW_OLD, M_TOKEN_WEIGHT, M_VALUE_MEAN, M_VALUE_LOSS, M_VALUE_MSE, M_MAX_REWARD, M_MIN_REWARD, M_MAX_ADV,
  M_MIN_ADV, M_MAX_KL, M_MIN_KL, M_MAX_TW, M_MIN_TW, M_MAX_VALUE, M_MIN_VALUE, M_FLAGS) = range(36)
 F_NEW_LP_NONFINITE, F_REF_NEW_NONFINITE, F_KL_NONFINITE, F_LOSS_NONFINITE, F_GROUP_TOKENS_LE0 = 1, 2, 4, 8, 16
+BWD_DLOGITS, BWD_DH, BWD_DW = 1, 2, 4                                      # B200GRPO_BWD_*
 STAT_SUM, STAT_MIN, STAT_MAX = 0, 1, 2                                    # B200GRPO_STAT_*
 STAT_KL_COEF, STAT_ENTROPY_COEF, STAT_INPUT_SIZE = -1, -2, -3
 STATS_MAX = 64
@@ -73,6 +74,8 @@ SIGNATURES = {
     "b200grpo_lmhead_bwd_workspace": (_sz, [_i, _i, _i, _i]),
     "b200grpo_lmhead_bwd": (_i, [_p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i64, _f, _p, _p, _i64, _p, _i64, _i, _i,
                                  _p, _sz, _p]),
+    "b200grpo_lmhead_bwd_staged": (_i, [_p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i64, _f, _p, _p, _i64, _p, _i64, _i, _i,
+                                        _i, _p, _sz, _p]),
     "b200grpo_group_advantage_workspace": (_sz, [_i, _i]),
     "b200grpo_group_advantage": (_i, [_p] * 6 + [_i, _i, _i] + [_p] * 5 + [_sz, _p]),
     "b200grpo_group_advantage_rows": (_i, [_p] * 5 + [_i, _i, _i] + [_p] * 5 + [_sz, _p]),

@@ -511,13 +511,20 @@ extern "C" size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc, int with
   return (with_saved ? 0 : panel_bytes(M, Vloc)) + slab + 256;
 }
 
-extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
-                                   const float* lse, const float* entropy, const float* coef_lp, const float* coef_ent,
-                                   const float* grad_scale, int M, int H, int Vloc, int64_t v_offset, float inv_temperature,
-                                   void* saved, void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw,
-                                   int grad_weight_is_f32, int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
+// stages: B200GRPO_BWD_DLOGITS (form dlogits: in place from the saved logits, or by recomputing them into the
+// workspace), _DH, _DW.  A caller that splits the backward in two calls passes the same saved / workspace buffers to
+// both and B200GRPO_BWD_DLOGITS only to the first.
+static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
+                           const float* lse, const float* entropy, const float* coef_lp, const float* coef_ent,
+                           const float* grad_scale, int M, int H, int Vloc, int64_t v_offset, float inv_temperature,
+                           void* saved, void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw,
+                           int grad_weight_is_f32, int accumulate, int stages, void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_device_sm100()) return e;
-  B200_REQUIRE(hidden && weight && targets && lse && entropy && coef_lp && coef_ent && workspace, "lmhead_bwd: null pointer");
+  const bool form = stages & B200GRPO_BWD_DLOGITS;
+  if (!(stages & B200GRPO_BWD_DH)) grad_hidden = nullptr;
+  if (!(stages & B200GRPO_BWD_DW)) grad_weight = nullptr;
+  B200_REQUIRE(hidden && weight && workspace, "lmhead_bwd: null pointer");
+  B200_REQUIRE(!form || (targets && lse && entropy && coef_lp && coef_ent), "lmhead_bwd: null per-token input");
   B200_REQUIRE(M >= 1 && H >= 8 && Vloc >= 1 && H % 8 == 0, "lmhead_bwd: M=%d H=%d Vloc=%d", M, H, Vloc);
   B200_REQUIRE(!accumulate || grad_weight_is_f32, "lmhead_bwd: accumulate needs an f32 grad_weight");
   const size_t need = b200grpo_lmhead_bwd_workspace(M, H, Vloc, saved != nullptr);
@@ -529,14 +536,17 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
   if (saved) {  // 1a. saved logits -> dlogits in place (no recompute GEMM)
     dlog = (__nv_bfloat16*)((char*)saved + part_bytes(M, Vloc));
     slab = (char*)workspace;
+  } else {
+    dlog = (__nv_bfloat16*)workspace;
+    slab = (char*)workspace + panel_bytes(M, Vloc);
+  }
+  if (saved && form) {
     ProfScope ps(PROF_DLOGITS_EW, st);
     dim3 grid(ceil_div(M, DL_ROWS), ceil_div(Vloc, PANEL_W));
     dlogits_from_saved_kernel<<<grid, DL_THREADS, 0, st>>>(dlog, (const float4*)saved, M, Vloc, (const long long*)targets, v_offset, lse,
                                                            entropy, coef_lp, coef_ent, grad_scale, inv_temperature); count_launch();
     B200_CUDA_OK(cudaGetLastError());
-  } else {      // 1b. recompute logits tile by tile -> bf16 dlogits
-    dlog = (__nv_bfloat16*)workspace;
-    slab = (char*)workspace + panel_bytes(M, Vloc);
+  } else if (form) {      // 1b. recompute logits tile by tile -> bf16 dlogits
     if (int e = clear_tail_panel(dlog, M, Vloc, st)) return e;
     GemmParams p = {};
     fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_GROUP_M), 1, 0, get_tunable(TUNE_HINT_RESIDENT), get_tunable(TUNE_HINT_STREAM));
@@ -562,6 +572,28 @@ extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* 
                                get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT), mrep_for(TUNE_DW_BIG_M, ctas))) return e;
   }
   return B200GRPO_OK;
+}
+
+extern "C" int b200grpo_lmhead_bwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
+                                   const float* lse, const float* entropy, const float* coef_lp, const float* coef_ent,
+                                   const float* grad_scale, int M, int H, int Vloc, int64_t v_offset, float inv_temperature,
+                                   void* saved, void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw,
+                                   int grad_weight_is_f32, int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
+  return lmhead_bwd_impl(hidden, ldh, weight, ldw, targets, lse, entropy, coef_lp, coef_ent, grad_scale, M, H, Vloc, v_offset,
+                         inv_temperature, saved, grad_hidden, ldgh, grad_weight, ldgw, grad_weight_is_f32, accumulate,
+                         B200GRPO_BWD_DLOGITS | B200GRPO_BWD_DH | B200GRPO_BWD_DW, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200grpo_lmhead_bwd_staged(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
+                                          const float* lse, const float* entropy, const float* coef_lp, const float* coef_ent,
+                                          const float* grad_scale, int M, int H, int Vloc, int64_t v_offset, float inv_temperature,
+                                          void* saved, void* grad_hidden, int64_t ldgh, void* grad_weight, int64_t ldgw,
+                                          int grad_weight_is_f32, int accumulate, int stages, void* workspace,
+                                          size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(stages > 0 && stages < 8, "lmhead_bwd_staged: stages=%d", stages);
+  return lmhead_bwd_impl(hidden, ldh, weight, ldw, targets, lse, entropy, coef_lp, coef_ent, grad_scale, M, H, Vloc, v_offset,
+                         inv_temperature, saved, grad_hidden, ldgh, grad_weight, ldgw, grad_weight_is_f32, accumulate, stages,
+                         workspace, workspace_bytes, stream);
 }
 
 extern "C" int b200grpo_gemm_bf16(const void* A, int64_t lda, int a_mn_major, const void* B, int64_t ldb, int b_mn_major, void* C,

@@ -14,8 +14,8 @@ from dataclasses import dataclass
 import torch
 from torch import nn
 
-from . import ops
-from .vocab_parallel import exchange_stats, reduce_grad_hidden
+from . import _abi, ops
+from .vocab_parallel import exchange_stats, reduce_grad_hidden, reduce_grad_hidden_async
 
 
 _SAVE_LOGITS = True
@@ -62,8 +62,16 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         coef_lp, coef_ent = g[:, 0].contiguous(), g[:, 1].contiguous()
         need_h, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         saved, ctx.saved = ctx.saved, None  # consumed in place by the backward; a second backward recomputes
-        gh, gw = ops.lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, ctx.inv_temperature, ctx.v_offset,
-                                need_grad_hidden=need_h, need_grad_weight=need_w, saved=saved)
+        args = (hidden, weight, targets, lse, entropy, coef_lp, coef_ent, ctx.inv_temperature, ctx.v_offset)
+        if ctx.group is not None and need_h and need_w:
+            # vocab-parallel: dH = sum over shards is all-reduced on NCCL's stream WHILE this rank's dW GEMM runs
+            gh, _ = ops.lmhead_bwd(*args, need_grad_weight=False, saved=saved, stages=_abi.BWD_DLOGITS | _abi.BWD_DH)
+            pending = reduce_grad_hidden_async(gh, ctx.group)
+            _, gw = ops.lmhead_bwd(*args, need_grad_hidden=False, saved=saved, stages=_abi.BWD_DW)
+            if pending is not None:
+                pending.wait()
+            return gh, gw, None, None, None, None
+        gh, gw = ops.lmhead_bwd(*args, need_grad_hidden=need_h, need_grad_weight=need_w, saved=saved)
         if gh is not None and ctx.group is not None:
             reduce_grad_hidden(gh, ctx.group)  # dH = sum over vocab shards
         return gh, gw, None, None, None, None

@@ -79,25 +79,36 @@ def lmhead_finalize(stats: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, to
 
 def lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, inv_temperature, v_offset=0, grad_scale=None,
                need_grad_hidden=True, need_grad_weight=True, grad_weight_out: torch.Tensor | None = None,
-               accumulate: bool = False, saved: torch.Tensor | None = None):
-    """K2: (grad_hidden bf16 [M,H] | None, grad_weight [V,H] | None).  ``saved`` (from the forward) is consumed."""
+               accumulate: bool = False, saved: torch.Tensor | None = None, stages: int | None = None,
+               grad_hidden_out: torch.Tensor | None = None):
+    """K2: (grad_hidden bf16 [M,H] | None, grad_weight [V,H] | None).  ``saved`` (from the forward) is consumed.
+
+    ``stages`` (``_abi.BWD_*`` bits) splits the backward: a first call with ``BWD_DLOGITS | BWD_DH`` and a second with
+    ``BWD_DW`` (same ``saved``, nothing re-formed) let the caller put a collective on grad_hidden in between."""
     _req(hidden, torch.bfloat16, "hidden"); _req(weight, torch.bfloat16, "weight"); _req(targets, torch.int64, "targets")
     for name, t in (("lse", lse), ("entropy", entropy), ("coef_lp", coef_lp), ("coef_ent", coef_ent)):
         _req(t, torch.float32, name)
     M, H = hidden.shape
     V = weight.shape[0]
-    gh = torch.empty(M, H, dtype=torch.bfloat16, device=hidden.device) if need_grad_hidden else None
+    if stages is not None:
+        need_grad_hidden = need_grad_hidden and bool(stages & _abi.BWD_DH)
+        need_grad_weight = need_grad_weight and bool(stages & _abi.BWD_DW)
+    gh = None
+    if need_grad_hidden:
+        gh = grad_hidden_out if grad_hidden_out is not None else torch.empty(M, H, dtype=torch.bfloat16, device=hidden.device)
     gw = None
     if need_grad_weight:
         gw = grad_weight_out if grad_weight_out is not None else torch.empty(V, H, dtype=torch.bfloat16, device=hidden.device)
         assert gw.shape == (V, H) and gw.is_contiguous() and gw.dtype in (torch.bfloat16, torch.float32)
     n = lib().b200grpo_lmhead_bwd_workspace(M, H, V, int(saved is not None))
     ws = _workspace(hidden.device, n, "dlogits")
-    check(lib().b200grpo_lmhead_bwd(hidden.data_ptr(), H, weight.data_ptr(), H, targets.data_ptr(), lse.data_ptr(),
-                                    entropy.data_ptr(), coef_lp.data_ptr(), coef_ent.data_ptr(), _ptr(grad_scale), M, H, V,
-                                    v_offset, float(inv_temperature), _ptr(saved), _ptr(gh), H, _ptr(gw), H,
-                                    int(gw is not None and gw.dtype == torch.float32), int(accumulate), ws.data_ptr(),
-                                    ws.numel(), _stream()))
+    args = (hidden.data_ptr(), H, weight.data_ptr(), H, targets.data_ptr(), lse.data_ptr(), entropy.data_ptr(), coef_lp.data_ptr(),
+            coef_ent.data_ptr(), _ptr(grad_scale), M, H, V, v_offset, float(inv_temperature), _ptr(saved), _ptr(gh), H, _ptr(gw), H,
+            int(gw is not None and gw.dtype == torch.float32), int(accumulate))
+    if stages is None:
+        check(lib().b200grpo_lmhead_bwd(*args, ws.data_ptr(), ws.numel(), _stream()))
+    else:
+        check(lib().b200grpo_lmhead_bwd_staged(*args, int(stages), ws.data_ptr(), ws.numel(), _stream()))
     return gh, gw
 
 

@@ -39,6 +39,14 @@ def reduce_grad_hidden(grad_hidden: torch.Tensor, group=None) -> torch.Tensor:
     return grad_hidden
 
 
+def reduce_grad_hidden_async(grad_hidden: torch.Tensor, group=None):
+    """Start dH = sum over vocab shards on NCCL's own stream (ordered after the work already queued on the current
+    stream); returns a handle whose ``wait()`` orders the current stream after the reduction, or None for one rank."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        return dist.all_reduce(grad_hidden, group=group, async_op=True)
+    return None
+
+
 def shard_weight(weight: torch.Tensor, world: int, rank: int) -> tuple[torch.Tensor, int]:
     """(this rank's rows as a contiguous tensor, v_offset)."""
     b, e = shard_range(weight.shape[0], world, rank)

@@ -452,3 +452,29 @@ def test_rl_step_through_the_value_head_wrapper():
     assert model.value_head.weight.grad is not None and float(model.value_head.weight.grad.abs().sum()) > 0
     assert model.pretrained_model.lm_head.weight.grad is not None
     assert torch.isfinite(loss).item()
+
+
+@pytest.mark.parametrize("save", [False, True])
+def test_lmhead_bwd_in_two_stages_is_bit_identical(save):
+    """stages = DLOGITS|DH then DW (what the vocab-parallel path does around its all-reduce) == the single call."""
+    from pipelinerl_swe_b200 import _abi, ops
+    d = _dev()
+    M, H, V, temp = 700, 256, 30000 + 8, 0.9
+    g = torch.Generator(device=d).manual_seed(12)
+    h = torch.randn(M, H, device=d, generator=g).bfloat16()
+    w = (torch.randn(V, H, device=d, generator=g) * 0.05).bfloat16()
+    tgt = torch.randint(0, V, (M,), device=d, generator=g)
+    c = torch.randn(2, M, device=d, generator=g) * 0.1
+    outs = []
+    for staged in (False, True):
+        saved = ops.lmhead_saved_buffer(M, H, V, d) if save else None
+        lp, ent, lse = ops.lmhead_finalize(ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp, saved=saved))
+        args = (h, w, tgt, lse, ent, c[0].contiguous(), c[1].contiguous(), 1.0 / temp)
+        if staged:
+            gh, none_w = ops.lmhead_bwd(*args, saved=saved, stages=_abi.BWD_DLOGITS | _abi.BWD_DH)
+            none_h, gw = ops.lmhead_bwd(*args, saved=saved, stages=_abi.BWD_DW)
+            assert none_w is None and none_h is None
+        else:
+            gh, gw = ops.lmhead_bwd(*args, saved=saved)
+        outs.append((gh.clone(), gw.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
