@@ -2,26 +2,30 @@
 //
 //   D[M,N] (f32 in TMEM) = A[M,K] . B[N,K]^T          bf16 operands, fp32 accumulate
 //
-// One CTA (or a cta_group::2 pair) owns 128 (256) rows x BLOCK_N columns per tile:
+// One CTA owns 128 * kMRep rows x BLOCK_N columns of a tile (a cta_group::2 pair: twice the rows):
 //   warp 0 lane 0 : TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem ring)
-//   warp 1 lane 0 : MMA issuer    (tcgen05.mma, accumulators double-buffered in TMEM)
+//   warp 1 lane 0 : MMA issuer    (tcgen05.mma; kMRep MMAs per k-step share one B tile in shared memory)
 //   warp 2        : TMEM allocator
-//   warps 4..7    : epilogue      (tcgen05.ld: thread == accumulator row, 32 cols per load)
-// Pipelines: smem full/empty mbarriers (TMA <-> MMA) and TMEM full/empty mbarriers
-// (MMA <-> epilogue), so the epilogue of tile i overlaps the MMAs of tile i+1.
+//   warps 4..7    : epilogue of accumulator rows 0-127   (tcgen05.ld: thread == row, 32 columns per load)
+//   warps 8..11   : epilogue of accumulator rows 128-255 (kMRep == 2 only)
+// Pipelines: smem full/empty mbarriers (TMA <-> MMA) and TMEM full/empty mbarriers (MMA <-> epilogue).
+// kMRep == 1: two accumulator stages, the epilogue of tile i overlaps the MMAs of tile i+1.
+// kMRep == 2: one accumulator stage (all 512 TMEM columns), 25 % fewer operand bytes per FLOP into the SM;
+//             for long-K GEMMs with a light epilogue (dH).
 //
-// Work decomposition: item = (output tile, k-split), dealt round-robin to the resident
-// clusters.  Tiles are rasterised in groups of `group_m` row blocks (row block fastest inside
-// a group) so that the clusters running together share operand tiles through L2:
-//   lm_head fwd / recompute : group_m = all row blocks -> the 74 live tiles read the same 2-3
-//                             weight tiles while hidden stays L2 resident;
-//   dW (tokens are K)       : group_m small -> one dlogits column slab is shared by the 14
-//                             n-tiles of its row block while hidden^T stays L2 resident;
+// Work decomposition: items dealt round-robin to the resident clusters.  An item is an output tile, a
+// (tile, k-split) pair (uniform split-K), or -- tail split -- a K-piece of one of the tiles of the last partial
+// wave (tiles % clusters), cut so that the last wave costs 1/pieces of a full one (decode_item).  Tiles are
+// rasterised in groups of `group_m` row blocks (row block fastest inside a group) so that the clusters running
+// together share operand tiles through L2:
+//   lm_head fwd / recompute : group_m = 16 row blocks -> the 74 live tiles read the same 4-5 weight tiles
+//                             while their slice of hidden stays L2 resident;
+//   dW (tokens are K)       : group_m = 1 -> one dlogits column slab is shared by the 14 n-tiles of its row
+//                             block (fewest bytes in flight per wave, profiles/r01/tile_variants_ab.md);
 //   dH (vocab is K)         : square-ish patches (both operands stream, nothing is resident).
-// Every epilogue is stateless per tile (the forward writes per-tile softmax partials that a
-// merge kernel combines), which is what makes the tile order free.  k-splits (EPI_STORE only)
-// write f32 partial slabs reduced by a second kernel: they remove wave quantisation when the
-// tile count is a poor multiple of the cluster count (dH: 448 tiles on 74 clusters).
+// Every epilogue is stateless per tile (the forward writes per-tile softmax partials that a merge kernel
+// combines), which is what makes the tile order free.  Split pieces (EPI_STORE only) go to f32 slabs summed in
+// fixed order by a second kernel (deterministic).
 #pragma once
 #include "common.cuh"
 #include "sm100_ptx.cuh"
