@@ -56,8 +56,13 @@ def completion_spans(traces: Sequence[dict[str, Any]]) -> list[tuple[int, int]]:
 
 @torch.no_grad()
 def annotate_traces_with_ref_logprobs(model, traces: list[dict[str, Any]], max_tokens: int = 8192, temperature: float = 1.0,
-                                      device: torch.device | str | None = None, group=None, v_offset: int = 0) -> list[dict[str, Any]]:
-    """Fill ``trace["ref_logprobs"]`` for every trace from ``model`` (a frozen copy of the policy).  In place."""
+                                      device: torch.device | str | None = None, group=None, v_offset: int = 0,
+                                      pack: bool = True) -> list[dict[str, Any]]:
+    """Fill ``trace["ref_logprobs"]`` for every trace from ``model`` (a frozen copy of the policy).  In place.
+
+    ``pack=True`` relies, like the reference's packed training batches (finetune_loop.py:279-287), on an attention
+    implementation that separates packed sequences by their restarting ``position_ids`` (flash-attention varlen);
+    with any other attention pass ``pack=False``: one trace per forward row."""
     if not traces:
         return traces
     dev = torch.device(device) if device is not None else next(model.parameters()).device
@@ -68,7 +73,7 @@ def annotate_traces_with_ref_logprobs(model, traces: list[dict[str, Any]], max_t
     was_training = model.training
     model.eval()
     try:
-        for pack in plan_packs([n for n, _ in spans], max_tokens):
+        for pack in plan_packs([n for n, _ in spans], max_tokens if pack else 0):
             ids = torch.tensor([t for i in pack for t in traces[i]["input_ids"]], dtype=torch.long).unsqueeze(0)
             pos = torch.cat([torch.arange(spans[i][0]) for i in pack]).unsqueeze(0)
             ids_d, pos_d = ids.to(dev, non_blocking=True), pos.to(dev, non_blocking=True)
