@@ -73,9 +73,9 @@ def annotate_traces_with_ref_logprobs(model, traces: list[dict[str, Any]], max_t
     was_training = model.training
     model.eval()
     try:
-        for pack in plan_packs([n for n, _ in spans], max_tokens if pack else 0):
-            ids = torch.tensor([t for i in pack for t in traces[i]["input_ids"]], dtype=torch.long).unsqueeze(0)
-            pos = torch.cat([torch.arange(spans[i][0]) for i in pack]).unsqueeze(0)
+        for members in plan_packs([n for n, _ in spans], max_tokens if pack else 0):
+            ids = torch.tensor([t for i in members for t in traces[i]["input_ids"]], dtype=torch.long).unsqueeze(0)
+            pos = torch.cat([torch.arange(spans[i][0]) for i in members]).unsqueeze(0)
             ids_d, pos_d = ids.to(dev, non_blocking=True), pos.to(dev, non_blocking=True)
             with logprob_request(LogprobRequest(ids_d, float(temperature), group, v_offset)):
                 out = model(input_ids=ids_d, attention_mask=torch.ones_like(ids_d), position_ids=pos_d)
@@ -84,7 +84,7 @@ def annotate_traces_with_ref_logprobs(model, traces: list[dict[str, Any]], max_t
                 raise _abi.B200GrpoError("model did not route through FusedLMHead (logits last dim != 2)")
             lp = lp_ent[0, :, 0].float().cpu()  # position p scores token p + 1
             off = 0
-            for i in pack:
+            for i in members:
                 n, c = spans[i]
                 traces[i]["ref_logprobs"] = lp[off + n - c - 1: off + n - 1].tolist()
                 assert len(traces[i]["ref_logprobs"]) == len(traces[i]["logprobs"]), (
