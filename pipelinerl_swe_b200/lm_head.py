@@ -32,6 +32,26 @@ def set_save_logits(flag: bool) -> None:
     _SAVE_LOGITS = bool(flag)
 
 
+_SKIP_MASKED = False
+
+
+def skip_masked_tokens_enabled() -> bool:
+    return _SKIP_MASKED
+
+
+def set_skip_masked_tokens(flag: bool) -> None:
+    """Opt-in: compute the lm_head path only for positions whose next token is labelled.
+
+    The reference projects every position to the vocabulary and then multiplies everything it derived from
+    them by ``labels != -100`` (rl/__init__.py:152-157, rl/utils.py:25-30): the log-prob, entropy and gradient
+    of a position whose next token is a prompt / observation token never reach the loss or a statistic.  With
+    this on, those rows are left out of the three GEMMs (their outputs read 0), so a batch with a fraction f of
+    masked tokens costs (1 - f) of the FLOPs; labelled positions get bit-identical log-probs.  Costs one extra
+    host sync per step (the number of labelled rows sizes the launch).  Off by default: exact drop-in."""
+    global _SKIP_MASKED
+    _SKIP_MASKED = bool(flag)
+
+
 class LMHeadLogprobFunction(torch.autograd.Function):
     """(hidden [M,H] bf16, weight [Vloc,H] bf16, targets [M] i64) -> out f32 [M,2] = (logprob, entropy).
 
@@ -78,11 +98,12 @@ class LMHeadLogprobFunction(torch.autograd.Function):
 
 
 def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch.Tensor, temperature: float, group=None,
-                    v_offset: int = 0) -> torch.Tensor:
+                    v_offset: int = 0, labels: torch.Tensor | None = None) -> torch.Tensor:
     """hidden [B,L,H], input_ids [B,L] -> f32 [B,L,2]: (logprob of input_ids[t+1], entropy) per position.
 
     Position L-1 of every row has no next token: it is scored against token 0 and the
     caller drops it (the reference slices ``[:, :-1]``, rl/__init__.py:200,208).
+    With ``labels`` and ``set_skip_masked_tokens(True)`` only positions whose next token is labelled are computed.
     """
     B, L, H = hidden.shape
     targets = torch.roll(input_ids, shifts=-1, dims=1).reshape(-1).contiguous()
@@ -90,7 +111,18 @@ def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch
     if h2.dtype != torch.bfloat16:
         h2 = h2.to(torch.bfloat16)
     w = weight if weight.dtype == torch.bfloat16 else weight.to(torch.bfloat16)
-    out = LMHeadLogprobFunction.apply(h2.contiguous(), w.contiguous(), targets, 1.0 / float(temperature), group, v_offset)
+    inv_t = 1.0 / float(temperature)
+    if labels is not None and skip_masked_tokens_enabled():
+        keep = torch.roll(labels, shifts=-1, dims=1) != -100
+        keep[:, -1] = False                                  # no next token
+        idx = keep.reshape(-1).nonzero().squeeze(1)          # host sync: the row count sizes the launch
+        out = torch.zeros(B * L, 2, dtype=torch.float32, device=hidden.device)
+        if idx.numel() > 0:
+            part = LMHeadLogprobFunction.apply(h2.index_select(0, idx), w.contiguous(), targets.index_select(0, idx), inv_t, group,
+                                               v_offset)
+            out = out.index_copy(0, idx, part)               # autograd scatters the gradient rows back (zeros elsewhere)
+        return out.reshape(B, L, 2)
+    out = LMHeadLogprobFunction.apply(h2.contiguous(), w.contiguous(), targets, inv_t, group, v_offset)
     return out.reshape(B, L, 2)
 
 
@@ -101,6 +133,7 @@ class LogprobRequest:
     temperature: float
     group: object = None
     v_offset: int = 0
+    labels: torch.Tensor | None = None   # only read when set_skip_masked_tokens(True)
 
 
 _tls = threading.local()
@@ -146,7 +179,7 @@ class FusedLMHead(nn.Module):
             if type(self) is FusedLMHead:
                 return nn.functional.linear(hidden, self.weight)
             return super().forward(hidden)  # the original class's own forward (plain Linear, LoRA-wrapped, ...)
-        return lmhead_logprobs(hidden, self.weight, req.input_ids, req.temperature, req.group, req.v_offset)
+        return lmhead_logprobs(hidden, self.weight, req.input_ids, req.temperature, req.group, req.v_offset, req.labels)
 
 
 def _check_fusable(linear: nn.Module) -> None:

@@ -130,7 +130,7 @@ def _forward_loss(model, batch, current_step: int, max_step: int, config):
         model_inputs["pixel_values"] = b["pixel_values"]
     if b["image_grid_thw"] is not None:
         model_inputs["image_grid_thw"] = b["image_grid_thw"]
-    with logprob_request(LogprobRequest(b["input_ids"], float(config.temperature))):
+    with logprob_request(LogprobRequest(b["input_ids"], float(config.temperature), labels=b["labels"])):
         outputs = model(**model_inputs)
     lp_ent = outputs.logits
     if lp_ent.shape[-1] != 2:

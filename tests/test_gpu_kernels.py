@@ -318,3 +318,35 @@ def test_rl_step_on_ingested_batch_equals_collated_batch():
     l1, s1 = rl_step(model, collate_packed(copy.deepcopy(ex), StubTokenizer(), 1).to_device(_dev()), 0, 1, cfg)
     l2, s2 = rl_step(model, ingest_packed(copy.deepcopy(ex), StubTokenizer(), 1, _dev()), 0, 1, cfg)
     assert l1.item() == l2.item() and s1 == s2
+
+
+# ---------------------------------------------------------------------------------------------
+# opt-in: leave positions whose next token is not labelled out of the lm_head GEMMs
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n_prompt", [40, 400])
+def test_skip_masked_tokens_gives_the_same_step(n_prompt):
+    from pipelinerl_swe_b200 import RLConfig, rl_step, set_skip_masked_tokens
+    from pipelinerl_swe_b200 import _abi
+    H, V, lens = 128, 4096 + 8, [300, 150, 420, 90]
+    T = sum(lens)
+    batch = synthetic_packed_batch(lens, V, seed=13, n_prompt=n_prompt)     # n_prompt=400: two rollouts are (almost) all prompt
+    res = []
+    for skip in (False, True):
+        model = StubLM(H, V, T, seed=4).to(_dev())
+        near_policy_logprobs(batch, model.hidden.detach().cpu()[0], model.lm_head.weight.detach().cpu(), 1.0, seed=2)
+        cfg = RLConfig(batch_size=4, kl_coef=0.1, final_kl_coef=0.1, entropy_bonus=0.01, final_entropy_bonus=0.01)
+        n0 = _abi.launch_count()
+        try:
+            set_skip_masked_tokens(skip)
+            loss, stats = rl_step(model, _to_dev(batch), 0, 1, cfg)
+            loss.backward()
+        finally:
+            set_skip_masked_tokens(False)
+        res.append((loss.item(), stats, model.lm_head.weight.grad.float().clone(), model.hidden.grad.float().clone()))
+    (l0, s0, gw0, gh0), (l1, s1, gw1, gh1) = res
+    assert abs(l0 - l1) <= 1e-6 * abs(l0) + 1e-9
+    assert_stats_close(s1, s0, rtol=1e-5, atol=1e-7)
+    assert float((gw0 - gw1).abs().max()) <= 2e-2 * float(gw0.abs().max())      # bf16 outputs, different token-sum order
+    assert float((gh0 - gh1).abs().max()) <= 2e-2 * float(gh0.abs().max())
+    labelled_next = (batch["labels"][0, 1:] != -100)
+    assert float(gh1[0, :-1][~labelled_next].abs().max()) == 0.0                  # skipped rows get exactly zero gradient
