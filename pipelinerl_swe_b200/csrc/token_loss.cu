@@ -3,7 +3,7 @@
 // rl/utils.py:25-30,66-87 (see include/b200grpo.h for the slot layout).
 //
 // HBM-bound byte work: 60 B/token algorithmic (9 f32 + 2 i64 in, 2 f32 out).  Grid is a
-// multiple of the SM count, coalesced 4-wide unrolled loads, warp-shuffle block reduce,
+// multiple of the SM count, coalesced loads all issued before the arithmetic, warp-shuffle block reduce,
 // deterministic last-block finish (no float atomics), one f64 vector out.
 #include "common.cuh"
 #include <float.h>
@@ -11,7 +11,11 @@
 namespace b200grpo {
 
 constexpr int TL_THREADS = 256;
-constexpr int TL_UNROLL = 4;
+// Measured on B200 at 8 M tokens (tools/bench_small_kernels.py --only k3): one token per thread per trip with three
+// resident CTAs per SM (80 registers) reaches 0.52 of the HBM peak; 2 or 4 tokens per trip cost registers, hence
+// occupancy, and are slower (0.38 / 0.28)
+constexpr int TL_UNROLL = 1;
+constexpr int TL_MINB = 3;
 constexpr int N_SUM = B200GRPO_M_MAX_REWARD;  // slots [0, N_SUM) reduce by +
 constexpr int N_EXT = 10;                     // max/min pairs: reward, adv, kl, tw, value
 
@@ -36,14 +40,17 @@ __device__ __forceinline__ float masked_term(float v, bool m) {
   return fminf(fmaxf(v, -FLT_MAX), FLT_MAX);
 }
 
-__global__ void __launch_bounds__(TL_THREADS) token_loss_kernel(const TokenLossArgs a) {
+__global__ void __launch_bounds__(TL_THREADS, TL_MINB) token_loss_kernel(const TokenLossArgs a) {
   const b200grpo_loss_cfg& c = a.cfg;
   const int L = a.L, Ls = a.L - 1;
   const long long n = (long long)a.rows * Ls;
-  double s[N_SUM];
+  // per-thread partial sums: f32 for the 24 statistics (a thread sees 1-2 tokens of a real micro-batch, <= ~110 at the
+  // 8 M-token bandwidth test), f64 for the two loss terms; everything is f64 from the warp reduction on
+  float s[N_SUM];
+  double s_loss = 0.0, s_vloss = 0.0;
   float ext[N_EXT];
 #pragma unroll
-  for (int i = 0; i < N_SUM; ++i) s[i] = 0.0;
+  for (int i = 0; i < N_SUM; ++i) s[i] = 0.f;
 #pragma unroll
   for (int i = 0; i < N_EXT; i += 2) { ext[i] = -INFINITY; ext[i + 1] = INFINITY; }
   unsigned flags = 0;
@@ -52,24 +59,50 @@ __global__ void __launch_bounds__(TL_THREADS) token_loss_kernel(const TokenLossA
 
   const long long stride = (long long)gridDim.x * TL_THREADS;
   for (long long base = (long long)blockIdx.x * TL_THREADS + threadIdx.x; base < n; base += stride * TL_UNROLL) {
+    // ---- phase 1: every load of TL_UNROLL tokens is issued before any arithmetic (11-13 independent 4/8-byte
+    // coalesced loads per token in flight per thread; the stores below cannot alias them: __restrict__) ----
+    float v_lp[TL_UNROLL], v_ent[TL_UNROLL], v_rew[TL_UNROLL], v_ref[TL_UNROLL], v_old[TL_UNROLL], v_gt[TL_UNROLL],
+        v_nl[TL_UNROLL], v_ovf[TL_UNROLL], v_adv[TL_UNROLL], v_val[TL_UNROLL];
+    int v_r[TL_UNROLL], v_t[TL_UNROLL];
+    bool v_m[TL_UNROLL];
+    int v_nseq[TL_UNROLL];
 #pragma unroll
     for (int u = 0; u < TL_UNROLL; ++u) {
       const long long i = base + u * stride;
-      if (i >= n) break;
+      v_t[u] = -1;
+      if (i >= n) continue;
       int r = 0, t = (int)i;                         // packed rows (rows == 1) need no division
       if (a.rows > 1) {
         if (n < (1ll << 31)) { r = (int)((unsigned)i / (unsigned)Ls); t = (int)i - r * Ls; }
         else { r = (int)(i / Ls); t = (int)(i - (long long)r * Ls); }
       }
       const long long j = (long long)r * L + t + 1;  // shifted view [:,1:]
-      const float lp = a.logprob[i], ent = a.entropy[i];
-      const bool m = a.labels[j] != -100;
-      const float rew = a.rewards[j], ref = a.ref_lp[j], old = a.old_lp[j];
-      const float gt = a.group_tokens[j], nl = a.num_labels[j];
+      v_r[u] = r; v_t[u] = t;
+      v_lp[u] = __ldg(a.logprob + i); v_ent[u] = __ldg(a.entropy + i);
+      v_m[u] = __ldg(a.labels + j) != -100;
+      v_rew[u] = __ldg(a.rewards + j); v_ref[u] = __ldg(a.ref_lp + j); v_old[u] = __ldg(a.old_lp + j);
+      v_gt[u] = __ldg(a.group_tokens + j); v_nl[u] = __ldg(a.num_labels + j);
+      v_ovf[u] = c.overlong_filtering ? __ldg(a.overflow + j) : 0.f;
+      v_val[u] = c.has_values ? __ldg(a.values + (j - 1)) : 0.f;
+      v_adv[u] = c.has_values ? 0.f : __ldg(a.advantages + j);
+      int ns = 0;
       if (c.is_packed) {  // segment starts in un-shifted coordinates (:159-171)
-        if (t == 0 || a.position_ids[j - 1] == 0) s[B200GRPO_M_N_SEQ] += 1.0;
-        if (t == Ls - 1 && a.position_ids[j] == 0) s[B200GRPO_M_N_SEQ] += 1.0;
+        if (t == 0 || __ldg(a.position_ids + (j - 1)) == 0) ++ns;
+        if (t == Ls - 1 && __ldg(a.position_ids + j) == 0) ++ns;
       }
+      v_nseq[u] = ns;
+    }
+    // ---- phase 2: arithmetic, in the same per-thread token order as the loads ----
+#pragma unroll
+    for (int u = 0; u < TL_UNROLL; ++u) {
+      if (v_t[u] < 0) continue;
+      const long long i = base + u * stride;
+      const int r = v_r[u], t = v_t[u];
+      const float lp = v_lp[u], ent = v_ent[u];
+      const bool m = v_m[u];
+      const float rew = v_rew[u], ref = v_ref[u], old = v_old[u];
+      const float gt = v_gt[u], nl = v_nl[u];
+      s[B200GRPO_M_N_SEQ] += (float)v_nseq[u];
       float tw;
       if (c.group_normalization) {
         if (!(gt > 0.f)) flags |= B200GRPO_F_GROUP_TOKENS_LE0;
@@ -77,15 +110,15 @@ __global__ void __launch_bounds__(TL_THREADS) token_loss_kernel(const TokenLossA
       } else {
         tw = inv_b;
       }
-      if (c.overlong_filtering) tw = tw * (1.0f - a.overflow[j]);
+      if (c.overlong_filtering) tw = tw * (1.0f - v_ovf[u]);
       if (!isfinite(lp)) flags |= B200GRPO_F_NEW_LP_NONFINITE;
       const float d_no = lp - old;
       float ratio = expf(d_no);
       const float d_rn = ref - lp;
       if (!isfinite(d_rn)) flags |= B200GRPO_F_REF_NEW_NONFINITE;
       float v_pred = 0.f, adv;
-      if (c.has_values) { v_pred = a.values[(long long)r * L + t]; adv = rew - v_pred; }
-      else adv = a.advantages[j];
+      if (c.has_values) { v_pred = v_val[u]; adv = rew - v_pred; }
+      else adv = v_adv[u];
       float w = c.use_advantages ? adv : rew;
       if (c.relu_log_p_weights) w = fmaxf(w, 0.f);
       const bool kl_clamped = fabsf(d_rn) > C;
@@ -111,8 +144,8 @@ __global__ void __launch_bounds__(TL_THREADS) token_loss_kernel(const TokenLossA
         dpol = w * ratio;
       }
       const float per_tok = (policy - c.kl_coef * kl + c.entropy_coef * ent) * tw;
-      if (isnan(per_tok)) s[B200GRPO_M_NUM_NANS] += 1.0;
-      s[B200GRPO_M_LOSS] += (double)masked_term(per_tok, m);
+      if (isnan(per_tok)) s[B200GRPO_M_NUM_NANS] += 1.f;
+      s_loss += (double)masked_term(per_tok, m);
       // gradient coefficients for an upstream gradient of 1
       const float inside = (d_rn >= -C && d_rn <= C) ? 1.f : 0.f;
       const float mw = m ? tw : 0.f;
@@ -120,9 +153,9 @@ __global__ void __launch_bounds__(TL_THREADS) token_loss_kernel(const TokenLossA
       a.coef_ent[i] = -mw * c.entropy_coef;
       if (c.has_values) {
         const float dv = v_pred - rew;
-        s[B200GRPO_M_VALUE_LOSS] += (double)masked_term(0.5f * dv * dv * tw, m);
-        s[B200GRPO_M_VALUE_MEAN] += (double)masked_term(v_pred / nl, m);
-        s[B200GRPO_M_VALUE_MSE] += (double)masked_term(dv * dv / nl, m);
+        s_vloss += (double)masked_term(0.5f * dv * dv * tw, m);
+        s[B200GRPO_M_VALUE_MEAN] += masked_term(v_pred / nl, m);
+        s[B200GRPO_M_VALUE_MSE] += masked_term(dv * dv / nl, m);
         if (a.coef_value) {
           a.coef_value[(long long)r * L + t] = c.value_loss_coef * dv * mw;
           if (t == Ls - 1) a.coef_value[(long long)r * L + t + 1] = 0.f;
@@ -130,31 +163,31 @@ __global__ void __launch_bounds__(TL_THREADS) token_loss_kernel(const TokenLossA
         if (m) { ext[8] = fmaxf(ext[8], v_pred); ext[9] = fminf(ext[9], v_pred); }
       }
       if (m) {  // masked-out tokens contribute exact zeros to every sum below (masked_term): skip them
-        s[B200GRPO_M_N_MASKED] += 1.0;
+        s[B200GRPO_M_N_MASKED] += 1.f;
         ext[0] = fmaxf(ext[0], rew); ext[1] = fminf(ext[1], rew);
         ext[2] = fmaxf(ext[2], adv); ext[3] = fminf(ext[3], adv);
         ext[4] = fmaxf(ext[4], kl);  ext[5] = fminf(ext[5], kl);
         ext[6] = fmaxf(ext[6], tw);  ext[7] = fminf(ext[7], tw);
         // x / num_labels as x * (1 / num_labels): one division per token instead of seventeen (<= 1 ulp apart)
         const float inv_nl = 1.0f / nl;
-        s[B200GRPO_M_REWARD] += (double)masked_term(rew * inv_nl, true);
-        s[B200GRPO_M_ENTROPY] += (double)masked_term(ent * inv_nl, true);
-        s[B200GRPO_M_OLD_LP] += (double)masked_term(old * inv_nl, true);
-        s[B200GRPO_M_NEW_LP] += (double)masked_term(lp * inv_nl, true);
-        s[B200GRPO_M_REF_LP] += (double)masked_term(ref * inv_nl, true);
-        s[B200GRPO_M_ADVANTAGE] += (double)masked_term(adv * inv_nl, true);
-        s[B200GRPO_M_KL] += (double)masked_term(kl * inv_nl, true);
-        s[B200GRPO_M_POLICY] += (double)masked_term(policy * inv_nl, true);
-        s[B200GRPO_M_SURR1] += (double)masked_term(surr1 * inv_nl, true);
-        s[B200GRPO_M_SURR2] += (double)masked_term(surr2 * inv_nl, true);
-        s[B200GRPO_M_RATIO] += (double)masked_term(ratio * inv_nl, true);
-        s[B200GRPO_M_RATIO_SUM] += (double)masked_term(ratio, true);
-        s[B200GRPO_M_RATIO_SQ_SUM] += (double)masked_term(ratio * ratio, true);
-        s[B200GRPO_M_RATIO_REF_NEW] += (double)masked_term(expf(d_rn) * inv_nl, true);
-        s[B200GRPO_M_RATIO_REF_OLD] += (double)masked_term(expf(ref - old) * inv_nl, true);
-        s[B200GRPO_M_CLAMP_REF_NEW] += (double)masked_term(kl_clamped ? inv_nl : 0.f, true);
-        s[B200GRPO_M_CLAMP_NEW_OLD] += (double)masked_term(r_clamped ? inv_nl : 0.f, true);
-        s[B200GRPO_M_TOKEN_WEIGHT] += (double)masked_term(tw * inv_nl, true);
+        s[B200GRPO_M_REWARD] += masked_term(rew * inv_nl, true);
+        s[B200GRPO_M_ENTROPY] += masked_term(ent * inv_nl, true);
+        s[B200GRPO_M_OLD_LP] += masked_term(old * inv_nl, true);
+        s[B200GRPO_M_NEW_LP] += masked_term(lp * inv_nl, true);
+        s[B200GRPO_M_REF_LP] += masked_term(ref * inv_nl, true);
+        s[B200GRPO_M_ADVANTAGE] += masked_term(adv * inv_nl, true);
+        s[B200GRPO_M_KL] += masked_term(kl * inv_nl, true);
+        s[B200GRPO_M_POLICY] += masked_term(policy * inv_nl, true);
+        s[B200GRPO_M_SURR1] += masked_term(surr1 * inv_nl, true);
+        s[B200GRPO_M_SURR2] += masked_term(surr2 * inv_nl, true);
+        s[B200GRPO_M_RATIO] += masked_term(ratio * inv_nl, true);
+        s[B200GRPO_M_RATIO_SUM] += masked_term(ratio, true);
+        s[B200GRPO_M_RATIO_SQ_SUM] += masked_term(ratio * ratio, true);
+        s[B200GRPO_M_RATIO_REF_NEW] += masked_term(expf(d_rn) * inv_nl, true);
+        s[B200GRPO_M_RATIO_REF_OLD] += masked_term(expf(ref - old) * inv_nl, true);
+        s[B200GRPO_M_CLAMP_REF_NEW] += masked_term(kl_clamped ? inv_nl : 0.f, true);
+        s[B200GRPO_M_CLAMP_NEW_OLD] += masked_term(r_clamped ? inv_nl : 0.f, true);
+        s[B200GRPO_M_TOKEN_WEIGHT] += masked_term(tw * inv_nl, true);
       }
     }
   }
@@ -167,7 +200,7 @@ __global__ void __launch_bounds__(TL_THREADS) token_loss_kernel(const TokenLossA
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll
   for (int i = 0; i < N_SUM; ++i) {
-    const double v = warp_sum(s[i]);
+    const double v = warp_sum(i == B200GRPO_M_LOSS ? s_loss : i == B200GRPO_M_VALUE_LOSS ? s_vloss : (double)s[i]);
     if (lane == 0) sh_sum[warp][i] = v;
   }
 #pragma unroll
@@ -243,7 +276,7 @@ static int token_loss_grid(long long n) {
   const int sms = sm_count();
   long long want = (n + (long long)TL_THREADS * TL_UNROLL - 1) / ((long long)TL_THREADS * TL_UNROLL);
   if (want < 1) want = 1;
-  const long long cap = (long long)sms * 8;  // 8 resident 256-thread CTAs per SM
+  const long long cap = (long long)sms * TL_MINB;  // resident 256-thread CTAs per SM
   if (want > cap) want = cap;
   if (want > sms) want = want / sms * sms;   // whole waves
   return (int)want;
@@ -305,7 +338,8 @@ extern "C" int b200grpo_token_loss(const float* logprob, const float* entropy, c
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA_OK(cudaMemsetAsync(a.ticket, 0, sizeof(unsigned), st));
   ProfScope ps(PROF_TOKEN_LOSS, st);
-  token_loss_kernel<<<grid, TL_THREADS, 0, st>>>(a); count_launch();
+  token_loss_kernel<<<grid, TL_THREADS, 0, st>>>(a);
+  count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }

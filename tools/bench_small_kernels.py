@@ -41,6 +41,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--once", action="store_true")
+    ap.add_argument("--only", default="", help="comma list of: k3,segments,k4,ingest,k6,dlogits (default: all)")
     args = ap.parse_args()
     from helpers import StubTokenizer, synthetic_packed_batch, synthetic_rollout_examples
     from pipelinerl_swe_b200 import RLConfig, ops, rl
@@ -73,8 +74,10 @@ def main():
         print(json.dumps(line), flush=True)
 
     g = torch.Generator(device=dev).manual_seed(0)
+    only = set(filter(None, args.only.split(",")))
+    want = lambda name: not only or name in only  # noqa: E731
     # ---- K3 token loss: 60 B/token in (11 fields incl. logprob/entropy) + 8 B/token coefficients out -----------
-    for T, n_seq in ((8192, 16), (1 << 20, 2048), (1 << 23, 16384)):
+    for T, n_seq in ((8192, 16), (1 << 20, 2048), (1 << 23, 16384)) if want("k3") else ():
         lens = [T // n_seq] * n_seq
         b = synthetic_packed_batch(lens, 152064, seed=1)
         bd = {k: (v.to(dev).contiguous() if isinstance(v, torch.Tensor) else v) for k, v in b.items()}
@@ -84,12 +87,12 @@ def main():
         ms = timed(lambda: ops.token_loss(lp, ent, bd, cfg))
         emit("token_loss (K3)", f"T={T} segments={n_seq}", 60 * T, ms, "8 B labels + 8 B position_ids + 7x4 B columns + 2x4 B logprob/entropy in, 2x4 B coefficients out")
     # ---- segment bounds: 8 B/token ---------------------------------------------------------------------------
-    for T in (1 << 20, 1 << 24):
+    for T in (1 << 20, 1 << 24) if want("segments") else ():
         pos = (torch.arange(T, device=dev) % 977).contiguous()
         ms = timed(lambda: ops.segment_bounds(pos))
         emit("segment_bounds", f"T={T}", 8 * T * 2, ms, "position_ids read twice (count pass + scatter pass)")
     # ---- K4 group advantages: 16 B/token out ------------------------------------------------------------------
-    for n_rows, n_tok in ((4096, 2048), (65536, 512)):
+    for n_rows, n_tok in ((4096, 2048), (65536, 512)) if want("k4") else ():
         reward = torch.rand(n_rows, device=dev, dtype=torch.float64, generator=g)
         gkey = (torch.arange(n_rows, device=dev, dtype=torch.int32) // 16).contiguous()
         offs = (torch.arange(n_rows + 1, device=dev, dtype=torch.int64) * n_tok).contiguous()
@@ -98,7 +101,7 @@ def main():
         ms = timed(lambda: ops.group_advantage(reward, gkey, offs, nlab, eos, n_rows // 16, True))
         emit("group_advantage (K4)", f"rollouts={n_rows} x {n_tok} tokens", 16 * n_rows * n_tok + 17 * n_rows, ms)
     # ---- packed ingest expansion: 16 B/token in, 60 B/token out -------------------------------------------------
-    for n_seq, n_tok in ((16, 512), (2048, 512)):
+    for n_seq, n_tok in ((16, 512), (2048, 512)) if want("ingest") else ():
         ex = synthetic_rollout_examples([n_tok] * n_seq, 152064, seed=2)
         wire = pack_rollouts(ex, StubTokenizer(), 1)
         T = wire.T
@@ -106,37 +109,39 @@ def main():
         emit("ingest: H2D + expand_packed", f"T={T} rollouts={n_seq}", 76 * T, ms,
              f"includes the {wire.nbytes} B pinned H2D copy and the output allocation; device traffic 16 B in + 60 B out per token")
     # ---- K6 bucket pack / unpack: 4 B/element (bf16 in + out) --------------------------------------------------
-    shapes = [(3584, 3584), (3584,), (512, 3584), (512,), (18944, 3584), (18944, 3584), (3584, 18944), (3584,), (3584,)] * 4
-    params = [torch.randn(*s, device=dev).bfloat16() for s in shapes]
-    n = ops.bucket_numel(params)
-    bucket = torch.empty(n, dtype=torch.bfloat16, device=dev)
-    ms = timed(lambda: ops.bucket_pack(params, bucket))
-    emit("bucket_pack (K6)", f"{len(params)} tensors, {2 * n / 1e9:.2f} GB", 4 * n, ms)
-    ms = timed(lambda: ops.bucket_unpack(bucket, params))
-    emit("bucket_unpack (K6)", f"{len(params)} tensors, {2 * n / 1e9:.2f} GB", 4 * n, ms)
-    masters = [p.float() for p in params[:18]]
-    n2 = ops.bucket_numel(masters)
-    b2 = torch.empty(n2, dtype=torch.bfloat16, device=dev)
-    ms = timed(lambda: ops.bucket_pack(masters, b2))
-    emit("bucket_pack (K6, fp32 masters)", f"{len(masters)} tensors, {2 * n2 / 1e9:.2f} GB out", 6 * n2, ms)
+    if want("k6"):
+        shapes = [(3584, 3584), (3584,), (512, 3584), (512,), (18944, 3584), (18944, 3584), (3584, 18944), (3584,), (3584,)] * 4
+        params = [torch.randn(*s, device=dev).bfloat16() for s in shapes]
+        n = ops.bucket_numel(params)
+        bucket = torch.empty(n, dtype=torch.bfloat16, device=dev)
+        ms = timed(lambda: ops.bucket_pack(params, bucket))
+        emit("bucket_pack (K6)", f"{len(params)} tensors, {2 * n / 1e9:.2f} GB", 4 * n, ms)
+        ms = timed(lambda: ops.bucket_unpack(bucket, params))
+        emit("bucket_unpack (K6)", f"{len(params)} tensors, {2 * n / 1e9:.2f} GB", 4 * n, ms)
+        masters = [p.float() for p in params[:18]]
+        n2 = ops.bucket_numel(masters)
+        b2 = torch.empty(n2, dtype=torch.bfloat16, device=dev)
+        ms = timed(lambda: ops.bucket_pack(masters, b2))
+        emit("bucket_pack (K6, fp32 masters)", f"{len(masters)} tensors, {2 * n2 / 1e9:.2f} GB out", 6 * n2, ms)
     # ---- dlogits pass + merge, at the C3 shape -----------------------------------------------------------------
-    M, H, V = 8191, 3584, 152064
-    h = torch.randn(M, H, device=dev, generator=g).bfloat16()
-    w = (torch.randn(V, H, device=dev, generator=g) * 0.02).bfloat16()
-    tgt = torch.randint(0, V, (M,), device=dev, generator=g)
-    saved = ops.lmhead_saved_buffer(M, H, V, dev)
-    stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0, saved=saved)
-    lp, ent, lse = ops.lmhead_finalize(stats)
-    c = torch.randn(2, M, device=dev, generator=g) * 0.1
-    from pipelinerl_swe_b200 import _abi
-    _abi.profile_enable(4096)
-    for _ in range(1 if args.once else 4):
-        ops.lmhead_bwd(h, w, tgt, lse, ent, c[0].contiguous(), c[1].contiguous(), 1.0, need_grad_hidden=False, need_grad_weight=False,
-                       saved=saved)
-    torch.cuda.synchronize()
-    if not args.once:
-        t = [ms for tag, ms in _abi.profile_read() if tag == "dlogits_pass"]
-        emit("dlogits_from_saved (K2a)", f"M={M} V={V}", 4 * M * V, sum(t[1:]) / len(t[1:]), "bf16 read + bf16 write in place; exp + 10 ALU per element")
+    if want("dlogits"):
+        M, H, V = 8191, 3584, 152064
+        h = torch.randn(M, H, device=dev, generator=g).bfloat16()
+        w = (torch.randn(V, H, device=dev, generator=g) * 0.02).bfloat16()
+        tgt = torch.randint(0, V, (M,), device=dev, generator=g)
+        saved = ops.lmhead_saved_buffer(M, H, V, dev)
+        stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0, saved=saved)
+        lp, ent, lse = ops.lmhead_finalize(stats)
+        c = torch.randn(2, M, device=dev, generator=g) * 0.1
+        from pipelinerl_swe_b200 import _abi
+        _abi.profile_enable(4096)
+        for _ in range(1 if args.once else 4):
+            ops.lmhead_bwd(h, w, tgt, lse, ent, c[0].contiguous(), c[1].contiguous(), 1.0, need_grad_hidden=False, need_grad_weight=False,
+                           saved=saved)
+        torch.cuda.synchronize()
+        if not args.once:
+            t = [ms for tag, ms in _abi.profile_read() if tag == "dlogits_pass"]
+            emit("dlogits_from_saved (K2a)", f"M={M} V={V}", 4 * M * V, sum(t[1:]) / len(t[1:]), "bf16 read + bf16 write in place; exp + 10 ALU per element")
 
 
 if __name__ == "__main__":
