@@ -579,11 +579,11 @@ def run_b200(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         import oracle
-        n_tok = args.cpu_sample_tokens or 256
+        n_tok = args.cpu_sample_tokens or 1024
         ocfg = oracle.OracleRLConfig(**wl.rlcfg.model_dump())
-        tps, dt, threads = time_cpu_reference(wl.hidden[0][:n_tok].cpu(), wl.weight.cpu(), wl.cpu_batches[0], ocfg, n_tok, 2, 1)
+        tps, dt, threads = time_cpu_reference(wl.hidden[0][:n_tok].cpu(), wl.weight.cpu(), wl.cpu_batches[0], ocfg, n_tok, 3, 1)
         cpu = {"value": tps, "unit": "tokens/s", "cores": threads, "kind": "port",
-               "sample": f"first {n_tok} tokens of the same packed row, 1 warm-up + 2 timed fwd+bwd calls ({dt:.2f} s each), fp32 torch math on the bf16 values"}
+               "sample": f"first {n_tok} tokens of the same packed row, 1 warm-up + 3 timed fwd+bwd calls ({dt:.2f} s each), fp32 torch math on the bf16 values"}
 
     if rank == 0:
         line = {

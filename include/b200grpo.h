@@ -330,6 +330,32 @@ int b200grpo_metrics_accumulate(const double* metrics, const int* slots, const i
                                 double kl_coef, double entropy_coef, double input_size,
                                 double n_samples, int record, double* acc, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Final RMSNorm + value head in one sweep.  Replaces, inside `model(**model_inputs)`
+ * of finetune/rl/__init__.py:183-195, the trunk's last op -- the final RMSNorm of the HF model
+ * (third-party transformers Qwen2RMSNorm / LlamaRMSNorm: ~7 elementwise launches over [T, H]) --
+ * and the value head `Linear(H, 1)` of finetune/value_model.py:40-52,100-106 that reads the same
+ * normalised tensor.  Numerics of the transformers module on bf16: f32 variance and scale, the
+ * normalised value rounded to bf16, then a bf16 multiply by gamma.
+ *
+ *   x bf16 [T,H] (ldx)  pre-norm hidden state        gamma bf16 [H]
+ *   value_w bf16 [H], value_b bf16 [1]  nullable: no value head (value / dvalue* unused)
+ *   y bf16 [T,H] (ldy)  out: gamma * norm(x) -- operand A of b200grpo_lmhead_fwd
+ *   rstd f32 [T]        out: rsqrt(mean(x^2) + eps), consumed by the backward
+ *   value f32 [T]       out: y . value_w + value_b
+ * Backward: dy bf16 [T,H] (gradient of y from K2's dH), dvalue f32 [T] (K3's coef_value), ->
+ *   dx bf16 [T,H], dgamma f32 [H], dvalue_w f32 [H], dvalue_b f32 [1]; the column sums are
+ *   reduced in fixed order (deterministic).  H % 8 == 0, H <= 8192, 16-byte aligned rows.
+ * ------------------------------------------------------------------------------------- */
+size_t b200grpo_final_norm_bwd_workspace(int T, int H);
+int b200grpo_final_norm_fwd(const void* x, int64_t ldx, const void* gamma, float eps,
+                            const void* value_w, const void* value_b, int T, int H, void* y,
+                            int64_t ldy, float* rstd, float* value, void* stream);
+int b200grpo_final_norm_bwd(const void* x, int64_t ldx, const void* gamma, const float* rstd,
+                            const void* dy, int64_t lddy, const float* dvalue, const void* value_w,
+                            int T, int H, void* dx, int64_t lddx, float* dgamma, float* dvalue_w,
+                            float* dvalue_b, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Tunables (for experiments from the test/bench harness; defaults are the shipped ones).
  * name in {"two_cta", "dh_ksplit", "dw_ksplit", "tail_split", "fwd_group_m", "dh_group_m", "dw_group_m", "dw_group_n",
  * "save_logits", "hint_resident", "hint_stream", "dh_big_m", "dw_big_m", "gemm_big_m"} (meanings: csrc/abi.cu);
@@ -345,7 +371,8 @@ uint64_t b200grpo_launch_count(void);
  * events, writes up to `capacity` (tag, milliseconds) pairs in launch order, clears the ring and
  * returns the count.  Tags: 1 fwd GEMM+stats, 2 split merge, 3 finalize, 4 token loss,
  * 5 bwd recompute->dlogits GEMM, 6 dH GEMM, 7 dW GEMM, 8 plain GEMM, 9 advantages, 10 bucket,
- * 11 segments, 12 fused logits GEMM, 13 logits->dlogits pass, 14 split-K reduce.
+ * 11 segments, 12 fused logits GEMM, 13 logits->dlogits pass, 14 split-K reduce, 15 ingest expand,
+ * 16 final norm (+ value head).
  * enable(0) switches it off. */
 int b200grpo_profile_enable(int capacity);
 int b200grpo_profile_read(int32_t* tags_host, float* ms_host, int capacity);

@@ -18,6 +18,7 @@ from .grpo_oracle import (  # noqa: F401
     oracle_aggregate_rl_stats,
     oracle_collate_packed,
     oracle_filter_zero_advantage_groups,
+    oracle_final_norm_value,
     oracle_linear_decay_coef,
     oracle_logprobs_entropy,
     oracle_merge_stats,

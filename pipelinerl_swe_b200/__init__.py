@@ -12,6 +12,7 @@ from .stats import aggregate_rl_stats  # noqa: F401
 from .data import collate_packed, create_sentinel_batch, create_sentinel_example  # noqa: F401
 from .advantage import filter_zero_advantage_groups, populate_rl_data, prepare_rl_fields  # noqa: F401
 from .lm_head import FusedLMHead, install_fused_lm_head, lmhead_logprobs, set_skip_masked_tokens  # noqa: F401
+from .final_norm import install_fused_final_norm  # noqa: F401
 from .rl import rl_step, rl_step_async  # noqa: F401
 from .metrics import StepMetrics  # noqa: F401
 from .ingest import PackedWire, ingest_packed, pack_rollouts  # noqa: F401
@@ -22,6 +23,6 @@ from . import host_step  # noqa: F401
 __all__ = [
     "RLConfig", "RL_DATA_COLUMNS", "linear_decay_coef", "PipelineBatchEncoding", "aggregate_rl_stats", "collate_packed",
     "create_sentinel_batch", "create_sentinel_example", "populate_rl_data", "prepare_rl_fields",
-    "filter_zero_advantage_groups", "FusedLMHead", "install_fused_lm_head", "lmhead_logprobs", "set_skip_masked_tokens", "rl_step", "rl_step_async", "StepMetrics", "PackedWire", "ingest_packed", "pack_rollouts",
+    "filter_zero_advantage_groups", "FusedLMHead", "install_fused_lm_head", "install_fused_final_norm", "lmhead_logprobs", "set_skip_masked_tokens", "rl_step", "rl_step_async", "StepMetrics", "PackedWire", "ingest_packed", "pack_rollouts",
     "annotate_traces_with_ref_logprobs", "weight_update", "host_step",
 ]

@@ -91,6 +91,9 @@ SIGNATURES = {
     "b200grpo_expand_packed": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, C.POINTER(PackedOut), _p]),
     "b200grpo_metrics_reset": (_i, [_p, _i, _p, _p]),
     "b200grpo_metrics_accumulate": (_i, [_p, _p, _p, _i, _d, _d, _d, _d, _i, _p, _p]),
+    "b200grpo_final_norm_bwd_workspace": (_sz, [_i, _i]),
+    "b200grpo_final_norm_fwd": (_i, [_p, _i64, _p, _f, _p, _p, _i, _i, _p, _i64, _p, _p, _p]),
+    "b200grpo_final_norm_bwd": (_i, [_p, _i64, _p, _p, _p, _i64, _p, _p, _i, _i, _p, _i64, _p, _p, _p, _p, _sz, _p]),
     "b200grpo_profile_enable": (_i, [_i]),
     "b200grpo_profile_read": (_i, [_p, _p, _i]),
     "b200grpo_gemm_bf16": (_i, [_p, _i64, _i, _p, _i64, _i, _p, _i64, _i, _i, _i, _i, _i, _i, _i, _p, _sz, _p]),
@@ -127,7 +130,7 @@ def check(code: int) -> None:
 
 PROF_TAGS = {1: "fwd_gemm_stats", 2: "fwd_merge", 3: "finalize", 4: "token_loss", 5: "bwd_recompute_dlogits", 6: "bwd_dH_gemm",
              7: "bwd_dW_gemm", 8: "gemm", 9: "group_advantage", 10: "bucket", 11: "segments", 12: "fused_logits_gemm",
-             13: "dlogits_pass", 14: "splitk_reduce", 15: "ingest_expand"}
+             13: "dlogits_pass", 14: "splitk_reduce", 15: "ingest_expand", 16: "final_norm"}
 
 
 def profile_enable(capacity: int) -> None:

@@ -244,3 +244,43 @@ def bucket_unpack(bucket: torch.Tensor, tensors: Sequence[torch.Tensor]) -> None
     n = len(tensors)
     ws = _workspace(bucket.device, lib().b200grpo_bucket_workspace(n), "bucket")
     check(lib().b200grpo_bucket_unpack(bucket.data_ptr(), ptrs, numel, is_f32, n, ws.data_ptr(), ws.numel(), _stream()))
+
+
+def final_norm_fwd(x: torch.Tensor, gamma: torch.Tensor, eps: float, value_w: torch.Tensor | None = None,
+                   value_b: torch.Tensor | None = None) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor | None]:
+    """Final RMSNorm (+ value head) in one sweep: x bf16 [T,H] -> (y bf16 [T,H], rstd f32 [T], value f32 [T] | None)."""
+    _req(x, torch.bfloat16, "x"); _req(gamma, torch.bfloat16, "gamma")
+    T, H = x.shape
+    assert gamma.numel() == H
+    if value_w is not None:
+        _req(value_w, torch.bfloat16, "value_w")
+        assert value_w.numel() == H
+        if value_b is not None:
+            _req(value_b, torch.bfloat16, "value_b")
+    y = torch.empty_like(x)
+    rstd = torch.empty(T, dtype=torch.float32, device=x.device)
+    value = torch.empty(T, dtype=torch.float32, device=x.device) if value_w is not None else None
+    check(lib().b200grpo_final_norm_fwd(x.data_ptr(), H, gamma.data_ptr(), float(eps), _ptr(value_w), _ptr(value_b), T, H,
+                                        y.data_ptr(), H, rstd.data_ptr(), _ptr(value), _stream()))
+    return y, rstd, value
+
+
+def final_norm_bwd(x: torch.Tensor, gamma: torch.Tensor, rstd: torch.Tensor, dy: torch.Tensor,
+                   dvalue: torch.Tensor | None = None, value_w: torch.Tensor | None = None):
+    """-> (dx bf16 [T,H], dgamma f32 [H], dvalue_w f32 [H] | None, dvalue_b f32 [1] | None)."""
+    _req(x, torch.bfloat16, "x"); _req(gamma, torch.bfloat16, "gamma"); _req(rstd, torch.float32, "rstd"); _req(dy, torch.bfloat16, "dy")
+    T, H = x.shape
+    assert dy.shape == x.shape and rstd.numel() == T
+    dx = torch.empty_like(x)
+    dgamma = torch.empty(H, dtype=torch.float32, device=x.device)
+    dvw = dvb = None
+    if dvalue is not None:
+        _req(dvalue, torch.float32, "dvalue"); _req(value_w, torch.bfloat16, "value_w")
+        dvw = torch.empty(H, dtype=torch.float32, device=x.device)
+        dvb = torch.empty(1, dtype=torch.float32, device=x.device)
+    n = lib().b200grpo_final_norm_bwd_workspace(T, H)
+    ws = _workspace(x.device, n, "final_norm")
+    check(lib().b200grpo_final_norm_bwd(x.data_ptr(), H, gamma.data_ptr(), rstd.data_ptr(), dy.data_ptr(), H, _ptr(dvalue),
+                                        _ptr(value_w), T, H, dx.data_ptr(), H, dgamma.data_ptr(), _ptr(dvw), _ptr(dvb),
+                                        ws.data_ptr(), ws.numel(), _stream()))
+    return dx, dgamma, dvw, dvb

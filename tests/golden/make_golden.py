@@ -219,9 +219,43 @@ def gen_aggregate(rlu):
         json.dump(dict(input=stats, num_samples=5, output=res), f, indent=1)
 
 
+def gen_final_norm():
+    """Final RMSNorm (transformers Qwen2RMSNorm, unmodified) + the reference's ValueHead (value_model.py:40-52), bf16, with
+    autograd gradients for an upstream (dy, dvalue)."""
+    from transformers.models.qwen2.modeling_qwen2 import Qwen2RMSNorm
+    from pipelinerl.finetune import value_model as vm  # the reference's module, after import_reference()'s stubs
+    out = {}
+    for name, (T, H) in {"a": (37, 64), "b": (5, 264)}.items():
+        g = torch.Generator().manual_seed(100 + T)
+        norm = Qwen2RMSNorm(H, eps=1e-6)
+        with torch.no_grad():
+            norm.weight.copy_(1.0 + 0.2 * torch.randn(H, generator=g))
+        head = vm.ValueHead(H)
+        with torch.no_grad():
+            head.output.weight.copy_(0.05 * torch.randn(1, H, generator=g))
+            head.output.bias.fill_(0.125)
+        norm, head = norm.to(torch.bfloat16), head.to(torch.bfloat16)
+        x = (torch.randn(T, H, generator=g) * 3.0).to(torch.bfloat16).requires_grad_(True)
+        y = norm(x)
+        value = head(y)
+        dy = (torch.randn(T, H, generator=g) * 0.1).to(torch.bfloat16)
+        dv = (torch.randn(T, generator=g) * 0.1).to(torch.bfloat16)
+        torch.autograd.backward([y, value], [dy, dv])
+        f = lambda t: t.detach().float().numpy()  # noqa: E731  (bf16 values are exact in f32)
+        out.update({f"{name}_x": f(x), f"{name}_gamma": f(norm.weight), f"{name}_vw": f(head.output.weight), f"{name}_vb": f(head.output.bias),
+                    f"{name}_y": f(y), f"{name}_value": f(value), f"{name}_dy": f(dy), f"{name}_dv": f(dv), f"{name}_dx": f(x.grad),
+                    f"{name}_dgamma": f(norm.weight.grad), f"{name}_dvw": f(head.output.weight.grad), f"{name}_dvb": f(head.output.bias.grad)})
+    np.savez_compressed(os.path.join(HERE, "final_norm.npz"), **out)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(1)  # deterministic reduction order
+    if sys.argv[1:] == ["final_norm"]:  # only the final-norm fixture (leaves the other files untouched)
+        import_reference()
+        gen_final_norm()
+        sys.exit(0)
     rl, rlu, PBE, data, futils = import_reference()
+    gen_final_norm()
     gen_rl_step(rl, PBE)
     gen_sentinel(rl, PBE, futils)
     gen_advantages(rl, data)

@@ -350,3 +350,82 @@ def test_skip_masked_tokens_gives_the_same_step(n_prompt):
     assert float((gh0 - gh1).abs().max()) <= 2e-2 * float(gh0.abs().max())
     labelled_next = (batch["labels"][0, 1:] != -100)
     assert float(gh1[0, :-1][~labelled_next].abs().max()) == 0.0                  # skipped rows get exactly zero gradient
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Final RMSNorm + value head in one sweep
+# ---------------------------------------------------------------------------------------------------------------
+def _final_norm_ref(x, gamma, eps, vw, vb, dy, dv):
+    """The oracle on the GPU tensors' CPU copies, with autograd gradients (bf16 semantics of the transformers module)."""
+    import oracle
+    xc, gc = x.cpu().requires_grad_(True), gamma.cpu().requires_grad_(True)
+    vwc = vw.cpu().requires_grad_(True) if vw is not None else None
+    vbc = vb.cpu().requires_grad_(True) if vb is not None else None
+    y, value = oracle.oracle_final_norm_value(xc, gc, eps, vwc, vbc)
+    outs, grads = [y], [dy.cpu()]
+    if value is not None:
+        outs.append(value); grads.append(dv.cpu().to(value.dtype))
+    torch.autograd.backward(outs, grads)
+    return y.detach(), (value.detach() if value is not None else None), xc.grad, gc.grad, (vwc.grad if vwc is not None else None), \
+        (vbc.grad if vbc is not None else None)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["a", "b"])
+def test_final_norm_value_golden(case):
+    """CUDA kernel vs outputs of transformers' Qwen2RMSNorm + the reference's ValueHead themselves (tests/golden/final_norm.npz)."""
+    import numpy as np
+    from helpers import GOLDEN
+    from pipelinerl_swe_b200 import ops
+    d = torch.device("cuda:0")
+    z = np.load(os.path.join(GOLDEN, "final_norm.npz"))
+    t = lambda k: torch.from_numpy(z[f"{case}_{k}"]).to(torch.bfloat16).to(d)  # noqa: E731
+    x, gamma, vw, vb = t("x"), t("gamma"), t("vw").reshape(-1), t("vb")
+    y, rstd, value = ops.final_norm_fwd(x, gamma, 1e-6, vw, vb)
+    # forward: every rounding point of the transformers module is reproduced; the f32 mean may differ in the last bit, which can
+    # flip a bf16 rounding of the normalised value (1 bf16 ulp = 2^-8 relative)
+    torch.testing.assert_close(y.float(), t("y").float(), rtol=2 ** -7, atol=1e-6)
+    assert (y != t("y")).float().mean().item() < 0.01
+    torch.testing.assert_close(value, t("value").float(), rtol=1e-2, atol=2e-3)   # golden value is bf16-rounded
+    dx, dgamma, dvw, dvb = ops.final_norm_bwd(x, gamma, rstd, t("dy"), t("dv").float(), vw)
+    for got, want, name in ((dx.float(), t("dx").float(), "dx"), (dgamma, t("dgamma").float(), "dgamma"), (dvw, t("dvw").float().reshape(-1), "dvw"),
+                            (dvb, t("dvb").float(), "dvb")):
+        err = (got - want).abs().max().item() / max(want.abs().max().item(), 1e-12)
+        assert err < 2e-2, (name, err)   # gradients: 2e-2 of max (north-star tolerance; the golden side is bf16 autograd)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("T,H,with_value", [(1, 8, True), (300, 1536, True), (257, 3584, False), (64, 5120, True), (33, 8192, True),
+                                            (1000, 896, False)])
+def test_final_norm_value_vs_oracle(T, H, with_value):
+    from pipelinerl_swe_b200 import ops
+    d = torch.device("cuda:0")
+    g = torch.Generator(device=d).manual_seed(T * 7 + H)
+    x = (torch.randn(T, H, device=d, generator=g) * 2.5).bfloat16()
+    gamma = (1.0 + 0.3 * torch.randn(H, device=d, generator=g)).bfloat16()
+    vw = (0.05 * torch.randn(H, device=d, generator=g)).bfloat16() if with_value else None
+    vb = torch.full((1,), 0.25, device=d).bfloat16() if with_value else None
+    dy = (0.1 * torch.randn(T, H, device=d, generator=g)).bfloat16()
+    dv = 0.1 * torch.randn(T, device=d, generator=g) if with_value else None
+    y, rstd, value = ops.final_norm_fwd(x, gamma, 1e-6, vw, vb)
+    dx, dgamma, dvw, dvb = ops.final_norm_bwd(x, gamma, rstd, dy, dv, vw)
+    ry, rvalue, rdx, rdg, rdvw, rdvb = _final_norm_ref(x, gamma, 1e-6, vw, vb, dy, dv.bfloat16() if dv is not None else None)
+    torch.testing.assert_close(y.float().cpu(), ry.float(), rtol=2 ** -7, atol=1e-6)
+    assert (y.cpu() != ry).float().mean().item() < 0.01
+    rel = lambda a, b: (a.float().cpu() - b.float()).abs().max().item() / max(b.float().abs().max().item(), 1e-12)  # noqa: E731
+    if with_value:
+        assert rel(value, rvalue) < 1e-2
+        assert rel(dvw, rdvw.reshape(-1)) < 2e-2 and rel(dvb, rdvb) < 2e-2
+    else:
+        assert value is None and dvw is None and dvb is None
+    assert rel(dx, rdx) < 2e-2 and rel(dgamma, rdg) < 2e-2
+
+
+@pytest.mark.gpu
+def test_final_norm_rejects_bad_shapes():
+    from pipelinerl_swe_b200 import _abi, ops
+    d = torch.device("cuda:0")
+    with pytest.raises(_abi.B200GrpoError):
+        ops.final_norm_fwd(torch.zeros(4, 12, device=d).bfloat16(), torch.ones(12, device=d).bfloat16(), 1e-6)   # H % 8
+    with pytest.raises(_abi.B200GrpoError):
+        ops.final_norm_fwd(torch.zeros(4, 8200, device=d).bfloat16(), torch.ones(8200, device=d).bfloat16(), 1e-6)  # H > 8192

@@ -478,3 +478,64 @@ def test_lmhead_bwd_in_two_stages_is_bit_identical(save):
             gh, gw = ops.lmhead_bwd(*args, saved=saved)
         outs.append((gh.clone(), gw.clone()))
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("with_value_head", [False, True])
+def test_fused_final_norm_inside_an_unmodified_transformers_model(with_value_head):
+    """install_fused_final_norm on a random tiny Qwen2 (and the reference's value-head wrapper shape, value_model.py:40-116):
+    same loss / stats / gradients as the model's own RMSNorm + Linear, module identity and state dict untouched."""
+    transformers = pytest.importorskip("transformers")
+    import copy
+    import types
+    from pipelinerl_swe_b200 import RLConfig, install_fused_final_norm, rl_step
+    from pipelinerl_swe_b200.final_norm import FusedFinalNorm, FusedValueHead
+    d = _dev()
+    V, lens = 1024 + 8, [50, 33, 70]
+    cfg_m = transformers.Qwen2Config(vocab_size=V, hidden_size=64, intermediate_size=128, num_hidden_layers=1, num_attention_heads=4,
+                                     num_key_value_heads=2, max_position_embeddings=256, tie_word_embeddings=False)
+
+    class ValueHead(torch.nn.Module):          # value_model.py:40-52
+        def __init__(self, H):
+            super().__init__()
+            self.output = torch.nn.Linear(H, 1)
+
+        def forward(self, hidden_states):
+            return self.output(hidden_states).squeeze(-1)
+
+    class WithValueHead(torch.nn.Module):      # value_model.py:55-116
+        def __init__(self, lm):
+            super().__init__()
+            self.pretrained_model = lm
+            self.value_head = ValueHead(lm.config.hidden_size)
+
+        def forward(self, **kw):
+            out = self.pretrained_model(**kw, output_hidden_states=True)
+            return types.SimpleNamespace(logits=out.logits, value=self.value_head(out.hidden_states[-1]))
+
+    torch.manual_seed(4)
+    lm = transformers.Qwen2ForCausalLM(cfg_m)
+    with torch.no_grad():
+        lm.model.norm.weight.add_(0.2 * torch.randn_like(lm.model.norm.weight))
+    plain = (WithValueHead(lm) if with_value_head else lm).to(torch.bfloat16).to(d)
+    fused = copy.deepcopy(plain)
+    keys_before = list(fused.state_dict().keys())
+    norm = install_fused_final_norm(fused)
+    assert isinstance(norm, FusedFinalNorm) and install_fused_final_norm(fused) is norm        # idempotent
+    assert list(fused.state_dict().keys()) == keys_before
+    if with_value_head:
+        assert isinstance(fused.value_head, FusedValueHead)
+    batch = _to_dev(synthetic_packed_batch(lens, V, seed=6, n_prompt=5))
+    cfg = RLConfig(batch_size=3, kl_coef=0.05, final_kl_coef=0.05, value_loss_coef=0.5, clamp_log_ratio_ref_new_value=5)
+    out = []
+    for m in (plain, fused):
+        loss, stats = rl_step(m, batch, 0, 1, cfg)
+        loss.backward()
+        out.append((loss.item(), stats, {n: p.grad.float().clone() for n, p in m.named_parameters() if p.grad is not None}))
+    (l0, s0, g0), (l1, s1, g1) = out
+    assert abs(l0 - l1) <= 1e-3 * abs(l0) + 1e-5, (l0, l1)
+    assert_stats_close(s1, s0, rtol=5e-3, atol=5e-4)
+    assert set(g0) == set(g1)
+    for n in g0:
+        err = (g0[n] - g1[n]).abs().max().item() / max(g0[n].abs().max().item(), 1e-12)
+        assert err < 3e-2, (n, err)   # bf16 autograd on both sides

@@ -86,3 +86,17 @@ def test_sentinel_batch_layout():
     z = np.load(os.path.join(GOLDEN, "rl_step_sentinel.npz"))
     for k in ("input_ids", "labels", "position_ids", "group_tokens", "num_labels", "seq_boundaries"):
         assert sb[k].tolist() == z[k].tolist(), k
+
+
+@pytest.mark.parametrize("case", ["a", "b"])
+def test_final_norm_value_matches_transformers_and_reference_value_head(case):
+    """oracle_final_norm_value vs transformers' Qwen2RMSNorm + the reference's ValueHead (bf16, with autograd)."""
+    import numpy as np
+    z = np.load(os.path.join(GOLDEN, "final_norm.npz"))
+    t = lambda k: torch.from_numpy(z[f"{case}_{k}"]).to(torch.bfloat16)  # noqa: E731
+    x, gamma, vw, vb = t("x").requires_grad_(True), t("gamma").requires_grad_(True), t("vw").requires_grad_(True), t("vb").requires_grad_(True)
+    y, value = oracle.oracle_final_norm_value(x, gamma, 1e-6, vw, vb)
+    assert torch.equal(y.detach(), t("y")) and torch.equal(value.detach(), t("value"))
+    torch.autograd.backward([y, value], [t("dy"), t("dv")])
+    assert torch.equal(x.grad, t("dx")) and torch.equal(gamma.grad, t("dgamma"))
+    assert torch.equal(vw.grad, t("dvw")) and torch.equal(vb.grad, t("dvb"))

@@ -41,7 +41,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--once", action="store_true")
-    ap.add_argument("--only", default="", help="comma list of: k3,segments,k4,ingest,k6,dlogits (default: all)")
+    ap.add_argument("--only", default="", help="comma list of: k3,segments,k4,ingest,final_norm,k6,dlogits (default: all)")
     args = ap.parse_args()
     from helpers import StubTokenizer, synthetic_packed_batch, synthetic_rollout_examples
     from pipelinerl_swe_b200 import RLConfig, ops, rl
@@ -108,6 +108,20 @@ def main():
         ms = timed(lambda: wire.to_device(dev))
         emit("ingest: H2D + expand_packed", f"T={T} rollouts={n_seq}", 76 * T, ms,
              f"includes the {wire.nbytes} B pinned H2D copy and the output allocation; device traffic 16 B in + 60 B out per token")
+    # ---- final RMSNorm + value head: 4 B/element forward, 6 B/element backward -------------------
+    for T, H in ((8192, 3584), (65536, 3584), (32768, 5120)) if want("final_norm") else ():
+        x = torch.randn(T, H, device=dev, generator=g).bfloat16()
+        gamma = torch.ones(H, device=dev).bfloat16()
+        vw = (0.01 * torch.randn(H, device=dev, generator=g)).bfloat16()
+        vb = torch.zeros(1, device=dev).bfloat16()
+        dy = torch.randn(T, H, device=dev, generator=g).bfloat16()
+        dv = torch.randn(T, device=dev, generator=g)
+        y, rstd, _ = ops.final_norm_fwd(x, gamma, 1e-6, vw, vb)
+        ms = timed(lambda: ops.final_norm_fwd(x, gamma, 1e-6, vw, vb))
+        emit("final_norm_fwd (+ value head)", f"T={T} H={H}", 4 * T * H, ms, "bf16 in + bf16 out; includes the output allocation")
+        ms = timed(lambda: ops.final_norm_bwd(x, gamma, rstd, dy, dv, vw))
+        emit("final_norm_bwd (+ value head)", f"T={T} H={H}", 6 * T * H, ms, "x, dy in; dx out; column partials + reduce kernel included")
+        del x, dy, y
     # ---- K6 bucket pack / unpack: 4 B/element (bf16 in + out) --------------------------------------------------
     if want("k6"):
         shapes = [(3584, 3584), (3584,), (512, 3584), (512,), (18944, 3584), (18944, 3584), (3584, 18944), (3584,), (3584,)] * 4
