@@ -358,7 +358,7 @@ int b200grpo_final_norm_bwd(const void* x, int64_t ldx, const void* gamma, const
 
 /* Tunables (for experiments from the test/bench harness; defaults are the shipped ones).
  * name in {"two_cta", "dh_ksplit", "dw_ksplit", "tail_split", "fwd_group_m", "dh_group_m", "dw_group_m", "dw_group_n",
- * "save_logits", "hint_resident", "hint_stream", "dh_big_m", "dw_big_m", "gemm_big_m"} (meanings: csrc/abi.cu);
+ * "save_logits", "hint_resident", "hint_stream", "dh_big_m", "dw_big_m", "gemm_big_m", "fwd_big_m", "dw_zigzag"} (meanings: csrc/abi.cu);
  * returns the previous value, or a negative B200GRPO_E* code for an unknown name. */
 int b200grpo_set_tunable(const char* name, int value);
 

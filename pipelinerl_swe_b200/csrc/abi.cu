@@ -56,10 +56,13 @@ int check_device_sm100() {
 //   operands (0 normal, 1 evict-first, 2 evict-last);
 //   dh_big_m / dw_big_m / gemm_big_m / fwd_big_m: 256 rows per CTA (pair tile 512 x 256, one accumulator stage).  dH ships with it
 //   (long K loop, plain store epilogue); dW does not: its f32 accumulate epilogue must overlap the next mainloop.
+//   dw_zigzag: odd tiles of a cluster walk the token (K) axis of dW backwards, so a wave starts on the rows of `hidden`
+//   the previous wave touched last (L2 reuse instead of a DRAM re-read).  Ships on: dW DRAM reads 12.0 -> 10.4 GB, dW -1 %
+//   same-box (profiles/r01/dw_zigzag_ab.md).
 static const char* const g_tunable_names[TUNE_COUNT] = {"two_cta", "dh_ksplit", "dw_ksplit", "tail_split", "fwd_group_m", "dh_group_m",
                                                         "dw_group_m", "dw_group_n", "save_logits", "hint_resident", "hint_stream",
-                                                        "dh_big_m", "dw_big_m", "gemm_big_m", "fwd_big_m"};
-static int g_tunables[TUNE_COUNT] = {1, 0, 0, 1, 16, 4, 1, 0, 1, 0, 0, 1, 0, 0, 0};
+                                                        "dh_big_m", "dw_big_m", "gemm_big_m", "fwd_big_m", "dw_zigzag"};
+static int g_tunables[TUNE_COUNT] = {1, 0, 0, 1, 16, 4, 1, 0, 1, 0, 0, 1, 0, 0, 0, 1};
 int get_tunable(int id) { return g_tunables[id]; }
 
 // ---- profiling ring (diagnostic; single-threaded use) -------------------------------------

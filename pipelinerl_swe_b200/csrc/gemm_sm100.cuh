@@ -52,6 +52,8 @@ struct GemmParams {
   int tail_split;           //   pieces per tail tile (>= 2 when the tail split is on, else 0)
   int tile_rows;            //   rows of one tile (all CTAs of the cluster)
   unsigned long long hint_a, hint_b;   // L2 eviction policy of the A / B operand loads
+  int zigzag;               // odd tiles of a cluster walk K backwards: the operand rows touched last by one wave are the first
+                            // the next wave asks L2 for (K-long operands that do not fit L2 whole, i.e. dW)
   // EPI_STORE
   void* C;
   long long ldc;
@@ -338,12 +340,14 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
 
   if (warp == 0 && lane == 0) {
     // ===================== TMA producer =====================
-    uint32_t stage = 0, phase = 0;
-    for (int item = cluster_id; item < n_items; item += n_clusters) {
+    uint32_t stage = 0, phase = 0, tile_iter = 0;
+    for (int item = cluster_id; item < n_items; item += n_clusters, ++tile_iter) {
       const Item it = decode_item(p, item);
       const int m0 = (it.m_blk * kCtas + (int)cta_rank) * CTA_M;
       const int n0 = it.nb * BLOCK_N + (int)cta_rank * LOAD_N;
-      for (int kb = it.kb0; kb < it.kb1; ++kb) {
+      const bool rev = p.zigzag && (tile_iter & 1);
+      for (int kbi = it.kb0; kbi < it.kb1; ++kbi) {
+        const int kb = rev ? it.kb1 - 1 - (kbi - it.kb0) : kbi;
         ptx::mbar_wait(&empty_bar[stage], phase ^ 1, 1);
         uint8_t* sa = smem + stage * L::STAGE_BYTES;
         uint8_t* sb = sa + L::A_BYTES;

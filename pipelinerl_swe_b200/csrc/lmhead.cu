@@ -384,8 +384,9 @@ static size_t store_gemm_slab_bytes(int M, int N, int K, int ctas, int forced_ks
 static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* C, long long ldc,
                           int c_is_f32, int accumulate, int M, int N, int K, int ctas, int group_m, int forced_ksplit,
                           void* slab, size_t slab_bytes, cudaStream_t st, int a_panel_rows = 0, int group_n = 0,
-                          int hint_a = 0, int hint_b = 0, int mrep = 1) {
+                          int hint_a = 0, int hint_b = 0, int mrep = 1, int zigzag = 0) {
   GemmParams p = {};
+  p.zigzag = zigzag;
   if (ctas != 2) mrep = 1;   // the 256-row variant exists for CTA pairs only
   const int tiles = ceil_div(M, GEMM_BLOCK_M * mrep * ctas) * ceil_div(N, BN);
   // forced_ksplit >= 1: uniform k-splits (1 = none); <= 0: automatic = tail split of the last partial wave
@@ -569,7 +570,7 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
     ProfScope ps(PROF_BWD_DW, st);
     if (int e = run_store_gemm(dlog, 0, 1, hidden, ldh, 1, grad_weight, ldgw, grad_weight_is_f32, accumulate, Vloc, H, M,
                                ctas, get_tunable(TUNE_DW_GROUP_M), get_tunable(TUNE_DW_KSPLIT), slab, slab_bytes, st, M, get_tunable(TUNE_DW_GROUP_N),
-                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT), mrep_for(TUNE_DW_BIG_M, ctas))) return e;
+                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT), mrep_for(TUNE_DW_BIG_M, ctas), get_tunable(TUNE_DW_ZIGZAG))) return e;
   }
   return B200GRPO_OK;
 }
