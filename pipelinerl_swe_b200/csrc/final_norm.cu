@@ -21,6 +21,11 @@
 namespace b200grpo {
 
 constexpr int FN_THREADS = 256;
+constexpr int FN_DEPTH = 4;   // rows of (x, dy) in flight per block in the backward's cp.async ring
+
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
 
 __device__ __forceinline__ void unpack8(const uint4& q, float (&f)[8]) {
   const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
@@ -97,21 +102,21 @@ __global__ void __launch_bounds__(FN_THREADS) final_norm_fwd_kernel(const __nv_b
 
 // ---- backward: a block owns rows blockIdx.x, +grid, ...; thread t owns columns (k*256 + t)*8 .. +8 -----------
 // so the column sums (dgamma, dvalue_w) stay in registers across rows; the per-row projection term is one block
-// reduction per row (double-buffered: one __syncthreads per row).
-template <int NCH, bool kValue>
-__global__ void __launch_bounds__(FN_THREADS, NCH <= 2 ? 2 : 1)
+// reduction per row (double-buffered: one __syncthreads per row); rows are prefetched FN_DEPTH deep with cp.async.
+template <int NCH, int kThreads, bool kValue>
+__global__ void __launch_bounds__(kThreads, kThreads == 256 ? 2 : 1)
 final_norm_bwd_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, const __nv_bfloat16* __restrict__ gamma,
                       const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dy, long long lddy,
                       const float* __restrict__ dvalue, const __nv_bfloat16* __restrict__ vw, int T, int H,
                       __nv_bfloat16* __restrict__ dx, long long lddx, float* __restrict__ part, float* __restrict__ part_b) {
-  __shared__ float red[2][FN_THREADS / 32];
+  __shared__ float red[2][kThreads / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nvec = H >> 3;
   uint4 g_pk[NCH], w_pk[NCH];
   float dg[NCH][8], dw[NCH][8];
 #pragma unroll
   for (int k = 0; k < NCH; ++k) {
-    const int v = k * FN_THREADS + tid;
+    const int v = k * kThreads + tid;
     g_pk[k] = v < nvec ? __ldg(reinterpret_cast<const uint4*>(gamma) + v) : make_uint4(0, 0, 0, 0);
     w_pk[k] = (kValue && v < nvec) ? __ldg(reinterpret_cast<const uint4*>(vw) + v) : make_uint4(0, 0, 0, 0);
 #pragma unroll
@@ -119,23 +124,40 @@ final_norm_bwd_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, const 
   }
   float db = 0.f;
   int parity = 0;
-  // The row's operands stay PACKED (bf16) across the block reduction and the f32 terms are recomputed after it
-  // (cheap ALU) -- that leaves registers for the NEXT row's loads to be in flight during the reduction.
-  uint4 xq[NCH], dq[NCH], xn_[NCH], dn_[NCH];
-  auto load_row = [&](int row, uint4 (&xo)[NCH], uint4 (&dO)[NCH]) {
-    const uint4* xr = reinterpret_cast<const uint4*>(x + (long long)row * ldx);
-    const uint4* dr = reinterpret_cast<const uint4*>(dy + (long long)row * lddy);
+  // Rows arrive through a cp.async ring in shared memory (FN_DEPTH rows of x and dy per block): every thread copies and
+  // later reads only ITS OWN 16-byte chunks, so the ring needs no block barrier and the loads in flight cost no
+  // registers.  Operands stay packed (bf16) across the block reduction; the f32 terms are recomputed after it.
+  extern __shared__ uint4 ring[];                    // [FN_DEPTH][2][nvec]
+  uint4 xq[NCH], dq[NCH];
+  auto issue_row = [&](int row, int slot) {
+    if (row < T) {
+      const uint4* xr = reinterpret_cast<const uint4*>(x + (long long)row * ldx);
+      const uint4* dr = reinterpret_cast<const uint4*>(dy + (long long)row * lddy);
+      uint4* sx = ring + (size_t)slot * 2 * nvec;
 #pragma unroll
-    for (int k = 0; k < NCH; ++k) {
-      const int v = k * FN_THREADS + tid;
-      xo[k] = v < nvec ? __ldg(xr + v) : make_uint4(0, 0, 0, 0);
-      dO[k] = v < nvec ? __ldg(dr + v) : make_uint4(0, 0, 0, 0);
+      for (int k = 0; k < NCH; ++k) {
+        const int v = k * kThreads + tid;
+        if (v < nvec) { cp_async_16(sx + v, xr + v); cp_async_16(sx + nvec + v, dr + v); }
+      }
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  if ((int)blockIdx.x < T) load_row(blockIdx.x, xq, dq);
+#pragma unroll
+  for (int d = 0; d < FN_DEPTH; ++d) issue_row(blockIdx.x + d * gridDim.x, d);
+  int slot = 0;
   for (int row = blockIdx.x; row < T; row += gridDim.x, parity ^= 1) {
-    const int next = row + gridDim.x;
-    if (next < T) load_row(next, xn_, dn_);
+    asm volatile("cp.async.wait_group %0;" ::"n"(FN_DEPTH - 1) : "memory");
+    {
+      const uint4* sx = ring + (size_t)slot * 2 * nvec;
+#pragma unroll
+      for (int k = 0; k < NCH; ++k) {
+        const int v = k * kThreads + tid;
+        xq[k] = v < nvec ? sx[v] : make_uint4(0, 0, 0, 0);
+        dq[k] = v < nvec ? sx[nvec + v] : make_uint4(0, 0, 0, 0);
+      }
+    }
+    issue_row(row + FN_DEPTH * gridDim.x, slot);     // refill the slot just drained (own chunks only: no hazard)
+    slot = slot + 1 == FN_DEPTH ? 0 : slot + 1;
     const float r = __ldg(rstd + row);
     const float dv = kValue ? __ldg(dvalue + row) : 0.f;
     if (kValue && tid == 0) db += dv;
@@ -163,12 +185,12 @@ final_norm_bwd_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, const 
     __syncthreads();
     float tot = 0.f;
 #pragma unroll
-    for (int w = 0; w < FN_THREADS / 32; ++w) tot += red[parity][w];
+    for (int w = 0; w < kThreads / 32; ++w) tot += red[parity][w];
     const float m = tot / (float)H;
     uint4* out = reinterpret_cast<uint4*>(dx + (long long)row * lddx);
 #pragma unroll
     for (int k = 0; k < NCH; ++k) {
-      const int v = k * FN_THREADS + tid;
+      const int v = k * kThreads + tid;
       float xv[8], dyv[8], g[8], w[8], o[8];
       unpack8(xq[k], xv); unpack8(dq[k], dyv); unpack8(g_pk[k], g);
       if constexpr (kValue) unpack8(w_pk[k], w);
@@ -180,14 +202,12 @@ final_norm_bwd_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, const 
       }
       if (v < nvec) out[v] = pack8(o);
     }
-#pragma unroll
-    for (int k = 0; k < NCH; ++k) { xq[k] = xn_[k]; dq[k] = dn_[k]; }
   }
   // per-block column partials: part[blockIdx][0][H] = dgamma, [1][H] = dvalue_w
   float* pg = part + (size_t)blockIdx.x * 2 * H;
 #pragma unroll
   for (int k = 0; k < NCH; ++k) {
-    const int v = k * FN_THREADS + tid;
+    const int v = k * kThreads + tid;
     if (v < nvec) {
       float4* a = reinterpret_cast<float4*>(pg + v * 8);
       a[0] = make_float4(dg[k][0], dg[k][1], dg[k][2], dg[k][3]);
@@ -224,7 +244,7 @@ __global__ void __launch_bounds__(FN_THREADS) final_norm_reduce_kernel(const flo
 }
 
 static int fn_bwd_grid(int T, int H) {
-  const int per_sm = (H >> 3) <= 2 * FN_THREADS ? 2 : 1;
+  const int per_sm = H <= 4096 ? 2 : 1;   // 256-thread blocks up to H = 4096, one 512-thread block per SM above
   int sms = sm_count();
   if (sms <= 0) sms = 148;
   const int g = sms * per_sm;
@@ -295,17 +315,28 @@ extern "C" int b200grpo_final_norm_bwd(const void* x, int64_t ldx, const void* g
                       *wp = (const __nv_bfloat16*)value_w;
   __nv_bfloat16* op = (__nv_bfloat16*)dx;
   ProfScope ps(PROF_FINAL_NORM, st);
-#define FN_BWD(N)                                                                                                                     \
-  do {                                                                                                                                \
-    if (val) final_norm_bwd_kernel<N, true><<<grid, FN_THREADS, 0, st>>>(xp, ldx, gp, rstd, dp, lddy, dvalue, wp, T, H, op, lddx, part, part_b); \
-    else final_norm_bwd_kernel<N, false><<<grid, FN_THREADS, 0, st>>>(xp, ldx, gp, rstd, dp, lddy, dvalue, wp, T, H, op, lddx, part, part_b);    \
+  const size_t ring_bytes = (size_t)FN_DEPTH * 2 * H * sizeof(__nv_bfloat16);
+#define FN_BWD_ONE(N, TH, V)                                                                                                    \
+  do {                                                                                                                          \
+    static bool configured = false;                                                                                             \
+    if (!configured) {                                                                                                          \
+      B200_CUDA_OK(cudaFuncSetAttribute(final_norm_bwd_kernel<N, TH, V>, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
+                                        FN_DEPTH * 2 * 8 * TH * N * (int)sizeof(__nv_bfloat16)));                               \
+      configured = true;                                                                                                        \
+    }                                                                                                                           \
+    final_norm_bwd_kernel<N, TH, V><<<grid, TH, ring_bytes, st>>>(xp, ldx, gp, rstd, dp, lddy, dvalue, wp, T, H, op, lddx, part, part_b); \
   } while (0)
-  const int nch = ceil_div(H >> 3, FN_THREADS);
-  if (nch <= 1) FN_BWD(1);
-  else if (nch == 2) FN_BWD(2);
-  else if (nch == 3) FN_BWD(3);
-  else FN_BWD(4);
+#define FN_BWD(N, TH)                  \
+  do {                                 \
+    if (val) FN_BWD_ONE(N, TH, true);  \
+    else FN_BWD_ONE(N, TH, false);     \
+  } while (0)
+  // every thread owns one or two 8-column chunks: 256-thread blocks (two per SM) up to H = 4096, 512-thread blocks above
+  if (H <= 2048) FN_BWD(1, 256);
+  else if (H <= 4096) FN_BWD(2, 256);
+  else FN_BWD(2, 512);
 #undef FN_BWD
+#undef FN_BWD_ONE
   final_norm_reduce_kernel<<<ceil_div(H, FN_THREADS), FN_THREADS, 0, st>>>(part, part_b, grid, H, dgamma, val ? dvalue_w : nullptr,
                                                                            val ? dvalue_b : nullptr);
   count_launch(2);
