@@ -88,6 +88,42 @@ def test_token_loss_vs_oracle(name, packed, lens, rows):
     torch.testing.assert_close(ent_d.grad.cpu(), ent_r.grad, rtol=1e-4, atol=1e-9)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("lens,poison", [([2], False), ([1, 1, 2], False), ([3, 1, 5], True), ([64, 1, 1, 1, 30], True)])
+def test_token_loss_tiny_rows_and_masked_nonfinite(lens, poison):
+    """Shortest possible rows (one shifted position, one-token segments) and NaN / inf rewards + advantages at MASKED positions:
+    `mask_sum` multiplies by the mask and then nan_to_num's (rl/utils.py:28-30), so they must vanish from every sum while
+    `num_nans` still counts them (rl/__init__.py:345), exactly as the oracle does."""
+    from pipelinerl_swe_b200 import RLConfig
+    from pipelinerl_swe_b200 import rl as prl
+    cfgkw = dict(policy_loss="ppo", kl_coef=0.1, final_kl_coef=0.1, batch_size=4, epsilon=0.2)
+    batch = synthetic_packed_batch(lens, 1000, seed=sum(lens), n_prompt=1)
+    L = batch["labels"].shape[1]
+    g = torch.Generator().manual_seed(3)
+    lp = -(torch.rand(1, L - 1, generator=g) + 0.05)
+    ent = torch.rand(1, L - 1, generator=g)
+    m = (batch["labels"][:, 1:] != -100).float()
+    batch["old_logprobs"][:, 1:] = (lp + 0.1 * torch.randn(lp.shape, generator=g)) * m
+    batch["ref_logprobs"][:, 1:] = (lp + 0.2 * torch.randn(lp.shape, generator=g)) * m
+    if poison:
+        masked = (batch["labels"][0] == -100).nonzero().flatten().tolist()
+        assert masked
+        batch["rewards"][0, masked[0]] = float("nan")
+        batch["advantages"][0, masked[0]] = float("inf")
+        batch["advantages"][0, masked[-1]] = float("nan")
+    ocfg = oracle.OracleRLConfig(**cfgkw)
+    want_loss, want_stats = oracle.oracle_token_loss(lp.clone(), ent.clone(), batch, 0, 1, ocfg)
+    cfg = prl.make_loss_cfg(RLConfig(**cfgkw), 0, 1, True, False)
+    sink = {}
+    loss = prl.TokenLossFunction.apply(lp.to(_dev()), ent.to(_dev()), None, _to_dev(batch), cfg, sink)
+    stats = prl.stats_from_metrics(sink["metrics"].tolist(), cfg, batch["input_ids"].numel(), False, (0.1, 0.0))
+    assert set(stats) == set(want_stats)
+    if "loss" in want_stats:
+        assert abs(loss.item() - want_loss.item()) <= 1e-5 * abs(want_loss.item()) + 1e-7
+        assert_stats_close(stats, want_stats, rtol=2e-4, atol=1e-6)
+        assert stats["num_nans"] == want_stats["num_nans"] and stats["num_output_tokens_sum"] == want_stats["num_output_tokens_sum"]
+
+
 def test_token_loss_flags_nonfinite():
     from pipelinerl_swe_b200 import RLConfig
     from pipelinerl_swe_b200 import rl as prl
