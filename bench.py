@@ -55,6 +55,8 @@ def parse_args():
     ap.add_argument("--no-torch-baseline", action="store_true", help="skip the torch-eager-on-this-GPU baseline (N=1 only)")
     ap.add_argument("--cpu-sample-tokens", type=int, default=0, help="tokens per CPU-baseline call (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "symm"],
+                    help="vocab-parallel transport: NCCL, or this library's NVSwitch multicast kernels (SymmetricExchange)")
     ap.add_argument("--tunable", action="append", default=[], metavar="NAME=VALUE", help="library tunable (experiments)")
     return ap.parse_args()
 
@@ -358,6 +360,10 @@ class DeviceWorkload:
         H, V, T, attempts, kl, clamp, B, desc = CONFIGS[args.config]
         self.H, self.V, self.T, self.desc = H, V, T, desc
         self.vocab_parallel = args.parallelism == "vocab" and world > 1
+        self.exchange = None
+        if self.vocab_parallel and args.exchange == "symm":
+            from pipelinerl_swe_b200.vocab_parallel import SymmetricExchange
+            self.exchange = SymmetricExchange(None, dev, T, H)
         seed = 1236 + (0 if self.vocab_parallel else rank)
         self.rlcfg = RLConfig(policy_loss="ppo", batch_size=B, kl_coef=kl, final_kl_coef=kl, clamp_log_ratio_ref_new_value=clamp,
                               epsilon=0.2, temperature=1.0)
@@ -399,6 +405,9 @@ class DeviceWorkload:
         torch.cuda.synchronize()
 
     def fwd_stats(self, h, tgt, saved=None):
+        if self.exchange is not None:   # the merge kernel's multimem.st is the all-gather
+            return self.exchange.forward_stats(
+                lambda mc: self.ops.lmhead_fwd_stats(h, self.weight, tgt, 1.0, self.v_offset, saved, stats_mc=mc), h.shape[0])
         stats = self.ops.lmhead_fwd_stats(h, self.weight, tgt, 1.0, self.v_offset, saved)
         if self.vocab_parallel:
             from pipelinerl_swe_b200.vocab_parallel import exchange_stats
@@ -414,7 +423,15 @@ class DeviceWorkload:
         lp, ent, lse = ops.lmhead_finalize(self.fwd_stats(h, tgt, saved))
         loss, metrics, coef_lp, coef_ent, _ = ops.token_loss(lp[None], ent[None], b, self.cfg)
         args = (h, self.weight, tgt, lse, ent, coef_lp[0], coef_ent[0], 1.0, self.v_offset)
-        if self.vocab_parallel:   # as LMHeadLogprobFunction.backward: the dH all-reduce runs while dW is computed
+        if self.exchange is not None:   # dH partial into the symmetric buffer, in-switch all-reduce beside the dW GEMM
+            from pipelinerl_swe_b200 import _abi
+            x, M = self.exchange, h.shape[0]
+            ops.lmhead_bwd(*args, need_grad_weight=False, saved=saved, stages=_abi.BWD_DLOGITS | _abi.BWD_DH, grad_hidden_out=x.dh_view(M))
+            done = x.allreduce_dh_async(M)
+            ops.lmhead_bwd(*args, need_grad_hidden=False, grad_weight_out=self.grad_weight, accumulate=True, saved=saved,
+                           stages=_abi.BWD_DW)
+            torch.cuda.current_stream().wait_event(done)
+        elif self.vocab_parallel:   # as LMHeadLogprobFunction.backward: the dH all-reduce runs while dW is computed
             from pipelinerl_swe_b200 import _abi
             from pipelinerl_swe_b200.vocab_parallel import reduce_grad_hidden_async
             gh, _ = ops.lmhead_bwd(*args, need_grad_weight=False, saved=saved, stages=_abi.BWD_DLOGITS | _abi.BWD_DH)
@@ -591,6 +608,7 @@ def run_b200(args):
             "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if wl.vocab_parallel else "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": wl.desc, "H": H, "V": V, "T": T, "parallelism": ("vocab" if wl.vocab_parallel else "dp") + str(world),
+                       **({"exchange": "nvswitch multicast kernels (SymmetricExchange)" if wl.exchange is not None else "nccl"} if wl.vocab_parallel else {}),
                        "grad_weight": "f32 accumulated across steps", "l2": "inputs exceed L2 (lm_head weight %.2f GB)" % (wl.weight.numel() * 2 / 1e9),
                        "bwd_mode": args.mode, "tunables": args.tunable, "tokens_per_gpu_per_sec": value / world if not wl.vocab_parallel else value},
             "roofline": roofline, "cpu_baseline": cpu, "torch_gpu_baseline": torch_gpu, "rl_step_api": api, "e2e": e2e, "gpu_launches": int(round(launches_per_step * K)),

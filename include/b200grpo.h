@@ -356,6 +356,29 @@ int b200grpo_final_norm_bwd(const void* x, int64_t ldx, const void* gamma, const
                             int T, int H, void* dx, int64_t lddx, float* dgamma, float* dvalue_w,
                             float* dvalue_b, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * K5  vocab-parallel exchange over NVSwitch multicast (a new capability -- the reference
+ * always holds the whole lm_head, finetune/rl/__init__.py:197).  Both calls take addresses of a
+ * SYMMETRIC buffer mapped through a multicast address (the caller allocates / rendezvous-es it,
+ * e.g. torch symmetric memory) and leave cross-rank ordering to the caller's barrier on `stream`.
+ *
+ * b200grpo_lmhead_fwd_multicast: b200grpo_lmhead_fwd whose merge kernel stores the per-token
+ *   partials with multimem.st to stats_mc = multicast address of THIS rank's [M,4] slot of a
+ *   symmetric [R][M][4] f32 buffer: the all-gather of the forward exchange is the kernel's own
+ *   store (16 B/token/rank through the switch).  After a barrier every rank finalizes its local
+ *   copy with b200grpo_lmhead_finalize(R, M).
+ * b200grpo_mc_allreduce_bf16: in place sum over ranks of a symmetric bf16 tensor (dH = sum over
+ *   vocab shards; the dH GEMM writes its partial straight into the local copy).  Two-shot: rank r
+ *   owns 1/R of the 16-byte vectors, multimem.ld_reduce (f32 accumulate in the switch) then
+ *   multimem.st to every copy.  `ctas` (<= 0: 16) blocks of 512 threads, no shared memory: they
+ *   co-reside with the dW GEMM instead of taking SMs from it.  Barrier before and after.
+ * ------------------------------------------------------------------------------------- */
+int b200grpo_lmhead_fwd_multicast(const void* hidden, int64_t ldh, const void* weight, int64_t ldw,
+                                  const int64_t* targets, int M, int H, int Vloc, int64_t v_offset,
+                                  float inv_temperature, void* stats_mc, void* saved, void* workspace,
+                                  size_t workspace_bytes, void* stream);
+int b200grpo_mc_allreduce_bf16(void* mc_ptr, int64_t numel, int rank, int world, int ctas, void* stream);
+
 /* Tunables (for experiments from the test/bench harness; defaults are the shipped ones).
  * name in {"two_cta", "dh_ksplit", "dw_ksplit", "tail_split", "fwd_group_m", "dh_group_m", "dw_group_m", "dw_group_n",
  * "save_logits", "hint_resident", "hint_stream", "dh_big_m", "dw_big_m", "gemm_big_m", "fwd_big_m", "dw_zigzag"} (meanings: csrc/abi.cu);
@@ -372,7 +395,7 @@ uint64_t b200grpo_launch_count(void);
  * returns the count.  Tags: 1 fwd GEMM+stats, 2 split merge, 3 finalize, 4 token loss,
  * 5 bwd recompute->dlogits GEMM, 6 dH GEMM, 7 dW GEMM, 8 plain GEMM, 9 advantages, 10 bucket,
  * 11 segments, 12 fused logits GEMM, 13 logits->dlogits pass, 14 split-K reduce, 15 ingest expand,
- * 16 final norm (+ value head).
+ * 16 final norm (+ value head), 17 multicast all-reduce.
  * enable(0) switches it off. */
 int b200grpo_profile_enable(int capacity);
 int b200grpo_profile_read(int32_t* tags_host, float* ms_host, int capacity);

@@ -67,6 +67,8 @@ SIGNATURES = {
     "b200grpo_lmhead_fwd_workspace": (_sz, [_i, _i, _i]),
     "b200grpo_lmhead_saved_bytes": (_sz, [_i, _i, _i]),
     "b200grpo_lmhead_fwd": (_i, [_p, _i64, _p, _i64, _p, _i, _i, _i, _i64, _f, _p, _p, _p, _sz, _p]),
+    "b200grpo_lmhead_fwd_multicast": (_i, [_p, _i64, _p, _i64, _p, _i, _i, _i, _i64, _f, _p, _p, _p, _sz, _p]),
+    "b200grpo_mc_allreduce_bf16": (_i, [_p, _i64, _i, _i, _i, _p]),
     "b200grpo_lmhead_finalize": (_i, [_p, _i, _i, _p, _p, _p, _p]),
     "b200grpo_token_loss_workspace": (_sz, [_i, _i]),
     "b200grpo_token_loss": (_i, [_p] * 12 + [_i, _i, C.POINTER(LossCfg)] + [_p] * 6 + [_sz, _p]),
@@ -130,7 +132,7 @@ def check(code: int) -> None:
 
 PROF_TAGS = {1: "fwd_gemm_stats", 2: "fwd_merge", 3: "finalize", 4: "token_loss", 5: "bwd_recompute_dlogits", 6: "bwd_dH_gemm",
              7: "bwd_dW_gemm", 8: "gemm", 9: "group_advantage", 10: "bucket", 11: "segments", 12: "fused_logits_gemm",
-             13: "dlogits_pass", 14: "splitk_reduce", 15: "ingest_expand", 16: "final_norm"}
+             13: "dlogits_pass", 14: "splitk_reduce", 15: "ingest_expand", 16: "final_norm", 17: "mc_allreduce"}
 
 
 def profile_enable(capacity: int) -> None:

@@ -45,7 +45,7 @@ void count_launch(int n = 1);  // kernel launches issued by this library (b200gr
 // ---- optional per-launch timing (b200grpo_profile_*): CUDA events on the launching stream ----
 enum { PROF_FWD_GEMM = 1, PROF_FWD_MERGE = 2, PROF_FINALIZE = 3, PROF_TOKEN_LOSS = 4, PROF_BWD_DLOGITS = 5,
        PROF_BWD_DH = 6, PROF_BWD_DW = 7, PROF_GEMM = 8, PROF_ADVANTAGE = 9, PROF_BUCKET = 10, PROF_SEGMENTS = 11,
-       PROF_FUSED_CHUNK = 12, PROF_DLOGITS_EW = 13, PROF_REDUCE = 14, PROF_INGEST = 15, PROF_FINAL_NORM = 16 };
+       PROF_FUSED_CHUNK = 12, PROF_DLOGITS_EW = 13, PROF_REDUCE = 14, PROF_INGEST = 15, PROF_FINAL_NORM = 16, PROF_MC_ALLREDUCE = 17 };
 struct ProfScope {  // records start/end events around the launches issued while it is alive (no-op when disabled)
   ProfScope(int tag, cudaStream_t st);
   ~ProfScope();

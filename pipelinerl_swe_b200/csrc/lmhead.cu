@@ -203,6 +203,10 @@ __device__ __forceinline__ void merge_one(float& m, float& sum, float& dot, floa
   const float w = __expf(q.x - m);
   sum = fmaf(q.y, w, sum); dot = fmaf(q.z, w, dot); tgt += q.w;
 }
+// kMulticast: `stats` is an NVSwitch multicast address (this rank's slot of a symmetric [R][M][4] buffer): the merged row is
+// stored with multimem.st, so the merge IS the all-gather of the vocab-parallel exchange -- every rank's copy of the slot is
+// written by the switch, no collective kernel follows (the caller only synchronises).
+template <bool kMulticast>
 __global__ void __launch_bounds__(32 * MG_SLICES) fwd_merge_kernel(const float4* __restrict__ part, int S, int M, float4* __restrict__ stats) {
   const int rx = threadIdx.x & 31, sy = threadIdx.x >> 5;
   const int row = blockIdx.x * 32 + rx;
@@ -229,7 +233,11 @@ __global__ void __launch_bounds__(32 * MG_SLICES) fwd_merge_kernel(const float4*
       if (q.x == -INFINITY) continue;  // slice saw no tile
       merge_one(M2, S2, D2, T2, q);
     }
-    stats[row] = make_float4(M2, S2, D2, T2);
+    if constexpr (kMulticast) {
+      asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(stats + row), "f"(M2), "f"(S2), "f"(D2), "f"(T2) : "memory");
+    } else {
+      stats[row] = make_float4(M2, S2, D2, T2);
+    }
   }
 }
 
@@ -459,9 +467,9 @@ extern "C" size_t b200grpo_lmhead_saved_bytes(int M, int H, int Vloc) {
   return part_bytes(M, Vloc) + panel_bytes(M, Vloc);
 }
 
-extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
-                                   int M, int H, int Vloc, int64_t v_offset, float inv_temperature, float* stats, void* saved,
-                                   void* workspace, size_t workspace_bytes, void* stream) {
+static int lmhead_fwd_impl(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
+                           int M, int H, int Vloc, int64_t v_offset, float inv_temperature, float* stats, bool stats_multicast,
+                           void* saved, void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_device_sm100()) return e;
   B200_REQUIRE(hidden && weight && targets && stats && (workspace || saved), "lmhead_fwd: null pointer");
   B200_REQUIRE(M >= 1 && H >= 8 && Vloc >= 1 && H % 8 == 0, "lmhead_fwd: M=%d H=%d Vloc=%d (H must be a multiple of 8)", M, H, Vloc);
@@ -490,9 +498,26 @@ extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* 
     if (e) return e;
   }
   ProfScope ps(PROF_FWD_MERGE, st);
-  fwd_merge_kernel<<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, p.n_blocks, M, (float4*)stats); count_launch();
+  if (stats_multicast) fwd_merge_kernel<true><<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, p.n_blocks, M, (float4*)stats);
+  else fwd_merge_kernel<false><<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, p.n_blocks, M, (float4*)stats);
+  count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
+}
+
+extern "C" int b200grpo_lmhead_fwd(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
+                                   int M, int H, int Vloc, int64_t v_offset, float inv_temperature, float* stats, void* saved,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
+  return lmhead_fwd_impl(hidden, ldh, weight, ldw, targets, M, H, Vloc, v_offset, inv_temperature, stats, false, saved, workspace,
+                         workspace_bytes, stream);
+}
+
+extern "C" int b200grpo_lmhead_fwd_multicast(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
+                                             int M, int H, int Vloc, int64_t v_offset, float inv_temperature, void* stats_mc, void* saved,
+                                             void* workspace, size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(((uintptr_t)stats_mc & 15) == 0, "lmhead_fwd_multicast: the multicast slot must be 16-byte aligned");
+  return lmhead_fwd_impl(hidden, ldh, weight, ldw, targets, M, H, Vloc, v_offset, inv_temperature, (float*)stats_mc, true, saved,
+                         workspace, workspace_bytes, stream);
 }
 
 extern "C" int b200grpo_lmhead_finalize(const float* stats, int R, int M, float* logprob, float* entropy, float* lse, void* stream) {

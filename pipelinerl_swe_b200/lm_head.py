@@ -15,7 +15,7 @@ import torch
 from torch import nn
 
 from . import _abi, ops
-from .vocab_parallel import exchange_stats, reduce_grad_hidden, reduce_grad_hidden_async
+from .vocab_parallel import SymmetricExchange, exchange_stats, reduce_grad_hidden, reduce_grad_hidden_async
 
 
 _SAVE_LOGITS = True
@@ -66,9 +66,13 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         need_bwd = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
         saved = ops.lmhead_saved_buffer(hidden.shape[0], hidden.shape[1], weight.shape[0], hidden.device) \
             if (need_bwd and save_logits_enabled()) else None
-        stats = ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset, saved)
-        if group is not None:
-            stats = exchange_stats(stats, group)  # [R,M,4], 16 B/token/rank over NCCL
+        if isinstance(group, SymmetricExchange):  # the merge kernel's multimem.st IS the all-gather (NVSwitch multicast)
+            stats = group.forward_stats(lambda mc: ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset, saved, stats_mc=mc),
+                                        hidden.shape[0])
+        else:
+            stats = ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset, saved)
+            if group is not None:
+                stats = exchange_stats(stats, group)  # [R,M,4], 16 B/token/rank over NCCL
         logprob, entropy, lse = ops.lmhead_finalize(stats)
         ctx.save_for_backward(hidden, weight, targets, lse, entropy)
         ctx.inv_temperature, ctx.group, ctx.v_offset = inv_temperature, group, v_offset
@@ -83,6 +87,14 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         need_h, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         saved, ctx.saved = ctx.saved, None  # consumed in place by the backward; a second backward recomputes
         args = (hidden, weight, targets, lse, entropy, coef_lp, coef_ent, ctx.inv_temperature, ctx.v_offset)
+        if isinstance(ctx.group, SymmetricExchange) and need_h:
+            # dH partial straight into the symmetric buffer; in-switch all-reduce on a side stream WHILE this rank's dW GEMM runs
+            x, M = ctx.group, hidden.shape[0]
+            ops.lmhead_bwd(*args, need_grad_weight=False, saved=saved, stages=_abi.BWD_DLOGITS | _abi.BWD_DH, grad_hidden_out=x.dh_view(M))
+            done = x.allreduce_dh_async(M)
+            gw = ops.lmhead_bwd(*args, need_grad_hidden=False, saved=saved, stages=_abi.BWD_DW)[1] if need_w else None
+            torch.cuda.current_stream().wait_event(done)
+            return x.dh_view(M).clone(), gw, None, None, None, None   # the symmetric buffer is reused by the next micro-batch
         if ctx.group is not None and need_h and need_w:
             # vocab-parallel: dH = sum over shards is all-reduced on NCCL's stream WHILE this rank's dW GEMM runs
             gh, _ = ops.lmhead_bwd(*args, need_grad_weight=False, saved=saved, stages=_abi.BWD_DLOGITS | _abi.BWD_DH)

@@ -52,15 +52,23 @@ def lmhead_saved_buffer(M: int, H: int, V: int, device) -> torch.Tensor:
 
 
 def lmhead_fwd_stats(hidden: torch.Tensor, weight: torch.Tensor, targets: torch.Tensor, inv_temperature: float,
-                     v_offset: int = 0, saved: torch.Tensor | None = None) -> torch.Tensor:
-    """K1: per-row (max, sumexp, sum e*z, z_target) over this rank's vocab rows -> f32 [M,4]."""
+                     v_offset: int = 0, saved: torch.Tensor | None = None, stats_mc: int | None = None) -> torch.Tensor | None:
+    """K1: per-row (max, sumexp, sum e*z, z_target) over this rank's vocab rows -> f32 [M,4].
+
+    ``stats_mc``: NVSwitch multicast address of this rank's [M,4] slot in a symmetric buffer -- the merge kernel stores
+    there with multimem.st (the vocab-parallel all-gather is the kernel's own store); nothing is returned."""
     _req(hidden, torch.bfloat16, "hidden"); _req(weight, torch.bfloat16, "weight"); _req(targets, torch.int64, "targets")
     M, H = hidden.shape
     V = weight.shape[0]
     assert weight.shape[1] == H and targets.numel() == M
-    stats = torch.empty(M, 4, dtype=torch.float32, device=hidden.device)
     n = lib().b200grpo_lmhead_fwd_workspace(M, H, V)
     ws = _workspace(hidden.device, n)
+    if stats_mc is not None:
+        check(lib().b200grpo_lmhead_fwd_multicast(hidden.data_ptr(), H, weight.data_ptr(), H, targets.data_ptr(), M, H, V, v_offset,
+                                                  float(inv_temperature), C.c_void_p(stats_mc), _ptr(saved), ws.data_ptr(), ws.numel(),
+                                                  _stream()))
+        return None
+    stats = torch.empty(M, 4, dtype=torch.float32, device=hidden.device)
     check(lib().b200grpo_lmhead_fwd(hidden.data_ptr(), H, weight.data_ptr(), H, targets.data_ptr(), M, H, V, v_offset,
                                     float(inv_temperature), stats.data_ptr(), _ptr(saved), ws.data_ptr(), ws.numel(), _stream()))
     return stats
@@ -284,3 +292,8 @@ def final_norm_bwd(x: torch.Tensor, gamma: torch.Tensor, rstd: torch.Tensor, dy:
                                         _ptr(value_w), T, H, dx.data_ptr(), H, dgamma.data_ptr(), _ptr(dvw), _ptr(dvb),
                                         ws.data_ptr(), ws.numel(), _stream()))
     return dx, dgamma, dvw, dvb
+
+
+def mc_allreduce_bf16(mc_ptr: int, numel: int, rank: int, world: int, ctas: int = 16) -> None:
+    """In place sum over ranks of a symmetric bf16 tensor through its NVSwitch multicast address (two-shot, in-switch reduce)."""
+    check(lib().b200grpo_mc_allreduce_bf16(C.c_void_p(mc_ptr), int(numel), int(rank), int(world), int(ctas), _stream()))

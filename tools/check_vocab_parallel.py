@@ -2,7 +2,7 @@
 """Vocab-parallel logprob/loss over NCCL == unsharded, on real GPUs (run under torchrun, N = 2/4/8).
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
-        tools/check_vocab_parallel.py
+        tools/check_vocab_parallel.py [--exchange=symm]
 
 Every rank holds the same hidden/targets and its contiguous shard of lm_head rows; forward exchanges the
 16 B/token partials with one all-gather, backward all-reduces dH.  Compared on every rank against the
@@ -25,7 +25,8 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     from pipelinerl_swe_b200.lm_head import LMHeadLogprobFunction
-    from pipelinerl_swe_b200.vocab_parallel import shard_weight
+    from pipelinerl_swe_b200.vocab_parallel import SymmetricExchange, shard_weight
+    symmetric = "--exchange=symm" in sys.argv or os.environ.get("B200GRPO_EXCHANGE") == "symm"
 
     M, H, V, temp = 1000, 512, 152064, 0.9
     g = torch.Generator(device=dev).manual_seed(7)  # same seed on every rank -> same tensors
@@ -40,9 +41,17 @@ def main():
 
     w_shard, v_off = shard_weight(weight, world, rank)
     h1, w1 = hidden.clone().requires_grad_(True), w_shard.clone().requires_grad_(True)
-    out1 = LMHeadLogprobFunction.apply(h1, w1, targets, 1.0 / temp, dist.group.WORLD, v_off)
+    # transport: NCCL (the process group) or NVSwitch multicast kernels of this library (SymmetricExchange)
+    transport = SymmetricExchange(dist.group.WORLD, dev, M, H) if symmetric else dist.group.WORLD
+    out1 = LMHeadLogprobFunction.apply(h1, w1, targets, 1.0 / temp, transport, v_off)
     (out1 * c).sum().backward()
     torch.cuda.synchronize()
+    if symmetric:   # a second micro-batch through the same buffers (other stats slot, reused dH buffer) must give the same result
+        h2, w2 = hidden.clone().requires_grad_(True), w_shard.clone().requires_grad_(True)
+        out2 = LMHeadLogprobFunction.apply(h2, w2, targets, 1.0 / temp, transport, v_off)
+        (out2 * c).sum().backward()
+        torch.cuda.synchronize()
+        assert torch.equal(out2, out1) and torch.equal(h2.grad, h1.grad) and torch.equal(w2.grad, w1.grad), "second pass differs"
 
     def rel(a, b):
         return float((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-20))
@@ -57,7 +66,7 @@ def main():
     t = torch.tensor([int(ok)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print(f"VOCAB_PARALLEL world={world} {'OK' if t.item() else 'FAIL'} identical_across_ranks={identical} "
+        print(f"VOCAB_PARALLEL transport={'nvswitch-multicast' if symmetric else 'nccl'} world={world} {'OK' if t.item() else 'FAIL'} identical_across_ranks={identical} "
               f"max|d(logprob,entropy)|={e_out:.2e} rel dW={e_dw:.2e} rel dH={e_dh:.2e}", flush=True)
     dist.destroy_process_group()
     sys.exit(0 if t.item() else 1)
