@@ -55,8 +55,9 @@ def parse_args():
     ap.add_argument("--no-torch-baseline", action="store_true", help="skip the torch-eager-on-this-GPU baseline (N=1 only)")
     ap.add_argument("--cpu-sample-tokens", type=int, default=0, help="tokens per CPU-baseline call (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--exchange", default="nccl", choices=["nccl", "symm"],
+    ap.add_argument("--exchange", default="symm", choices=["nccl", "symm"],
                     help="vocab-parallel transport: NCCL, or this library's NVSwitch multicast kernels (SymmetricExchange)")
+    ap.add_argument("--exchange-ctas", type=int, default=16, help="CTAs of the multicast dH all-reduce kernel (--exchange symm)")
     ap.add_argument("--tunable", action="append", default=[], metavar="NAME=VALUE", help="library tunable (experiments)")
     return ap.parse_args()
 
@@ -363,7 +364,10 @@ class DeviceWorkload:
         self.exchange = None
         if self.vocab_parallel and args.exchange == "symm":
             from pipelinerl_swe_b200.vocab_parallel import SymmetricExchange
-            self.exchange = SymmetricExchange(None, dev, T, H)
+            try:
+                self.exchange = SymmetricExchange(None, dev, T, H, allreduce_ctas=args.exchange_ctas)
+            except RuntimeError as e:   # no NVSwitch multicast mapping on this box: NCCL transport, reported in `config.exchange`
+                print(f"bench.py: {e}", file=sys.stderr)
         seed = 1236 + (0 if self.vocab_parallel else rank)
         self.rlcfg = RLConfig(policy_loss="ppo", batch_size=B, kl_coef=kl, final_kl_coef=kl, clamp_log_ratio_ref_new_value=clamp,
                               epsilon=0.2, temperature=1.0)
