@@ -1,6 +1,7 @@
 """The rows of the hot path chained the way the reference chains them (preprocess.py:133-170 -> finetune_loop.py:661-670,767):
 traces -> reference log-probs -> prepare_rl_fields -> populate_rl_data -> packed batch -> rl_step -> step metrics."""
 import copy
+import os
 
 import pytest
 import torch
@@ -71,3 +72,21 @@ def test_traces_to_step_metrics_end_to_end():
         assert abs(got[k] - w) <= 1e-5 * max(1.0, abs(w)), (k, got[k], w)
     # the KL to the frozen copy of an unchanged policy is ~0 (ref log-probs came from the same weights)
     assert abs(got["rl/kl"]) < 1e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("transport", ["nccl", "symm"])
+def test_vocab_parallel_two_gpus_equals_unsharded(transport):
+    """tools/check_vocab_parallel.py under torchrun on 2 GPUs of this box (skipped on a 1-GPU box): NCCL transport and this
+    library's NVSwitch multicast kernels (SymmetricExchange) both reproduce the unsharded log-probs / gradients."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29541" if transport == "nccl" else "29542", os.path.join(root, "tools", "check_vocab_parallel.py")]
+    if transport == "symm":
+        cmd.append("--exchange=symm")
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "VOCAB_PARALLEL" in out.stdout and " OK " in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]

@@ -233,3 +233,64 @@ def test_install_fused_lm_head_keeps_module_identity_and_hooks():
         install_fused_lm_head(torch.nn.ModuleDict({"lm_head": torch.nn.Linear(4, 4, bias=True)}))
     standalone = FusedLMHead(torch.nn.Linear(16, 40, bias=False))
     assert standalone(x).shape == (2, 3, 40)
+
+
+def test_install_fused_final_norm_is_an_in_place_reclass():
+    """Same module objects and state dict; CPU tensors keep the module's own forward (the kernel has no CPU path); the
+    value head falls back to its own Linear when it is not handed the fused norm's output; unsuitable norms are refused."""
+    from pipelinerl_swe_b200 import install_fused_final_norm
+    from pipelinerl_swe_b200.final_norm import FusedFinalNorm, FusedValueHead
+
+    class RMSNorm(torch.nn.Module):            # the transformers Qwen2RMSNorm / LlamaRMSNorm shape
+        def __init__(self, H, eps=1e-6):
+            super().__init__()
+            self.weight = torch.nn.Parameter(torch.ones(H))
+            self.variance_epsilon = eps
+
+        def forward(self, x):
+            h = x.float()
+            h = h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + self.variance_epsilon)
+            return self.weight * h.to(x.dtype)
+
+    class Decoder(torch.nn.Module):
+        def __init__(self, H):
+            super().__init__()
+            self.layers = torch.nn.ModuleList([torch.nn.Linear(H, H)])
+            self.norm = RMSNorm(H)
+
+    class LM(torch.nn.Module):
+        def __init__(self, H):
+            super().__init__()
+            self.model = Decoder(H)
+            self.lm_head = torch.nn.Linear(H, 32, bias=False)
+
+    class ValueHead(torch.nn.Module):          # pipelinerl/finetune/value_model.py:40-52
+        def __init__(self, H):
+            super().__init__()
+            self.output = torch.nn.Linear(H, 1)
+
+        def forward(self, hidden_states):
+            return self.output(hidden_states).squeeze(-1)
+
+    class WithValueHead(torch.nn.Module):      # value_model.py:55-66
+        def __init__(self, lm, H):
+            super().__init__()
+            self.pretrained_model = lm
+            self.value_head = ValueHead(H)
+
+    m = WithValueHead(LM(16), 16)
+    norm, head = m.pretrained_model.model.norm, m.value_head
+    keys = list(m.state_dict().keys())
+    got = install_fused_final_norm(m)
+    assert got is norm and isinstance(norm, FusedFinalNorm) and isinstance(norm, RMSNorm) and isinstance(head, FusedValueHead)
+    assert install_fused_final_norm(m) is norm and type(norm).__mro__.count(FusedFinalNorm) == 1
+    assert list(m.state_dict().keys()) == keys and "_b200_value_linear" not in dict(norm.named_modules())
+    x = torch.randn(3, 5, 16)
+    assert torch.equal(norm(x), RMSNorm.forward(norm, x))                 # CPU tensors: the module's own forward
+    assert torch.equal(head(x), head.output(x).squeeze(-1))              # not the fused norm's output: own Linear
+    bad = LM(16)
+    del bad.model.norm.variance_epsilon
+    with pytest.raises(ValueError):
+        install_fused_final_norm(bad)
+    with pytest.raises(AttributeError):
+        install_fused_final_norm(torch.nn.Linear(4, 4))
