@@ -77,8 +77,11 @@ class FusedFinalNorm(nn.Module):
     """Mixin given to the model's final RMSNorm by ``install_fused_final_norm``."""
 
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
-        if not hidden_states.is_cuda:
-            return super().forward(hidden_states)  # CPU tensors (e.g. a meta / init-time call): the module's own forward
+        if not hidden_states.is_cuda or hidden_states.dtype != torch.bfloat16 or self.weight.dtype != torch.bfloat16:
+            # CPU tensors (a meta / init-time call) and non-bf16 models keep the module's own forward: the kernel computes
+            # what the transformers module computes on bf16 and would round an fp32 model's hidden state
+            _tls.last = None
+            return super().forward(hidden_states)
         linear = self.__dict__.get("_b200_value_linear")
         y, value = final_norm_value(hidden_states, self.weight, self.variance_epsilon, linear)
         _tls.last = (y, value) if value is not None else None
