@@ -11,7 +11,8 @@ from .types import PipelineBatchEncoding  # noqa: F401
 from .stats import aggregate_rl_stats  # noqa: F401
 from .data import collate_packed, create_sentinel_batch, create_sentinel_example  # noqa: F401
 from .advantage import filter_zero_advantage_groups, populate_rl_data, prepare_rl_fields  # noqa: F401
-from .lm_head import FusedLMHead, install_fused_lm_head, lmhead_logprobs, set_skip_masked_tokens  # noqa: F401
+from .lm_head import (FusedLMHead, fold_main_grad, install_fused_lm_head, lmhead_logprobs, set_fused_grad_accumulation,  # noqa: F401
+                      set_save_logits, set_saved_logits_budget, set_skip_masked_tokens)
 from .final_norm import install_fused_final_norm  # noqa: F401
 from .rl import rl_step, rl_step_async  # noqa: F401
 from .metrics import StepMetrics  # noqa: F401
@@ -23,6 +24,7 @@ from . import host_step  # noqa: F401
 __all__ = [
     "RLConfig", "RL_DATA_COLUMNS", "linear_decay_coef", "PipelineBatchEncoding", "aggregate_rl_stats", "collate_packed",
     "create_sentinel_batch", "create_sentinel_example", "populate_rl_data", "prepare_rl_fields",
-    "filter_zero_advantage_groups", "FusedLMHead", "install_fused_lm_head", "install_fused_final_norm", "lmhead_logprobs", "set_skip_masked_tokens", "rl_step", "rl_step_async", "StepMetrics", "PackedWire", "ingest_packed", "pack_rollouts",
+    "filter_zero_advantage_groups", "FusedLMHead", "install_fused_lm_head", "install_fused_final_norm", "lmhead_logprobs", "set_skip_masked_tokens",
+    "set_save_logits", "set_saved_logits_budget", "set_fused_grad_accumulation", "fold_main_grad", "rl_step", "rl_step_async", "StepMetrics", "PackedWire", "ingest_packed", "pack_rollouts",
     "annotate_traces_with_ref_logprobs", "weight_update", "host_step",
 ]

@@ -1,8 +1,13 @@
 """lm_head projection fused with log-softmax / entropy / gather (K1) and its backward (K2).
 
 Replaces ``model(**inputs).logits`` -> ``/temperature`` -> ``log_softmax`` -> ``softmax`` ->
-entropy -> ``gather`` of pipelinerl/finetune/rl/__init__.py:197-208: the [tokens x vocab]
-logits never exist in HBM.  ``FusedLMHead`` is a drop-in for ``model.lm_head``: it owns the
+entropy -> ``gather`` of pipelinerl/finetune/rl/__init__.py:197-208.  No fp32 logits / log-probs / probs tensor is
+ever formed.  What IS kept between forward and backward depends on the mode: by default (``set_save_logits(True)``) the
+forward stores bf16 logits relative to their tile maximum -- 2 B x tokens x vocab, 2.49 GB at T=8192, capped by
+``set_saved_logits_budget`` -- so that the backward needs no third GEMM; with ``set_save_logits(False)`` nothing of
+size tokens x vocab survives the forward and the backward recomputes the logits tile by tile (the north-star design,
+~20 % slower).  Either way the backward's bf16 dlogits scratch is bounded by the same budget (row chunks).
+``FusedLMHead`` is a drop-in for ``model.lm_head``: it owns the
 same ``weight`` Parameter, so ZeRO-3 / FSDP gather hooks and tied embeddings keep working,
 and only switches to the fused op while ``rl_step`` has an active ``LogprobRequest``.
 """
@@ -19,6 +24,8 @@ from .vocab_parallel import SymmetricExchange, exchange_stats, reduce_grad_hidde
 
 
 _SAVE_LOGITS = True
+_SAVED_BUDGET = 4 << 30
+_FUSED_GRAD_ACC = False
 
 
 def save_logits_enabled() -> bool:
@@ -26,10 +33,55 @@ def save_logits_enabled() -> bool:
 
 
 def set_save_logits(flag: bool) -> None:
-    """True (default): forward keeps bf16 logits (2 B x tokens x vocab until backward), backward skips the
-    recompute GEMM.  False: nothing of size tokens x vocab is kept; backward recomputes the logits."""
+    """True (default): forward keeps bf16 logits (2 B x tokens x vocab until backward, capped by
+    ``set_saved_logits_budget``), backward skips the recompute GEMM.  False: nothing of size tokens x vocab is kept
+    between forward and backward; backward recomputes the logits tile by tile."""
     global _SAVE_LOGITS
     _SAVE_LOGITS = bool(flag)
+
+
+def saved_logits_budget() -> int:
+    return _SAVED_BUDGET
+
+
+def set_saved_logits_budget(nbytes: int) -> None:
+    """Upper bound (bytes, default 4 GiB) on every [rows x vocab]-sized bf16 buffer of the lm_head path: the logits the
+    forward keeps AND the dlogits scratch of the backward.  A micro-batch whose rows x vocab x 2 B exceeds it is cut into
+    row chunks that fit (whole multiples of 512 rows, at least 4096 so the dW accumulate stays amortised): the first chunk
+    keeps its logits, the others are recomputed in the backward, one chunk at a time through the same scratch.  A 50 000
+    token row (the reference's SWE recipe, launch_train.sh:3) then needs 4 GiB instead of 15.2 GB, at recompute speed for
+    the rows beyond the first chunk."""
+    global _SAVED_BUDGET
+    _SAVED_BUDGET = int(nbytes)
+
+
+def fused_grad_accumulation_enabled() -> bool:
+    return _FUSED_GRAD_ACC
+
+
+def set_fused_grad_accumulation(flag: bool) -> None:
+    """Opt-in (Megatron ``main_grad`` convention).  Off: backward returns a fresh bf16 [V,H] dW and autograd adds it to
+    ``lm_head.weight.grad`` in bf16, as for any module.  On: the dW GEMM's epilogue adds straight into the f32 buffer
+    ``lm_head.weight.main_grad`` (``red.global.add.v4.f32``; allocated zeroed on first use) and autograd sees no gradient
+    for the weight -- no 2 B x V x H temporary per micro-batch, f32 accumulation across the micro-batches of an optimizer
+    step.  The optimizer side reads ``weight.main_grad`` or calls ``fold_main_grad(model)`` before its step."""
+    global _FUSED_GRAD_ACC
+    _FUSED_GRAD_ACC = bool(flag)
+
+
+def fold_main_grad(model: nn.Module, zero: bool = True) -> None:
+    """Add every ``main_grad`` written by the fused accumulate into the parameter's ``.grad`` (created if absent) in the
+    parameter's dtype, and zero the f32 buffer: what an unmodified optimizer / grad-clipping loop expects to find."""
+    for p in model.parameters():
+        mg = getattr(p, "main_grad", None)
+        if mg is None:
+            continue
+        if p.grad is None:
+            p.grad = mg.to(p.dtype)
+        else:
+            p.grad.add_(mg.to(p.dtype))
+        if zero:
+            mg.zero_()
 
 
 _SKIP_MASKED = False
@@ -52,6 +104,26 @@ def set_skip_masked_tokens(flag: bool) -> None:
     _SKIP_MASKED = bool(flag)
 
 
+def row_chunks(M: int, Vloc: int, budget: int | None = None) -> list[tuple[int, int]]:
+    """Row ranges of one micro-batch such that rows x ceil(Vloc/256)*256 x 2 B <= budget per chunk (see
+    ``set_saved_logits_budget``).  One chunk when everything fits."""
+    budget = saved_logits_budget() if budget is None else budget
+    per_row = -(-Vloc // 256) * 256 * 2
+    fit = max(4096, budget // per_row // 512 * 512)
+    if M <= fit:
+        return [(0, M)]
+    n = -(-M // fit)
+    size = min(fit, -(-(-(-M // n)) // 512) * 512)     # balanced: no sliver of a last chunk
+    return [(r, min(M, r + size)) for r in range(0, M, size)]
+
+
+class _GradSink:
+    """Carries the weight Parameter into the autograd Function without making it a differentiable input twice."""
+
+    def __init__(self, param):
+        self.param = param
+
+
 class LMHeadLogprobFunction(torch.autograd.Function):
     """(hidden [M,H] bf16, weight [Vloc,H] bf16, targets [M] i64) -> out f32 [M,2] = (logprob, entropy).
 
@@ -61,22 +133,39 @@ class LMHeadLogprobFunction(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, hidden, weight, targets, inv_temperature: float, group=None, v_offset: int = 0):
-        # keep bf16 logits for a recompute-free backward when a backward will follow
+    def forward(ctx, hidden, weight, targets, inv_temperature: float, group=None, v_offset: int = 0, sink: _GradSink | None = None):
+        M, H = hidden.shape
+        Vloc = weight.shape[0]
         need_bwd = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
-        saved = ops.lmhead_saved_buffer(hidden.shape[0], hidden.shape[1], weight.shape[0], hidden.device) \
-            if (need_bwd and save_logits_enabled()) else None
+        chunks = row_chunks(M, Vloc)
+        # keep bf16 logits for a recompute-free backward when a backward will follow: the whole micro-batch when it fits
+        # the budget, else its first row chunk (the other chunks are recomputed in the backward)
+        saved = None
+        if need_bwd and save_logits_enabled():
+            r0, r1 = chunks[0]
+            saved = ops.lmhead_saved_buffer(r1 - r0, H, Vloc, hidden.device)
+
+        def k1(stats_mc=None):
+            """K1 over all rows -> [M,4] partials (or stored through the multicast address)."""
+            if len(chunks) == 1:
+                return ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset, saved, stats_mc=stats_mc)
+            parts = []
+            for ci, (r0, r1) in enumerate(chunks):
+                mc = None if stats_mc is None else stats_mc + 16 * r0
+                parts.append(ops.lmhead_fwd_stats(hidden[r0:r1], weight, targets[r0:r1], inv_temperature, v_offset,
+                                                  saved if ci == 0 else None, stats_mc=mc))
+            return None if stats_mc is not None else torch.cat(parts)
+
         if isinstance(group, SymmetricExchange):  # the merge kernel's multimem.st IS the all-gather (NVSwitch multicast)
-            stats = group.forward_stats(lambda mc: ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset, saved, stats_mc=mc),
-                                        hidden.shape[0])
+            stats = group.forward_stats(k1, M)
         else:
-            stats = ops.lmhead_fwd_stats(hidden, weight, targets, inv_temperature, v_offset, saved)
+            stats = k1()
             if group is not None:
                 stats = exchange_stats(stats, group)  # [R,M,4], 16 B/token/rank over NCCL
         logprob, entropy, lse = ops.lmhead_finalize(stats)
         ctx.save_for_backward(hidden, weight, targets, lse, entropy)
         ctx.inv_temperature, ctx.group, ctx.v_offset = inv_temperature, group, v_offset
-        ctx.saved = saved
+        ctx.saved, ctx.chunks, ctx.sink = saved, chunks, sink
         return torch.stack((logprob, entropy), dim=1)
 
     @staticmethod
@@ -86,27 +175,58 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         coef_lp, coef_ent = g[:, 0].contiguous(), g[:, 1].contiguous()
         need_h, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         saved, ctx.saved = ctx.saved, None  # consumed in place by the backward; a second backward recomputes
-        args = (hidden, weight, targets, lse, entropy, coef_lp, coef_ent, ctx.inv_temperature, ctx.v_offset)
-        if isinstance(ctx.group, SymmetricExchange) and need_h:
-            # dH partial straight into the symmetric buffer; in-switch all-reduce on a side stream WHILE this rank's dW GEMM runs
-            x, M = ctx.group, hidden.shape[0]
-            ops.lmhead_bwd(*args, need_grad_weight=False, saved=saved, stages=_abi.BWD_DLOGITS | _abi.BWD_DH, grad_hidden_out=x.dh_view(M))
-            done = x.allreduce_dh_async(M)
-            gw = ops.lmhead_bwd(*args, need_grad_hidden=False, saved=saved, stages=_abi.BWD_DW)[1] if need_w else None
+        chunks, group = ctx.chunks, ctx.group
+        M, H = hidden.shape
+        symmetric = isinstance(group, SymmetricExchange)
+        # ---- where the gradients go
+        gh = None
+        if need_h:   # vocab-parallel over multicast: the dH partial is written straight into the symmetric buffer
+            gh = group.dh_view(M) if symmetric else torch.empty(M, H, dtype=torch.bfloat16, device=hidden.device)
+        gw, gw_ret, acc_first = None, None, False
+        if need_w:
+            sink = ctx.sink
+            if sink is not None and fused_grad_accumulation_enabled():
+                p = sink.param
+                if getattr(p, "main_grad", None) is None:
+                    p.main_grad = torch.zeros(weight.shape, dtype=torch.float32, device=weight.device)
+                gw, acc_first = p.main_grad, True           # f32 accumulate in the GEMM epilogue; autograd gets no dW
+            elif len(chunks) > 1:
+                gw = torch.empty(weight.shape, dtype=torch.float32, device=weight.device)   # chunks accumulate in f32
+            else:
+                gw = torch.empty(weight.shape, dtype=torch.bfloat16, device=weight.device)
+        # ---- row chunks (one unless the micro-batch exceeds the [rows x vocab] budget); the collective on dH is started
+        #      after the LAST chunk's dH so that it runs beside that chunk's dW GEMM
+        overlap = group is not None and need_h and need_w
+        pending = done = None
+        for ci, (r0, r1) in enumerate(chunks):
+            a = (hidden[r0:r1], weight, targets[r0:r1], lse[r0:r1], entropy[r0:r1], coef_lp[r0:r1], coef_ent[r0:r1],
+                 ctx.inv_temperature, ctx.v_offset)
+            kw = dict(saved=saved if ci == 0 else None, grad_hidden_out=gh[r0:r1] if need_h else None, grad_weight_out=gw)
+            acc = need_w and (acc_first or ci > 0)
+            if overlap and ci == len(chunks) - 1:
+                ops.lmhead_bwd(*a, need_grad_weight=False, stages=_abi.BWD_DLOGITS | _abi.BWD_DH, **kw)
+                if symmetric:   # in-switch all-reduce on a side stream WHILE this rank's dW GEMM runs
+                    done = group.allreduce_dh_async(M)
+                else:           # dH = sum over shards on NCCL's stream WHILE this rank's dW GEMM runs
+                    pending = reduce_grad_hidden_async(gh, group)
+                ops.lmhead_bwd(*a, need_grad_hidden=False, stages=_abi.BWD_DW, accumulate=acc, **kw)
+            else:
+                ops.lmhead_bwd(*a, need_grad_hidden=need_h, need_grad_weight=need_w, accumulate=acc, **kw)
+            saved = kw = None   # the first chunk's logits are consumed: their memory serves the next chunk's dlogits scratch
+        if done is not None:
             torch.cuda.current_stream().wait_event(done)
-            return x.dh_view(M).clone(), gw, None, None, None, None   # the symmetric buffer is reused by the next micro-batch
-        if ctx.group is not None and need_h and need_w:
-            # vocab-parallel: dH = sum over shards is all-reduced on NCCL's stream WHILE this rank's dW GEMM runs
-            gh, _ = ops.lmhead_bwd(*args, need_grad_weight=False, saved=saved, stages=_abi.BWD_DLOGITS | _abi.BWD_DH)
-            pending = reduce_grad_hidden_async(gh, ctx.group)
-            _, gw = ops.lmhead_bwd(*args, need_grad_hidden=False, saved=saved, stages=_abi.BWD_DW)
-            if pending is not None:
-                pending.wait()
-            return gh, gw, None, None, None, None
-        gh, gw = ops.lmhead_bwd(*args, need_grad_hidden=need_h, need_grad_weight=need_w, saved=saved)
-        if gh is not None and ctx.group is not None:
-            reduce_grad_hidden(gh, ctx.group)  # dH = sum over vocab shards
-        return gh, gw, None, None, None, None
+        elif pending is not None:
+            pending.wait()
+        elif group is not None and need_h:
+            if symmetric:
+                torch.cuda.current_stream().wait_event(group.allreduce_dh_async(M))
+            else:
+                reduce_grad_hidden(gh, group)  # dH = sum over vocab shards
+        if symmetric and need_h:
+            gh = gh.clone()   # the symmetric buffer is reused by the next micro-batch
+        if need_w and not acc_first:
+            gw_ret = gw if gw.dtype == torch.bfloat16 else gw.to(torch.bfloat16)
+        return gh, gw_ret, None, None, None, None, None
 
 
 def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch.Tensor, temperature: float, group=None,
@@ -124,6 +244,7 @@ def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch
         h2 = h2.to(torch.bfloat16)
     w = weight if weight.dtype == torch.bfloat16 else weight.to(torch.bfloat16)
     inv_t = 1.0 / float(temperature)
+    sink = _GradSink(weight) if (isinstance(weight, nn.Parameter) and w is weight) else None   # fused f32 accumulate target
     if labels is not None and skip_masked_tokens_enabled():
         keep = torch.roll(labels, shifts=-1, dims=1) != -100
         keep[:, -1] = False                                  # no next token
@@ -131,10 +252,10 @@ def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch
         out = torch.zeros(B * L, 2, dtype=torch.float32, device=hidden.device)
         if idx.numel() > 0:
             part = LMHeadLogprobFunction.apply(h2.index_select(0, idx), w.contiguous(), targets.index_select(0, idx), inv_t, group,
-                                               v_offset)
+                                               v_offset, sink)
             out = out.index_copy(0, idx, part)               # autograd scatters the gradient rows back (zeros elsewhere)
         return out.reshape(B, L, 2)
-    out = LMHeadLogprobFunction.apply(h2.contiguous(), w.contiguous(), targets, inv_t, group, v_offset)
+    out = LMHeadLogprobFunction.apply(h2.contiguous(), w.contiguous(), targets, inv_t, group, v_offset, sink)
     return out.reshape(B, L, 2)
 
 
@@ -191,7 +312,10 @@ class FusedLMHead(nn.Module):
             if type(self) is FusedLMHead:
                 return nn.functional.linear(hidden, self.weight)
             return super().forward(hidden)  # the original class's own forward (plain Linear, LoRA-wrapped, ...)
-        return lmhead_logprobs(hidden, self.weight, req.input_ids, req.temperature, req.group, req.v_offset, req.labels)
+        group, v_offset = req.group, req.v_offset
+        if group is None and getattr(self, "vocab_group", None) is not None:   # sharded head declared at install time
+            group, v_offset = self.vocab_group, self.v_offset
+        return lmhead_logprobs(hidden, self.weight, req.input_ids, req.temperature, group, v_offset, req.labels)
 
 
 def _check_fusable(linear: nn.Module) -> None:
@@ -201,10 +325,15 @@ def _check_fusable(linear: nn.Module) -> None:
         raise ValueError("lm_head must own a 2-D `weight`")
 
 
-def install_fused_lm_head(model: nn.Module) -> FusedLMHead:
+def install_fused_lm_head(model: nn.Module, vocab_group=None, v_offset: int | None = None) -> FusedLMHead:
     """Idempotently give ``model.lm_head`` the fused forward, looking through the usual wrappers: DeepSpeed / DDP
     ``.module``, the reference's value-head wrapper ``.pretrained_model`` (finetune/value_model.py:60-66), PEFT
-    ``.base_model`` / ``.model``."""
+    ``.base_model`` / ``.model``.
+
+    ``vocab_group`` (a process group, or a ``SymmetricExchange`` for the NVSwitch-multicast transport) declares that
+    ``lm_head.weight`` holds only this rank's contiguous shard of the vocabulary rows (BASELINE config 4): every
+    ``rl_step`` on this model then runs vocab-parallel.  ``v_offset`` = first vocab row of the shard; by default the summed
+    shard sizes of the lower ranks (one all-gather at install time)."""
     owner = model
     for _ in range(6):
         if hasattr(owner, "lm_head"):
@@ -225,4 +354,8 @@ def install_fused_lm_head(model: nn.Module) -> FusedLMHead:
         _check_fusable(head)
         base = type(head)
         head.__class__ = type("Fused" + base.__name__, (FusedLMHead, base), {"__module__": __name__})
+    if vocab_group is not None and (getattr(head, "vocab_group", None) is not vocab_group or v_offset is not None):
+        from .vocab_parallel import shard_offset
+        head.vocab_group = vocab_group
+        head.v_offset = int(v_offset) if v_offset is not None else shard_offset(head.weight.shape[0], vocab_group)
     return head

@@ -3,8 +3,8 @@
 Same signature and returns: ``rl_step(model, batch, current_step, max_step, config) ->
 (loss, stats)`` with a 0-dim autograd-connected ``loss`` and the reference's 34 (39 with a
 value head) float stats, or ``{"input_size": ...}`` when the batch holds no labels.
-What differs is only how it is computed: K1 inside the swapped ``lm_head`` (no logits in
-HBM), one K3 launch for every per-token term / reduction / metric, ONE host sync (the
+What differs is only how it is computed: K1 inside the swapped ``lm_head`` (no fp32
+logits / log-probs / probs tensors; see lm_head.py for what the two backward modes keep), one K3 launch for every per-token term / reduction / metric, ONE host sync (the
 metrics vector) instead of ~40, and K2 in backward.
 """
 from __future__ import annotations
@@ -115,14 +115,14 @@ def grpo_loss_from_logprobs(lp_ent: torch.Tensor, b: dict, cfg: LossCfg, values:
     return loss, sink["metrics"]
 
 
-def _forward_loss(model, batch, current_step: int, max_step: int, config):
+def _forward_loss(model, batch, current_step: int, max_step: int, config, vocab_group=None, v_offset=None):
     """Shared by rl_step / rl_step_async: model forward through the fused lm_head + K3.  No host sync."""
     b = _batch_dict(batch)
     has_value_head = hasattr(model, "value_head")
     cfg = make_loss_cfg(config, current_step, max_step, b["is_packed"], has_value_head)
     if not b["input_ids"].is_cuda:
         raise _abi.B200GrpoError("rl_step: batch must be on a CUDA device (no CPU path); call batch.to_device(...) first")
-    install_fused_lm_head(model)
+    head = install_fused_lm_head(model, vocab_group, v_offset)
     model_inputs = {"input_ids": b["input_ids"], "attention_mask": b["attention_mask"]}  # labels dropped: no HF CE pass
     if b["is_packed"]:
         model_inputs["position_ids"] = b["position_ids"]
@@ -130,7 +130,9 @@ def _forward_loss(model, batch, current_step: int, max_step: int, config):
         model_inputs["pixel_values"] = b["pixel_values"]
     if b["image_grid_thw"] is not None:
         model_inputs["image_grid_thw"] = b["image_grid_thw"]
-    with logprob_request(LogprobRequest(b["input_ids"], float(config.temperature), labels=b["labels"])):
+    req = LogprobRequest(b["input_ids"], float(config.temperature), labels=b["labels"],
+                         group=getattr(head, "vocab_group", None), v_offset=getattr(head, "v_offset", 0))
+    with logprob_request(req):
         outputs = model(**model_inputs)
     lp_ent = outputs.logits
     if lp_ent.shape[-1] != 2:
@@ -143,9 +145,17 @@ def _forward_loss(model, batch, current_step: int, max_step: int, config):
     return loss, metrics, cfg, coefs, b["input_ids"].numel(), has_value_head
 
 
-def rl_step(model, batch, current_step: int, max_step: int, config) -> tuple[torch.Tensor, dict[str, float]]:
-    """Perform a single RL step; see module docstring.  Handles packed and unpacked batches."""
-    loss, metrics, cfg, coefs, input_size, has_value_head = _forward_loss(model, batch, current_step, max_step, config)
+def rl_step(model, batch, current_step: int, max_step: int, config, *, vocab_group=None,
+            v_offset: int | None = None) -> tuple[torch.Tensor, dict[str, float]]:
+    """Perform a single RL step; see module docstring.  Handles packed and unpacked batches.
+
+    The five positional arguments are the reference's.  ``vocab_group`` (keyword-only, beyond the reference: BASELINE
+    config 4) says ``model.lm_head.weight`` is this rank's contiguous shard of the vocabulary rows and names the ranks
+    that hold the others -- a process group (NCCL exchange) or a ``SymmetricExchange`` (NVSwitch multicast kernels).
+    Every rank must pass the same batch; each gets bit-identical log-probs, loss and stats.  Equivalent to calling
+    ``install_fused_lm_head(model, vocab_group=...)`` once."""
+    loss, metrics, cfg, coefs, input_size, has_value_head = _forward_loss(model, batch, current_step, max_step, config,
+                                                                          vocab_group, v_offset)
     m = metrics.tolist()  # the one host sync of the step
     stats = stats_from_metrics(m, cfg, input_size, has_value_head, coefs)
     return loss, stats
@@ -159,13 +169,14 @@ def batch_sequence_count(batch) -> int:
     return int(get("input_ids").shape[0])
 
 
-def rl_step_async(model, batch, current_step: int, max_step: int, config, step_metrics, record: bool = True) -> torch.Tensor:
+def rl_step_async(model, batch, current_step: int, max_step: int, config, step_metrics, record: bool = True, *,
+                  vocab_group=None, v_offset: int | None = None) -> torch.Tensor:
     """``rl_step`` without its host sync: the stats go into ``step_metrics`` (metrics.StepMetrics) on the device.
 
     Replaces ``loss, m = rl_step(...); for k, v in m.items(): rl_metrics[k].append(v)`` of
     finetune_loop.py:661-670; ``record=False`` is the sentinel-batch branch (:664-666) -- the caller still
     multiplies the loss by 0.  The reference's asserts fire at ``step_metrics.reduce``.
     """
-    loss, metrics, cfg, coefs, input_size, _ = _forward_loss(model, batch, current_step, max_step, config)
+    loss, metrics, cfg, coefs, input_size, _ = _forward_loss(model, batch, current_step, max_step, config, vocab_group, v_offset)
     step_metrics.add(metrics, coefs[0], coefs[1], input_size, batch_sequence_count(batch), record)
     return loss

@@ -52,6 +52,17 @@ def reduce_grad_hidden_async(grad_hidden: torch.Tensor, group=None):
     return None
 
 
+def shard_offset(n_local_rows: int, group=None) -> int:
+    """First vocab row of this rank's shard = the summed row counts of the lower ranks (one small all-gather; called once,
+    when the sharded head is installed).  ``group``: a process group or a ``SymmetricExchange``."""
+    pg = getattr(group, "group", group)
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(pg) == 1:
+        return 0
+    sizes = [None] * dist.get_world_size(pg)
+    dist.all_gather_object(sizes, int(n_local_rows), group=pg)
+    return int(sum(sizes[: dist.get_rank(pg)]))
+
+
 def shard_weight(weight: torch.Tensor, world: int, rank: int) -> tuple[torch.Tensor, int]:
     """(this rank's rows as a contiguous tensor, v_offset)."""
     b, e = shard_range(weight.shape[0], world, rank)

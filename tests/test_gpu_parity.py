@@ -539,3 +539,80 @@ def test_fused_final_norm_inside_an_unmodified_transformers_model(with_value_hea
     for n in g0:
         err = (g0[n] - g1[n]).abs().max().item() / max(g0[n].abs().max().item(), 1e-12)
         assert err < 3e-2, (n, err)   # bf16 autograd on both sides
+
+
+def test_fused_grad_accumulation_three_micro_batches_sum_in_f32():
+    """set_fused_grad_accumulation(True): the dW GEMM epilogue adds into lm_head.weight.main_grad (f32); three micro-batches
+    accumulate to the f32 sum of their gradients, autograd sees no weight gradient, fold_main_grad hands it to .grad."""
+    from pipelinerl_swe_b200 import RLConfig, fold_main_grad, rl_step, set_fused_grad_accumulation
+    H, V = 128, 3000
+    cfg = RLConfig(policy_loss="ppo", batch_size=3, kl_coef=0.1, final_kl_coef=0.1, entropy_bonus=0.01, final_entropy_bonus=0.01)
+    cases = [([70, 41, 90], 5), ([201], 6), ([30, 30, 60, 81], 7)]
+    # per-micro-batch gradients through the default path (fresh dW each), summed in f32 on the host side
+    want = torch.zeros(V, H, device=_dev())
+    models = []
+    for lens, seed in cases:
+        m = StubLM(H, V, sum(lens), seed=8).to(_dev())          # same lm_head weights (seed), different hidden length
+        loss, _ = rl_step(m, _to_dev(synthetic_packed_batch(lens, V, seed=seed)), 0, 1, cfg)
+        loss.backward()
+        want += m.lm_head.weight.grad.float()
+        models.append(m)
+    set_fused_grad_accumulation(True)
+    try:
+        head_owner = StubLM(H, V, 201, seed=8).to(_dev())
+        for (lens, seed), m in zip(cases, models):
+            m.lm_head = head_owner.lm_head                       # ONE shared lm_head parameter across the micro-batches
+            m.zero_grad(set_to_none=True)
+            loss, _ = rl_step(m, _to_dev(synthetic_packed_batch(lens, V, seed=seed)), 0, 1, cfg)
+            loss.backward()
+            assert m.hidden.grad is not None
+        w = head_owner.lm_head.weight
+        assert w.grad is None and w.main_grad.dtype == torch.float32
+        assert _rel(w.main_grad, want) < 5e-3                     # `want` carries one bf16 rounding per micro-batch
+        fold_main_grad(head_owner)
+        assert w.grad is not None and w.grad.dtype == torch.bfloat16 and _rel(w.grad, want) < 1e-2
+        assert torch.count_nonzero(w.main_grad) == 0
+    finally:
+        set_fused_grad_accumulation(False)
+
+
+@pytest.mark.parametrize("save", [True, False])
+def test_row_chunked_backward_under_a_scratch_budget(save):
+    """A 20 000-token row at the real vocab size exceeds a 2 GiB [rows x vocab] budget: forward + backward run in row chunks
+    (first chunk keeps its logits, the rest are recomputed) and reproduce the un-chunked result; the scratch stays under
+    the budget."""
+    from pipelinerl_swe_b200 import lm_head as LH
+    from pipelinerl_swe_b200 import ops
+    d = _dev()
+    M, H, V, temp = 20000, 256, 152064, 0.9
+    g = torch.Generator(device=d).manual_seed(21)
+    h = torch.randn(M, H, device=d, generator=g).bfloat16().requires_grad_(True)
+    w = (torch.randn(V, H, device=d, generator=g) * 0.05).bfloat16().requires_grad_(True)
+    tgt = torch.randint(0, V, (M,), device=d, generator=g)
+    c = torch.randn(M, 2, device=d, generator=g) * torch.tensor([0.1, 0.01], device=d)
+    outs = []
+    old_budget, old_save = LH.saved_logits_budget(), LH.save_logits_enabled()
+    try:
+        LH.set_save_logits(save)
+        for budget in (64 << 30, 2 << 30):
+            LH.set_saved_logits_budget(budget)
+            n_chunks = len(LH.row_chunks(M, V))
+            assert n_chunks == (1 if budget > (8 << 30) else 3)
+            ops._ws_cache.clear()
+            torch.cuda.empty_cache()
+            torch.cuda.reset_peak_memory_stats(d)
+            base = torch.cuda.memory_allocated(d)
+            out = LH.LMHeadLogprobFunction.apply(h, w, tgt, 1.0 / temp, None, 0)
+            (out * c).sum().backward()
+            peak = torch.cuda.max_memory_allocated(d) - base
+            outs.append((out.detach().clone(), h.grad.clone(), w.grad.clone(), peak))
+            h.grad = w.grad = None
+    finally:
+        LH.set_saved_logits_budget(old_budget)
+        LH.set_save_logits(old_save)
+    (o0, gh0, gw0, p0), (o1, gh1, gw1, p1) = outs
+    assert torch.equal(o0, o1)                                   # K1 is row-independent: bit-identical log-probs / entropies
+    assert _rel(gh1, gh0.float()) < 1e-2 and _rel(gw1, gw0.float()) < 1e-2
+    per_row = -(-V // 256) * 512
+    assert p0 > M * per_row                                      # un-chunked: the whole [rows x vocab] bf16 buffer existed
+    assert p1 < (2 << 30) * (2 if save else 1) + 3 * V * H * 4 + (64 << 20), (p0, p1)   # chunked: <= budget per live buffer + dW temporaries

@@ -294,3 +294,70 @@ def test_install_fused_final_norm_is_an_in_place_reclass():
         install_fused_final_norm(bad)
     with pytest.raises(AttributeError):
         install_fused_final_norm(torch.nn.Linear(4, 4))
+
+
+def test_row_chunks_respect_the_budget():
+    """set_saved_logits_budget: every chunk's rows x padded vocab x 2 B fits the budget (floor 4096 rows), chunks tile the
+    rows exactly, are multiples of 512 rows, balanced, and a micro-batch that fits is never cut."""
+    from pipelinerl_swe_b200.lm_head import row_chunks
+    V = 152064
+    per_row = -(-V // 256) * 256 * 2
+    assert row_chunks(8191, V) == [(0, 8191)]
+    for M, budget in ((20000, 4 << 30), (20000, 2 << 30), (49999, 4 << 30), (50000, 1 << 28)):
+        ch = row_chunks(M, V, budget)
+        assert ch[0][0] == 0 and ch[-1][1] == M and all(a[1] == b[0] for a, b in zip(ch, ch[1:]))
+        fit = max(4096, budget // per_row // 512 * 512)
+        assert all(r1 - r0 <= fit for r0, r1 in ch) and all((r1 - r0) % 512 == 0 for r0, r1 in ch[:-1])
+        assert len(ch) == -(-M // fit)                                  # as few chunks as the budget allows
+        assert ch[-1][1] - ch[-1][0] > M - (len(ch) - 1) * fit - 1          # and balanced: the last one is not the sliver M % fit
+    assert row_chunks(49999, 19008) == [(0, 49999)]   # a vocab shard of eight: 50k rows fit the default budget
+
+
+def test_install_with_vocab_group_records_the_shard():
+    """install_fused_lm_head(model, vocab_group=..., v_offset=...) marks the head as a vocab shard; rl_step's request picks it up."""
+    from pipelinerl_swe_b200 import install_fused_lm_head
+    m = torch.nn.ModuleDict({"lm_head": torch.nn.Linear(16, 40, bias=False)})
+    grp = object()
+    head = install_fused_lm_head(m, vocab_group=grp, v_offset=80)
+    assert head.vocab_group is grp and head.v_offset == 80
+    assert install_fused_lm_head(m) is head and head.vocab_group is grp          # a later plain install keeps it
+    assert "vocab_group" not in dict(head.named_parameters()) and list(m.state_dict().keys()) == ["lm_head.weight"]
+
+
+def test_rl_step_signature_is_the_reference_plus_keyword_only_extras():
+    import inspect
+    from pipelinerl_swe_b200 import rl_step
+    params = list(inspect.signature(rl_step).parameters.values())
+    assert [p.name for p in params[:5]] == ["model", "batch", "current_step", "max_step", "config"]   # rl/__init__.py:130-136
+    assert all(p.kind is inspect.Parameter.KEYWORD_ONLY and p.default is None for p in params[5:])
+
+
+def test_staged_reference_reproduces_the_golden_vectors_and_the_oracle():
+    """oracle/_ref (the reference's own files staged by oracle/build_ref.py; what bench.py's CPU arm runs) gives the committed
+    golden loss / stats, i.e. it IS the code that pinned the oracle.  Skipped where neither _ref nor /root/reference exists."""
+    import types
+    from oracle import build_ref
+    if not build_ref.available() and not build_ref.build():
+        pytest.skip("oracle/_ref not staged and /root/reference absent")
+    rl = build_ref.load()
+    import sys
+    PBE = sys.modules["pipelinerl.finetune.types"].PipelineBatchEncoding
+    from helpers import load_rl_case
+    import oracle
+    for name in ("ppo_kl_packed", "reinforce_gn_of_ent"):
+        batch, ocfg, meta, x = load_rl_case(name)
+        h = x["hidden"].float().requires_grad_(True)
+        w = x["weight"].float().requires_grad_(True)
+        hh = h if h.dim() == 3 else h[None]
+
+        class M(torch.nn.Module):
+            def forward(self, **kw):
+                return types.SimpleNamespace(logits=hh @ w.t())
+
+        b = {k: v for k, v in batch.items() if k != "seq_boundaries"}
+        loss, stats = rl.rl_step(M(), PBE(**b, model_version=0), meta["step"], meta["max_step"], rl.RLConfig(**meta["cfg"]))
+        assert abs(float(loss) - float(x["loss"])) <= 1e-6 * abs(float(x["loss"])) + 1e-7
+        for k, v in meta["stats"].items():
+            assert abs(stats[k] - v) <= 1e-5 * abs(v) + 1e-6, (name, k)
+        o_loss, _ = oracle.oracle_rl_step(x["hidden"].float(), x["weight"].float(), batch, meta["step"], meta["max_step"], ocfg)
+        assert abs(float(o_loss) - float(loss)) <= 1e-5 * abs(float(loss)) + 1e-6

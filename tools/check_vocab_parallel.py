@@ -63,11 +63,41 @@ def main():
     e_dw = rel(w1.grad, w0.grad[v_off:v_off + w_shard.shape[0]])
     e_dh = rel(h1.grad, h0.grad)
     ok = identical and e_out < 1e-4 and e_dw < 1e-2 and e_dh < 1e-2
+
+    # ---- the drop-in itself: rl_step(model, batch, step, max_step, config, vocab_group=...) on a model whose lm_head holds
+    #      only this rank's vocab rows == rl_step on the unsharded model (loss, all stats, dH, this rank's rows of dW)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import StubLM, synthetic_packed_batch
+    from pipelinerl_swe_b200 import RLConfig, rl_step
+    Hs, Vs, lens = 256, 32000 + 8, [300, 140, 260]
+    batch = synthetic_packed_batch(lens, Vs, seed=5)
+    dbatch = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+    cfg = RLConfig(policy_loss="ppo", batch_size=3, kl_coef=0.1, final_kl_coef=0.1, entropy_bonus=0.01, final_entropy_bonus=0.01,
+                   temperature=0.9)
+    full = StubLM(Hs, Vs, sum(lens), seed=8).to(dev)
+    loss_f, stats_f = rl_step(full, dbatch, 1, 10, cfg)
+    loss_f.backward()
+    shard = StubLM(Hs, Vs, sum(lens), seed=8).to(dev)
+    w_sh, off = shard_weight(shard.lm_head.weight.detach(), world, rank)
+    shard.lm_head = torch.nn.Linear(Hs, w_sh.shape[0], bias=False, dtype=torch.bfloat16, device=dev)
+    with torch.no_grad():
+        shard.lm_head.weight.copy_(w_sh)
+    group = SymmetricExchange(dist.group.WORLD, dev, sum(lens), Hs) if symmetric else dist.group.WORLD
+    loss_s, stats_s = rl_step(shard, dbatch, 1, 10, cfg, vocab_group=group)
+    loss_s.backward()
+    assert shard.lm_head.v_offset == off, (shard.lm_head.v_offset, off)
+    e_loss = abs(loss_s.item() - loss_f.item())
+    e_stats = max(abs(stats_s[k] - stats_f[k]) / (abs(stats_f[k]) + 0.1) for k in stats_f)   # 1e-3 relative with a 1e-4 absolute floor
+    e_rl_dh = rel(shard.hidden.grad, full.hidden.grad)
+    e_rl_dw = rel(shard.lm_head.weight.grad, full.lm_head.weight.grad[off:off + w_sh.shape[0]])
+    rl_ok = set(stats_s) == set(stats_f) and e_loss < 1e-5 + 1e-3 * abs(loss_f.item()) and e_stats < 1e-3 and e_rl_dh < 1e-2 and e_rl_dw < 1e-2
+    ok = ok and rl_ok
     t = torch.tensor([int(ok)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(f"VOCAB_PARALLEL transport={'nvswitch-multicast' if symmetric else 'nccl'} world={world} {'OK' if t.item() else 'FAIL'} identical_across_ranks={identical} "
-              f"max|d(logprob,entropy)|={e_out:.2e} rel dW={e_dw:.2e} rel dH={e_dh:.2e}", flush=True)
+              f"max|d(logprob,entropy)|={e_out:.2e} rel dW={e_dw:.2e} rel dH={e_dh:.2e} | rl_step(vocab_group=...): "
+              f"|d loss|={e_loss:.1e} stats rel={e_stats:.1e} rel dH={e_rl_dh:.2e} rel dW={e_rl_dw:.2e}", flush=True)
     dist.destroy_process_group()
     sys.exit(0 if t.item() else 1)
 
