@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200GRPO_ABI_VERSION 2
+#define B200GRPO_ABI_VERSION 3
 
 enum {
   B200GRPO_OK = 0,
@@ -137,7 +137,8 @@ int b200grpo_token_loss(const float* logprob, const float* entropy, const int64_
 
 /* Segment boundaries exactly as rl/__init__.py:159-170: starts where position_ids==0 plus
  * index 0, then T.  bounds i32[T+1] (capacity), n_bounds i32[1] = S+1.
- * workspace: 4*ceil(T/1024) bytes. */
+ * position_ids is read once (8 B/token); workspace: b200grpo_segment_bounds_workspace(T) bytes. */
+size_t b200grpo_segment_bounds_workspace(int T);
 int b200grpo_segment_bounds(const int64_t* position_ids, int T, int32_t* bounds,
                             int32_t* n_bounds, void* workspace, size_t workspace_bytes,
                             void* stream);
@@ -184,26 +185,34 @@ int b200grpo_lmhead_bwd_staged(const void* hidden, int64_t ldh, const void* weig
  * K4  group-normalised advantages.  Replaces the pandas path rl/__init__.py:394-499.
  * Per rollout row i (n_rows): reward f64 (rewards[0] of the row, :402), group_key i32
  * (dense id of group_id+"_"+step_index, :395), row_offsets i64[n_rows+1] (token ranges),
- * n_labels i32 (:487), has_eos u8 (:481-484).  token_rewards f64[total] (nullable: every
- * token of a row then carries row_reward, the documented assumption at :401) feeds the
- * numerator (:466).  Outputs f32[total]: advantages, group_tokens, num_labels, overflow.
- * Group mean / ddof=1 std / mean length are computed in f64 like pandas (:408-416);
- * a singleton group has std NaN -> 0 (:466).
+ * n_labels i32 (:487), has_eos u8 (:481-484).  row_order i32[n_rows] = the row indices stably
+ * sorted by group_key (dataset order inside a group) and group_starts i32[n_groups+1] = where
+ * each group begins in it: one thread per group folds its rows in that order, O(n_rows) reads.
+ * Group mean / ddof=1 std / mean length follow pandas' groupby kernels operation by operation
+ * (Kahan-compensated mean, Welford variance, f64, no FMA contraction; :408-416), so statistics
+ * and advantages are bit-identical to the reference's; a singleton group has std NaN -> 0 (:466).
+ * token_rewards f64[total] (nullable: every token of a row then carries row_reward, the
+ * documented assumption at :401) feeds the numerator (:466).
+ * Outputs f32[total]: advantages, group_tokens, num_labels, overflow (the device batch columns);
+ * advantages_f64 (nullable) f64[total]: the un-rounded values the reference's lists hold.
  * ------------------------------------------------------------------------------------- */
 size_t b200grpo_group_advantage_workspace(int n_rows, int n_groups);
 int b200grpo_group_advantage(const double* row_reward, const int32_t* group_key,
+                             const int32_t* row_order, const int32_t* group_starts,
                              const int64_t* row_offsets, const int32_t* n_labels,
                              const uint8_t* has_eos, const double* token_rewards, int n_rows,
                              int n_groups, int divide_by_std, float* advantages,
                              float* group_tokens, float* num_labels, float* overflow,
-                             void* workspace, size_t workspace_bytes, void* stream);
-/* Same statistics, one output value per ROLLOUT (f32[n_rows] each) instead of per token: what the list-of-dict
- * contract of populate_rl_data needs when rewards are constant inside a rollout (the host repeats the value). */
+                             double* advantages_f64, void* workspace, size_t workspace_bytes,
+                             void* stream);
+/* Same statistics, one f64 value per ROLLOUT: advantages[n_rows] and group_tokens[n_rows] (mean row length of the
+ * row's group) -- what the list-of-dict contract of populate_rl_data holds as Python floats when rewards are constant
+ * inside a rollout (the host repeats the value; num_labels and overflow are host-side facts). */
 int b200grpo_group_advantage_rows(const double* row_reward, const int32_t* group_key,
-                                  const int64_t* row_offsets, const int32_t* n_labels,
-                                  const uint8_t* has_eos, int n_rows, int n_groups, int divide_by_std,
-                                  float* advantages, float* group_tokens, float* num_labels,
-                                  float* overflow, void* workspace, size_t workspace_bytes, void* stream);
+                                  const int32_t* row_order, const int32_t* group_starts,
+                                  const int64_t* row_offsets, int n_rows, int n_groups, int divide_by_std,
+                                  double* advantages, double* group_tokens, void* workspace,
+                                  size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * K6  weight-update buckets.  Replaces the per-parameter loop of

@@ -72,6 +72,7 @@ SIGNATURES = {
     "b200grpo_lmhead_finalize": (_i, [_p, _i, _i, _p, _p, _p, _p]),
     "b200grpo_token_loss_workspace": (_sz, [_i, _i]),
     "b200grpo_token_loss": (_i, [_p] * 12 + [_i, _i, C.POINTER(LossCfg)] + [_p] * 6 + [_sz, _p]),
+    "b200grpo_segment_bounds_workspace": (_sz, [_i]),
     "b200grpo_segment_bounds": (_i, [_p, _i, _p, _p, _p, _sz, _p]),
     "b200grpo_lmhead_bwd_workspace": (_sz, [_i, _i, _i, _i]),
     "b200grpo_lmhead_bwd": (_i, [_p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i64, _f, _p, _p, _i64, _p, _i64, _i, _i,
@@ -79,8 +80,8 @@ SIGNATURES = {
     "b200grpo_lmhead_bwd_staged": (_i, [_p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i64, _f, _p, _p, _i64, _p, _i64, _i, _i,
                                         _i, _p, _sz, _p]),
     "b200grpo_group_advantage_workspace": (_sz, [_i, _i]),
-    "b200grpo_group_advantage": (_i, [_p] * 6 + [_i, _i, _i] + [_p] * 5 + [_sz, _p]),
-    "b200grpo_group_advantage_rows": (_i, [_p] * 5 + [_i, _i, _i] + [_p] * 5 + [_sz, _p]),
+    "b200grpo_group_advantage": (_i, [_p] * 8 + [_i, _i, _i] + [_p] * 6 + [_sz, _p]),
+    "b200grpo_group_advantage_rows": (_i, [_p] * 5 + [_i, _i, _i] + [_p] * 3 + [_sz, _p]),
     "b200grpo_bucket_workspace": (_sz, [_i]),
     "b200grpo_bucket_numel": (_i64, [_p, _i]),
     "b200grpo_bucket_pack": (_i, [_p, _p, _p, _i, _p, _i64, _p, _sz, _p]),

@@ -66,10 +66,14 @@ def rollout_scalars(dataset: list[dict[str, Any]], eos_token_id: int):
         eos[i] = eos_token_id in ids
     offsets = np.zeros(n + 1, dtype=np.int64)
     np.cumsum(lens, out=offsets[1:])
+    # stable sort of the rows by group key (numpy radix argsort over int32: O(n)) -> the CSR the stats kernel walks
+    order = np.argsort(gkey, kind="stable").astype(np.int32)
+    starts = np.zeros(len(keys) + 1, dtype=np.int32)
+    np.cumsum(np.bincount(gkey, minlength=len(keys)), out=starts[1:])
     tok_rewards = None
     if not uniform:  # per-token rewards differ inside a row: ship them (f64) so :466 is followed literally
         tok_rewards = np.concatenate([np.asarray(row["rewards"], dtype=np.float64) for row in dataset])
-    return reward, gkey, offsets, nlab, eos, len(keys), tok_rewards
+    return reward, gkey, offsets, nlab, eos, len(keys), tok_rewards, order, starts
 
 
 def populate_rl_data(dataset: list[dict[str, Any]], eos_token_id: int, config, device: torch.device | str | None = None) -> list[dict[str, Any]]:
@@ -81,27 +85,30 @@ def populate_rl_data(dataset: list[dict[str, Any]], eos_token_id: int, config, d
     if not dataset:
         return dataset
     dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
-    reward, gkey, offsets, nlab, eos, n_groups, tok_rewards = rollout_scalars(dataset, eos_token_id)
+    reward, gkey, offsets, nlab, eos, n_groups, tok_rewards, order, starts = rollout_scalars(dataset, eos_token_id)
     to = lambda a: torch.from_numpy(a).to(dev, non_blocking=True)  # noqa: E731
     std = bool(config.divide_advantage_by_std)
     if tok_rewards is None:
-        rows = ops.group_advantage_rows(to(reward), to(gkey), to(offsets), to(nlab), to(eos), n_groups, std)
-        adv, gtok, _, ovf = rows.cpu().numpy().astype(np.float64).tolist()  # python floats carry the f32 values the trainer will see
+        rows = ops.group_advantage_rows(to(reward), to(gkey), to(offsets), n_groups, std, to(order), to(starts))
+        adv, gtok = rows.cpu().numpy().tolist()  # f64 -> Python floats: the very values the reference's lists hold (:461-469, :486)
         for i, row in enumerate(dataset):
             n = int(offsets[i + 1] - offsets[i])
             row["advantages"] = [adv[i]] * len(row["rewards"])
             row["group_tokens"] = [gtok[i]] * n
-            row["overflow"] = [ovf[i]] * len(row["overflow"]) if n > 0 else []
+            row["overflow"] = [0.0 if eos[i] else 1.0] * len(row["overflow"])   # :481-484
             row["num_labels"] = [int(nlab[i])] * n
         return dataset
-    out = ops.group_advantage(to(reward), to(gkey), to(offsets), to(nlab), to(eos), n_groups, std, to(tok_rewards))
-    host = out.cpu().numpy().astype(np.float64)
+    # rewards vary inside a rollout: the GPU forms every token's f64 advantage (:466 followed literally)
+    out, adv64 = ops.group_advantage(to(reward), to(gkey), to(offsets), to(nlab), to(eos), n_groups, std, to(tok_rewards),
+                                     to(order), to(starts), want_f64=True)
+    host = adv64.cpu().numpy()
+    gtok = ops.group_advantage_rows(to(reward), to(gkey), to(offsets), n_groups, std, to(order), to(starts))[1].cpu().numpy().tolist()
     for i, row in enumerate(dataset):
         a, b = int(offsets[i]), int(offsets[i + 1])
         n_adv = len(row["rewards"])
-        row["advantages"] = host[0, a:a + n_adv].tolist()
-        row["group_tokens"] = host[1, a:b].tolist()
-        row["overflow"] = [float(host[3, a])] * len(row["overflow"]) if b > a else []
+        row["advantages"] = host[a:a + n_adv].tolist()
+        row["group_tokens"] = [gtok[i]] * (b - a)
+        row["overflow"] = [0.0 if eos[i] else 1.0] * len(row["overflow"])
         row["num_labels"] = [int(nlab[i])] * (b - a)
     return dataset
 

@@ -1,25 +1,37 @@
 // Segment boundaries of a packed row, bit-exact with
 // /root/reference/pipelinerl/finetune/rl/__init__.py:159-170:
 //   starts = where(position_ids == 0) with index 0 forced; bounds = cat(starts, [T]).
-// Three small launches (count -> scan -> scatter); ordered output, no atomics.
+// Three small launches (count -> scan -> scatter); ordered output, no atomics.  position_ids is read ONCE (8 B/token,
+// eight independent coalesced loads in flight per thread): the count pass also leaves a 1-bit-per-token start mask
+// (one ballot word per warp and trip, 1/8 B per token) and the scatter pass works from that mask alone.
 #include "common.cuh"
 
 namespace b200grpo {
 
 constexpr int SB_THREADS = 256;
-constexpr int SB_ITEMS = 4;  // 1024 positions per block
+constexpr int SB_ITEMS = 8;                         // 2048 positions per block
+constexpr int SB_WORDS = SB_THREADS * SB_ITEMS / 32;  // 64 mask words per block
 
-__device__ __forceinline__ bool is_start(const int64_t* pos, int i) { return i == 0 || pos[i] == 0; }
-
-__global__ void __launch_bounds__(SB_THREADS) seg_count_kernel(const int64_t* pos, int T, int* block_counts) {
+__global__ void __launch_bounds__(SB_THREADS) seg_count_kernel(const int64_t* __restrict__ pos, int T, int* __restrict__ block_counts,
+                                                               uint32_t* __restrict__ mask) {
   const int base = blockIdx.x * SB_THREADS * SB_ITEMS;
+  int64_t v[SB_ITEMS];
+#pragma unroll
+  for (int k = 0; k < SB_ITEMS; ++k) {   // all loads issued before any is used
+    const int i = base + k * SB_THREADS + threadIdx.x;
+    v[k] = i < T ? __ldg(pos + i) : 1;
+  }
   int c = 0;
 #pragma unroll
   for (int k = 0; k < SB_ITEMS; ++k) {
     const int i = base + k * SB_THREADS + threadIdx.x;
-    if (i < T && is_start(pos, i)) ++c;
+    const bool f = i < T && (i == 0 || v[k] == 0);
+    const unsigned m = __ballot_sync(0xffffffffu, f);
+    if ((threadIdx.x & 31) == 0) {
+      mask[(base + k * SB_THREADS + (int)threadIdx.x) >> 5] = m;   // word of tokens [i, i + 32)
+      c += __popc(m);
+    }
   }
-  c = (int)warp_sum((float)c);
   __shared__ int sh[SB_THREADS / 32];
   if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = c;
   __syncthreads();
@@ -55,26 +67,28 @@ __global__ void __launch_bounds__(1024) seg_scan_kernel(int* block_counts, int n
   if (threadIdx.x == 0) *n_bounds = carry + 1;
 }
 
-__global__ void __launch_bounds__(SB_THREADS) seg_scatter_kernel(const int64_t* pos, int T, const int* block_offsets,
-                                                                 const int32_t* n_bounds, int32_t* bounds) {
-  // positions are visited in index order: thread t owns SB_ITEMS consecutive positions
-  const int base = blockIdx.x * SB_THREADS * SB_ITEMS + threadIdx.x * SB_ITEMS;
-  bool f[SB_ITEMS];
-  int c = 0;
+// one thread per mask word (32 positions), SB_WORDS words per block == one count block: ordered emission of the set bits
+__global__ void __launch_bounds__(SB_WORDS) seg_scatter_kernel(const uint32_t* __restrict__ mask, int T, const int* __restrict__ block_offsets,
+                                                               const int32_t* __restrict__ n_bounds, int32_t* __restrict__ bounds) {
+  const int word = blockIdx.x * SB_WORDS + threadIdx.x;
+  uint32_t m = (word * 32 < T) ? mask[word] : 0u;
+  const int c = __popc(m);
+  // exclusive scan of the SB_WORDS (= 64) popcounts: two warps
+  int incl = c;
 #pragma unroll
-  for (int k = 0; k < SB_ITEMS; ++k) { f[k] = (base + k < T) && is_start(pos, base + k); c += f[k]; }
-  __shared__ int sh[SB_THREADS];
-  sh[threadIdx.x] = c;
-  __syncthreads();
-  for (int o = 1; o < SB_THREADS; o <<= 1) {
-    const int add = threadIdx.x >= o ? sh[threadIdx.x - o] : 0;
-    __syncthreads();
-    sh[threadIdx.x] += add;
-    __syncthreads();
+  for (int o = 1; o < 32; o <<= 1) {
+    const int up = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((threadIdx.x & 31) >= o) incl += up;
   }
-  int w = block_offsets[blockIdx.x] + sh[threadIdx.x] - c;
-#pragma unroll
-  for (int k = 0; k < SB_ITEMS; ++k) if (f[k]) bounds[w++] = base + k;
+  __shared__ int warp_total[SB_WORDS / 32];
+  if ((threadIdx.x & 31) == 31) warp_total[threadIdx.x >> 5] = incl;
+  __syncthreads();
+  int w = block_offsets[blockIdx.x] + incl - c;
+  for (int k = 0; k < (int)(threadIdx.x >> 5); ++k) w += warp_total[k];
+  while (m) {
+    bounds[w++] = word * 32 + __ffs(m) - 1;
+    m &= m - 1;
+  }
   if (blockIdx.x == 0 && threadIdx.x == 0) bounds[*n_bounds - 1] = T;
 }
 
@@ -82,18 +96,26 @@ __global__ void __launch_bounds__(SB_THREADS) seg_scatter_kernel(const int64_t* 
 
 using namespace b200grpo;
 
+static size_t seg_counts_bytes(int T) { return align_up((size_t)ceil_div(T, SB_THREADS * SB_ITEMS) * sizeof(int), 256); }
+
+extern "C" size_t b200grpo_segment_bounds_workspace(int T) {
+  if (T < 1) T = 1;
+  return seg_counts_bytes(T) + align_up((size_t)ceil_div(T, SB_THREADS * SB_ITEMS) * SB_WORDS * sizeof(uint32_t), 256);
+}
+
 extern "C" int b200grpo_segment_bounds(const int64_t* position_ids, int T, int32_t* bounds, int32_t* n_bounds,
                                        void* workspace, size_t workspace_bytes, void* stream) {
   if (int e = check_device_sm100()) return e;
   B200_REQUIRE(position_ids && bounds && n_bounds && workspace && T >= 1, "segment_bounds: bad argument");
   const int n_blocks = ceil_div(T, SB_THREADS * SB_ITEMS);
-  if (workspace_bytes < (size_t)n_blocks * sizeof(int)) { set_error("segment_bounds: workspace too small"); return B200GRPO_EWORKSPACE; }
+  if (workspace_bytes < b200grpo_segment_bounds_workspace(T)) { set_error("segment_bounds: workspace too small"); return B200GRPO_EWORKSPACE; }
   cudaStream_t st = (cudaStream_t)stream;
   int* counts = (int*)workspace;
+  uint32_t* mask = (uint32_t*)((char*)workspace + seg_counts_bytes(T));
   ProfScope ps(PROF_SEGMENTS, st);
-  seg_count_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts);
+  seg_count_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts, mask);
   seg_scan_kernel<<<1, 1024, 0, st>>>(counts, n_blocks, n_bounds);
-  seg_scatter_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts, n_bounds, bounds); count_launch(3);
+  seg_scatter_kernel<<<n_blocks, SB_WORDS, 0, st>>>(mask, T, counts, n_bounds, bounds); count_launch(3);
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }

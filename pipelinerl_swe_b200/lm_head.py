@@ -230,15 +230,20 @@ class LMHeadLogprobFunction(torch.autograd.Function):
 
 
 def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch.Tensor, temperature: float, group=None,
-                    v_offset: int = 0, labels: torch.Tensor | None = None) -> torch.Tensor:
+                    v_offset: int = 0, labels: torch.Tensor | None = None, boundary_ids: torch.Tensor | None = None,
+                    boundary_labels: torch.Tensor | None = None) -> torch.Tensor:
     """hidden [B,L,H], input_ids [B,L] -> f32 [B,L,2]: (logprob of input_ids[t+1], entropy) per position.
 
     Position L-1 of every row has no next token: it is scored against token 0 and the
-    caller drops it (the reference slices ``[:, :-1]``, rl/__init__.py:200,208).
+    caller drops it (the reference slices ``[:, :-1]``, rl/__init__.py:200,208) -- unless ``boundary_ids`` [B] names
+    the token that follows each row (the first token of the next sequence-parallel slice): then L-1 is scored against it.
     With ``labels`` and ``set_skip_masked_tokens(True)`` only positions whose next token is labelled are computed.
     """
     B, L, H = hidden.shape
-    targets = torch.roll(input_ids, shifts=-1, dims=1).reshape(-1).contiguous()
+    targets = torch.roll(input_ids, shifts=-1, dims=1)
+    if boundary_ids is not None:
+        targets[:, -1] = boundary_ids.to(targets.dtype)
+    targets = targets.reshape(-1).contiguous()
     h2 = hidden.reshape(B * L, H)
     if h2.dtype != torch.bfloat16:
         h2 = h2.to(torch.bfloat16)
@@ -247,7 +252,7 @@ def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch
     sink = _GradSink(weight) if (isinstance(weight, nn.Parameter) and w is weight) else None   # fused f32 accumulate target
     if labels is not None and skip_masked_tokens_enabled():
         keep = torch.roll(labels, shifts=-1, dims=1) != -100
-        keep[:, -1] = False                                  # no next token
+        keep[:, -1] = False if boundary_labels is None else (boundary_labels != -100)   # no next token unless it is carried
         idx = keep.reshape(-1).nonzero().squeeze(1)          # host sync: the row count sizes the launch
         out = torch.zeros(B * L, 2, dtype=torch.float32, device=hidden.device)
         if idx.numel() > 0:
@@ -267,6 +272,8 @@ class LogprobRequest:
     group: object = None
     v_offset: int = 0
     labels: torch.Tensor | None = None   # only read when set_skip_masked_tokens(True)
+    boundary_ids: torch.Tensor | None = None      # [B] next-slice first token (types.make_slices(carry_boundary_target=True))
+    boundary_labels: torch.Tensor | None = None
 
 
 _tls = threading.local()
@@ -315,7 +322,8 @@ class FusedLMHead(nn.Module):
         group, v_offset = req.group, req.v_offset
         if group is None and getattr(self, "vocab_group", None) is not None:   # sharded head declared at install time
             group, v_offset = self.vocab_group, self.v_offset
-        return lmhead_logprobs(hidden, self.weight, req.input_ids, req.temperature, group, v_offset, req.labels)
+        return lmhead_logprobs(hidden, self.weight, req.input_ids, req.temperature, group, v_offset, req.labels,
+                               req.boundary_ids, req.boundary_labels)
 
 
 def _check_fusable(linear: nn.Module) -> None:

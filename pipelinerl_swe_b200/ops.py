@@ -154,7 +154,7 @@ def segment_bounds(position_ids: torch.Tensor) -> torch.Tensor:
     T = pos.numel()
     bounds = torch.empty(T + 1, dtype=torch.int32, device=pos.device)
     n = torch.empty(1, dtype=torch.int32, device=pos.device)
-    ws = _workspace(pos.device, 4 * ((T + 1023) // 1024) + 256)
+    ws = _workspace(pos.device, lib().b200grpo_segment_bounds_workspace(T))
     check(lib().b200grpo_segment_bounds(pos.data_ptr(), T, bounds.data_ptr(), n.data_ptr(), ws.data_ptr(), ws.numel(), _stream()))
     return bounds[: int(n.item())]
 
@@ -176,38 +176,55 @@ def gemm_bf16(A: torch.Tensor, B: torch.Tensor, a_mn_major=False, b_mn_major=Fal
     return out
 
 
+def group_order(group_key: torch.Tensor, n_groups: int) -> tuple[torch.Tensor, torch.Tensor]:
+    """(row_order i32[n_rows], group_starts i32[n_groups+1]): rows stably sorted by dense group key -- the CSR K4 walks."""
+    order = torch.argsort(group_key, stable=True).to(torch.int32)
+    starts = torch.zeros(n_groups + 1, dtype=torch.int32, device=group_key.device)
+    if group_key.numel():
+        starts[1:] = torch.cumsum(torch.bincount(group_key, minlength=n_groups), 0).to(torch.int32)
+    return order, starts
+
+
 def group_advantage(row_reward: torch.Tensor, group_key: torch.Tensor, row_offsets: torch.Tensor, n_labels: torch.Tensor,
-                    has_eos: torch.Tensor, n_groups: int, divide_by_std: bool, token_rewards: torch.Tensor | None = None):
-    """K4 -> f32 [4, total_tokens]: advantages, group_tokens, num_labels, overflow."""
+                    has_eos: torch.Tensor, n_groups: int, divide_by_std: bool, token_rewards: torch.Tensor | None = None,
+                    row_order: torch.Tensor | None = None, group_starts: torch.Tensor | None = None, want_f64: bool = False):
+    """K4 -> f32 [4, total_tokens]: advantages, group_tokens, num_labels, overflow (+ f64 [total] advantages if ``want_f64``)."""
     _req(row_reward, torch.float64, "row_reward"); _req(group_key, torch.int32, "group_key")
     _req(row_offsets, torch.int64, "row_offsets"); _req(n_labels, torch.int32, "n_labels"); _req(has_eos, torch.uint8, "has_eos")
     if token_rewards is not None:
         _req(token_rewards, torch.float64, "token_rewards")
+    if row_order is None:
+        row_order, group_starts = group_order(group_key, n_groups)
+    _req(row_order, torch.int32, "row_order"); _req(group_starts, torch.int32, "group_starts")
     n_rows = row_reward.numel()
     total = int(row_offsets[-1].item()) if n_rows else 0
     pitch = (total + 3) // 4 * 4  # 16-byte aligned columns -> vector stores in the expand kernel
     out = torch.empty(4, pitch, dtype=torch.float32, device=row_reward.device)[:, :total]
+    adv64 = torch.empty(total, dtype=torch.float64, device=row_reward.device) if want_f64 else None
     n = lib().b200grpo_group_advantage_workspace(n_rows, n_groups)
     ws = _workspace(row_reward.device, n)
-    check(lib().b200grpo_group_advantage(row_reward.data_ptr(), group_key.data_ptr(), row_offsets.data_ptr(), n_labels.data_ptr(),
-                                         has_eos.data_ptr(), _ptr(token_rewards), n_rows, n_groups, int(divide_by_std),
-                                         out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(), out[3].data_ptr(),
-                                         ws.data_ptr(), ws.numel(), _stream()))
-    return out
+    check(lib().b200grpo_group_advantage(row_reward.data_ptr(), group_key.data_ptr(), row_order.data_ptr(), group_starts.data_ptr(),
+                                         row_offsets.data_ptr(), n_labels.data_ptr(), has_eos.data_ptr(), _ptr(token_rewards), n_rows,
+                                         n_groups, int(divide_by_std), out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(),
+                                         out[3].data_ptr(), _ptr(adv64), ws.data_ptr(), ws.numel(), _stream()))
+    return (out, adv64) if want_f64 else out
 
 
-def group_advantage_rows(row_reward: torch.Tensor, group_key: torch.Tensor, row_offsets: torch.Tensor, n_labels: torch.Tensor,
-                         has_eos: torch.Tensor, n_groups: int, divide_by_std: bool) -> torch.Tensor:
-    """K4, per-rollout form -> f32 [4, n_rows]: advantage, group_tokens, num_labels, overflow of every rollout."""
+def group_advantage_rows(row_reward: torch.Tensor, group_key: torch.Tensor, row_offsets: torch.Tensor, n_groups: int,
+                         divide_by_std: bool, row_order: torch.Tensor | None = None,
+                         group_starts: torch.Tensor | None = None) -> torch.Tensor:
+    """K4, per-rollout form -> f64 [2, n_rows]: advantage and mean group length of every rollout (bit-identical to pandas)."""
     _req(row_reward, torch.float64, "row_reward"); _req(group_key, torch.int32, "group_key")
-    _req(row_offsets, torch.int64, "row_offsets"); _req(n_labels, torch.int32, "n_labels"); _req(has_eos, torch.uint8, "has_eos")
+    _req(row_offsets, torch.int64, "row_offsets")
+    if row_order is None:
+        row_order, group_starts = group_order(group_key, n_groups)
+    _req(row_order, torch.int32, "row_order"); _req(group_starts, torch.int32, "group_starts")
     n_rows = row_reward.numel()
-    out = torch.empty(4, n_rows, dtype=torch.float32, device=row_reward.device)
+    out = torch.empty(2, n_rows, dtype=torch.float64, device=row_reward.device)
     ws = _workspace(row_reward.device, lib().b200grpo_group_advantage_workspace(n_rows, n_groups))
-    check(lib().b200grpo_group_advantage_rows(row_reward.data_ptr(), group_key.data_ptr(), row_offsets.data_ptr(), n_labels.data_ptr(),
-                                              has_eos.data_ptr(), n_rows, n_groups, int(divide_by_std), out[0].data_ptr(),
-                                              out[1].data_ptr(), out[2].data_ptr(), out[3].data_ptr(), ws.data_ptr(), ws.numel(),
-                                              _stream()))
+    check(lib().b200grpo_group_advantage_rows(row_reward.data_ptr(), group_key.data_ptr(), row_order.data_ptr(), group_starts.data_ptr(),
+                                              row_offsets.data_ptr(), n_rows, n_groups, int(divide_by_std), out[0].data_ptr(),
+                                              out[1].data_ptr(), ws.data_ptr(), ws.numel(), _stream()))
     return out
 
 

@@ -48,6 +48,7 @@ def _batch_dict(batch: Any) -> dict:
     get = (lambda k: batch.get(k)) if isinstance(batch, dict) else (lambda k: getattr(batch, k, None))
     d = {k: get(k) for k in names}
     d["is_packed"] = bool(get("is_packed"))
+    d["boundary"] = get("boundary")   # opt-in SP-slice boundary target (types.make_slices(carry_boundary_target=True))
     return d
 
 
@@ -106,10 +107,34 @@ def stats_from_metrics(m: list[float], cfg: LossCfg, input_size: int, has_values
     return stats
 
 
+_PER_TOKEN = ("labels", "position_ids", "rewards", "advantages", "ref_logprobs", "old_logprobs", "group_tokens", "num_labels", "overflow")
+
+
+def _append_boundary(b: dict) -> dict:
+    """[1, L] fields + the next slice's first token -> [1, L+1], so that K3's shifted view ``[:, 1:]`` reaches the boundary
+    target.  The carried position id is kept non-zero: the sequence that may start there is counted by the next slice."""
+    bd = b["boundary"]
+    out = dict(b)
+    for k in _PER_TOKEN:
+        if b.get(k) is None:
+            continue
+        extra = bd[k].to(b[k].dtype)
+        if k == "position_ids":
+            extra = extra.clamp(min=1)
+        out[k] = torch.cat([b[k], extra], dim=1)
+    return out
+
+
 def grpo_loss_from_logprobs(lp_ent: torch.Tensor, b: dict, cfg: LossCfg, values: torch.Tensor | None = None):
     """lp_ent f32 [B,L,2] from the fused lm_head -> (loss, device metrics f64[40])."""
-    logprob = lp_ent[:, :-1, 0].contiguous()  # the reference's [:, :-1] (:200)
-    entropy = lp_ent[:, :-1, 1].contiguous()
+    if b.get("boundary") is not None:   # the last position was scored against the next slice's first token: keep it
+        b = _append_boundary(b)
+        if values is not None:
+            values = torch.cat([values, values[:, -1:]], dim=1)   # placeholder for the carried position (never read as a prediction)
+        logprob, entropy = lp_ent[:, :, 0].contiguous(), lp_ent[:, :, 1].contiguous()
+    else:
+        logprob = lp_ent[:, :-1, 0].contiguous()  # the reference's [:, :-1] (:200)
+        entropy = lp_ent[:, :-1, 1].contiguous()
     sink: dict = {}
     loss = TokenLossFunction.apply(logprob, entropy, values, b, cfg, sink)
     return loss, sink["metrics"]
@@ -131,7 +156,9 @@ def _forward_loss(model, batch, current_step: int, max_step: int, config, vocab_
     if b["image_grid_thw"] is not None:
         model_inputs["image_grid_thw"] = b["image_grid_thw"]
     req = LogprobRequest(b["input_ids"], float(config.temperature), labels=b["labels"],
-                         group=getattr(head, "vocab_group", None), v_offset=getattr(head, "v_offset", 0))
+                         group=getattr(head, "vocab_group", None), v_offset=getattr(head, "v_offset", 0),
+                         boundary_ids=None if b["boundary"] is None else b["boundary"]["input_ids"].reshape(-1),
+                         boundary_labels=None if b["boundary"] is None else b["boundary"]["labels"].reshape(-1))
     with logprob_request(req):
         outputs = model(**model_inputs)
     lp_ent = outputs.logits

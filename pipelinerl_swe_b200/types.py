@@ -37,6 +37,9 @@ class PipelineBatchEncoding(BaseModel):
     seq_boundaries: torch.Tensor | None = None
     pixel_values: torch.Tensor | None = None
     image_grid_thw: torch.Tensor | None = None
+    # Beyond the reference (opt-in, see make_slices): the first token of the NEXT sequence-parallel slice -- every sliced
+    # field as a [1, 1] tensor -- so that this slice's last position can be scored against it.
+    boundary: Dict[str, torch.Tensor] | None = None
 
     @field_validator("input_ids", "attention_mask", "labels", "position_ids", "image_grid_thw", mode="before")
     @classmethod
@@ -75,6 +78,8 @@ class PipelineBatchEncoding(BaseModel):
             value = getattr(self, name)
             if isinstance(value, torch.Tensor):
                 setattr(self, name, value.to(device, non_blocking=True))
+        if self.boundary is not None:
+            self.boundary = {k: v.to(device, non_blocking=True) for k, v in self.boundary.items()}
         return self
 
     @classmethod
@@ -82,8 +87,15 @@ class PipelineBatchEncoding(BaseModel):
         merged = {**defaults, **data}
         return cls(**{k: v for k, v in merged.items() if k in cls.model_fields})
 
-    def make_slices(self, num_slices: int) -> List["PipelineBatchEncoding"]:
-        """Contiguous equal cuts of every [1, L] tensor (types.py:144-178)."""
+    def make_slices(self, num_slices: int, carry_boundary_target: bool = False) -> List["PipelineBatchEncoding"]:
+        """Contiguous equal cuts of every [1, L] tensor (types.py:144-178).
+
+        The reference scores position t of a slice against token t+1 OF THE SAME SLICE (rl/__init__.py:200,208), so the first
+        token of every slice but the first is nobody's target: ``num_slices - 1`` labelled tokens per row drop out of the
+        loss.  ``carry_boundary_target=True`` (opt-in, default off = the reference's behaviour bit for bit) attaches to each
+        slice but the last the next slice's first token (``boundary``: every sliced field as [1, 1]); ``rl_step`` then scores
+        the slice's last position against it -- the model forward is untouched, slices keep equal length (ring attention),
+        and the slices together cover exactly the targets of the un-sliced row."""
         if self.position_ids is None or self.input_ids.shape[0] > 1:
             raise ValueError("Cannot a batch that is not properly packed")
         L = self.input_ids.shape[1]
@@ -98,5 +110,7 @@ class PipelineBatchEncoding(BaseModel):
             fields.update(model_version=self.model_version, sentinel=self.sentinel, is_packed=self.is_packed,
                           padding=self.padding, seq_boundaries=self.seq_boundaries, pixel_values=self.pixel_values,
                           image_grid_thw=self.image_grid_thw)
+            if carry_boundary_target and b < L:
+                fields["boundary"] = {k: getattr(self, k)[:, b:b + 1] for k in _SLICED}
             out.append(PipelineBatchEncoding(**fields))
         return out

@@ -616,3 +616,42 @@ def test_row_chunked_backward_under_a_scratch_budget(save):
     per_row = -(-V // 256) * 512
     assert p0 > M * per_row                                      # un-chunked: the whole [rows x vocab] bf16 buffer existed
     assert p1 < (2 << 30) * (2 if save else 1) + 3 * V * H * 4 + (64 << 20), (p0, p1)   # chunked: <= budget per live buffer + dW temporaries
+
+
+def test_sp_slices_with_carried_boundary_targets_cover_the_unsliced_row():
+    """Opt-in beyond the reference: make_slices(n, carry_boundary_target=True).  PPO with 1/batch_size token weights is a plain
+    sum over target tokens, so the per-slice losses / token counts / gradients must add up to the un-sliced row's; without
+    the carry (the reference's behaviour, default) the n-1 boundary targets are missing."""
+    from pipelinerl_swe_b200 import PipelineBatchEncoding, RLConfig, rl_step
+    H, V, lens, n_slices = 128, 3000, [70, 41, 90, 55], 4
+    T = sum(lens)
+    batch = synthetic_packed_batch(lens, V, seed=5, n_prompt=3)
+    cfg = RLConfig(policy_loss="ppo", batch_size=4, kl_coef=0.1, final_kl_coef=0.1, entropy_bonus=0.01, final_entropy_bonus=0.01)
+    full = StubLM(H, V, T, seed=8).to(_dev())
+    loss_full, stats_full = rl_step(full, _to_dev(batch), 0, 1, cfg)
+    loss_full.backward()
+    pbe = PipelineBatchEncoding(**batch, model_version=0)
+    results = {}
+    for carry in (False, True):
+        tot_loss, tot_tokens, gw = 0.0, 0, torch.zeros(V, H, device=_dev())
+        gh = []
+        for k, sl in enumerate(pbe.make_slices(n_slices, carry_boundary_target=carry)):
+            a = k * T // n_slices
+            m = StubLM(H, V, T // n_slices, seed=8).to(_dev())
+            with torch.no_grad():
+                m.hidden.copy_(full.hidden[:, a:a + T // n_slices])
+            loss, stats = rl_step(m, sl.to_device(_dev()), 0, 1, cfg)
+            loss.backward()
+            tot_loss += loss.item()
+            tot_tokens += stats["num_output_tokens_sum"]
+            gw += m.lm_head.weight.grad.float()
+            gh.append(m.hidden.grad.float())
+        results[carry] = (tot_loss, tot_tokens, gw, torch.cat(gh, dim=1))
+    n_boundary_labelled = sum(int(batch["labels"][0, k * T // n_slices] != -100) for k in range(1, n_slices))
+    assert n_boundary_labelled > 0
+    assert results[False][1] == stats_full["num_output_tokens_sum"] - n_boundary_labelled      # the reference drops them
+    assert results[True][1] == stats_full["num_output_tokens_sum"]                              # the carry restores them
+    assert abs(results[True][0] - loss_full.item()) <= 1e-4 * abs(loss_full.item()) + 1e-6
+    assert abs(results[False][0] - loss_full.item()) > abs(results[True][0] - loss_full.item())
+    assert _rel(results[True][2], full.lm_head.weight.grad.float()) < 1e-2
+    assert _rel(results[True][3], full.hidden.grad.float()) < 1e-2

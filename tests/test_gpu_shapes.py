@@ -45,7 +45,7 @@ def _problem(name):
 def test_fast_reference_is_the_fp32_reference(name):
     """The chunked comparator (bf16 x bf16 products accumulated in fp32) equals plain fp32 matmul + log_softmax."""
     p = _problem(name)
-    assert sp.fast_reference_is_fp32(p["hidden"], p["weight"], p["targets"], p["inv_temp"]) < 2e-5
+    assert sp.fast_reference_is_fp32(p["hidden"], p["weight"], p["targets"], p["inv_temp"]) < 2e-4   # |logprob| ~ 12: 2e-5 relative, the summation-order noise of the plain fp32 matmul itself
 
 
 @pytest.mark.parametrize("mode", ["saved", "recompute"])

@@ -31,7 +31,7 @@ def test_library_exports_every_header_symbol():
     for n in names:
         assert hasattr(handle, n), f"libb200grpo.so does not export {n}"
     assert set(names) == set(_abi.SIGNATURES), set(names) ^ set(_abi.SIGNATURES)
-    assert _abi.lib().b200grpo_abi_version() == 2
+    assert _abi.lib().b200grpo_abi_version() == 3
 
 
 def test_struct_layouts_match_header():
@@ -132,13 +132,18 @@ def test_rlconfig_ignores_unknown_keys_like_reference():
 def test_rollout_scalars_host_side():
     from pipelinerl_swe_b200.advantage import rollout_scalars
     case = ADV["singleton_and_steps"]
-    reward, gkey, offsets, nlab, eos, n_groups, tok = rollout_scalars(copy.deepcopy(case["input"]), case["eos"])
+    reward, gkey, offsets, nlab, eos, n_groups, tok, order, starts = rollout_scalars(copy.deepcopy(case["input"]), case["eos"])
     rows = case["input"]
     assert offsets.tolist() == np.concatenate([[0], np.cumsum([len(r["input_ids"]) for r in rows])]).tolist()
     assert n_groups == len({f"{r['group_id']}_{r['step_index']}" for r in rows})
     assert nlab.tolist() == [sum(t != -100 for t in r["labels"]) for r in rows]
     assert eos.tolist() == [int(case["eos"] in r["input_ids"]) for r in rows]
     assert tok is None and reward.dtype == np.float64
+    # the CSR K4 walks: rows stably sorted by group key (dataset order inside a group), group g at order[starts[g]:starts[g+1]]
+    assert order.dtype == np.int32 and starts.dtype == np.int32 and starts[0] == 0 and starts[-1] == len(rows)
+    for g in range(n_groups):
+        members = order[starts[g]:starts[g + 1]].tolist()
+        assert members == [i for i in range(len(rows)) if gkey[i] == g] and members == sorted(members)
 
 
 def test_plan_buckets():
@@ -361,3 +366,28 @@ def test_staged_reference_reproduces_the_golden_vectors_and_the_oracle():
             assert abs(stats[k] - v) <= 1e-5 * abs(v) + 1e-6, (name, k)
         o_loss, _ = oracle.oracle_rl_step(x["hidden"].float(), x["weight"].float(), batch, meta["step"], meta["max_step"], ocfg)
         assert abs(float(o_loss) - float(loss)) <= 1e-5 * abs(float(loss)) + 1e-6
+
+
+def test_make_slices_can_carry_the_boundary_target():
+    """Default = the reference's cuts (types.py:144-178).  carry_boundary_target=True attaches the next slice's first token to
+    every slice but the last, so that the slices together hold every (position, next token) pair of the un-sliced row."""
+    from pipelinerl_swe_b200 import PipelineBatchEncoding
+    from helpers import synthetic_packed_batch
+    b = synthetic_packed_batch([10, 14, 8], 50, seed=1)
+    pbe = PipelineBatchEncoding(**b, model_version=0)
+    plain = pbe.make_slices(4)
+    carried = pbe.make_slices(4, carry_boundary_target=True)
+    assert all(s.boundary is None for s in plain) and carried[-1].boundary is None
+    pairs = []
+    for k, s in enumerate(carried):
+        assert torch.equal(s.input_ids, plain[k].input_ids) and s.input_ids.shape == (1, 8)     # the cuts themselves do not move
+        ids = s.input_ids[0].tolist()
+        pairs += list(zip(ids[:-1], ids[1:]))
+        if s.boundary is not None:
+            assert set(s.boundary) >= {"input_ids", "labels", "rewards", "advantages", "old_logprobs", "ref_logprobs", "position_ids"}
+            assert all(v.shape == (1, 1) for v in s.boundary.values())
+            assert s.boundary["input_ids"][0, 0] == carried[k + 1].input_ids[0, 0]
+            assert s.boundary["old_logprobs"][0, 0] == carried[k + 1].old_logprobs[0, 0]
+            pairs.append((ids[-1], int(s.boundary["input_ids"][0, 0])))
+    full = pbe.input_ids[0].tolist()
+    assert pairs == list(zip(full[:-1], full[1:]))

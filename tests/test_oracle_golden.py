@@ -47,10 +47,24 @@ def test_populate_rl_data_matches_reference(name):
         assert got["num_labels"] == want["num_labels"]
         assert got["overflow"] == want["overflow"]
         assert got["group_tokens"] == want["group_tokens"]
-        # fp64 mean/std may differ from pandas in the last ulp; fp32 view must agree
-        g = torch.tensor(got["advantages"], dtype=torch.float32)
-        w = torch.tensor(want["advantages"], dtype=torch.float32)
-        torch.testing.assert_close(g, w, rtol=2e-7, atol=1e-9)
+        assert got["advantages"] == want["advantages"]          # f64 Python floats, bit-identical to the pandas path
+
+
+def test_group_statistics_are_pandas_bit_for_bit():
+    """pandas_group_mean / pandas_group_std (the restated third-party algorithm) against pandas itself: random group
+    sizes and magnitudes, 0/1 rewards, singleton groups -- exact f64 equality, NaN for one sample."""
+    import numpy as np
+    pd = pytest.importorskip("pandas")
+    rng = np.random.default_rng(0)
+    for trial in range(300):
+        n = int(rng.integers(1, 40))
+        vals = (rng.normal(size=n) * 10.0 ** rng.integers(-3, 4) if trial % 3 == 0 else
+                rng.integers(0, 2, size=n).astype(float) if trial % 3 == 1 else rng.random(n))
+        r = pd.DataFrame({"g": ["a"] * n, "v": vals}).groupby("g").agg(m=("v", "mean"), s=("v", "std"))
+        m, s = float(r["m"].iloc[0]), float(r["s"].iloc[0])
+        assert oracle.grpo_oracle.pandas_group_mean(vals.tolist()) == m
+        got = oracle.grpo_oracle.pandas_group_std(vals.tolist())
+        assert got == s or (np.isnan(got) and np.isnan(s))
 
 
 def test_collate_packed_matches_reference():

@@ -90,7 +90,7 @@ def main():
     for T in (1 << 20, 1 << 24) if want("segments") else ():
         pos = (torch.arange(T, device=dev) % 977).contiguous()
         ms = timed(lambda: ops.segment_bounds(pos))
-        emit("segment_bounds", f"T={T}", 8 * T * 2, ms, "position_ids read twice (count pass + scatter pass)")
+        emit("segment_bounds", f"T={T}", 8 * T, ms, "position_ids read once (flags kept as per-block counts + a 1-bit mask)")
     # ---- K4 group advantages: 16 B/token out ------------------------------------------------------------------
     for n_rows, n_tok in ((4096, 2048), (65536, 512)) if want("k4") else ():
         reward = torch.rand(n_rows, device=dev, dtype=torch.float64, generator=g)
@@ -98,8 +98,12 @@ def main():
         offs = (torch.arange(n_rows + 1, device=dev, dtype=torch.int64) * n_tok).contiguous()
         nlab = torch.full((n_rows,), n_tok - 8, device=dev, dtype=torch.int32)
         eos = torch.ones(n_rows, device=dev, dtype=torch.uint8)
-        ms = timed(lambda: ops.group_advantage(reward, gkey, offs, nlab, eos, n_rows // 16, True))
-        emit("group_advantage (K4)", f"rollouts={n_rows} x {n_tok} tokens", 16 * n_rows * n_tok + 17 * n_rows, ms)
+        order, starts = ops.group_order(gkey, n_rows // 16)
+        ms = timed(lambda: ops.group_advantage(reward, gkey, offs, nlab, eos, n_rows // 16, True, None, order, starts))
+        emit("group_advantage (K4: stats + per-token expand)", f"rollouts={n_rows} x {n_tok} tokens", 16 * n_rows * n_tok + 25 * n_rows, ms)
+        ms = timed(lambda: ops.group_advantage_rows(reward, gkey, offs, n_rows // 16, True, order, starts))
+        emit("group_advantage_rows (K4: stats + per-rollout f64)", f"rollouts={n_rows}", 41 * n_rows, ms,
+             "launch-bound: 25 B/rollout in (reward, key, order, two offsets), 16 B/rollout out")
     # ---- packed ingest expansion: 16 B/token in, 60 B/token out -------------------------------------------------
     for n_seq, n_tok in ((16, 512), (2048, 512)) if want("ingest") else ():
         ex = synthetic_rollout_examples([n_tok] * n_seq, 152064, seed=2)
