@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--no-parity", action="store_true", help="skip the pre-run parity gate at the benchmarked shape")
     ap.add_argument("--no-recompute", action="store_true", help="skip the recompute-mode sub-record")
     ap.add_argument("--no-vocab-record", action="store_true", help="N>1: skip the config-4 vocab-parallel sub-record")
+    ap.add_argument("--no-weight-record", action="store_true", help="N>1: skip the config-5 weight-broadcast sub-record")
     ap.add_argument("--cpu-budget-s", type=float, default=0.0, help="wall-clock budget of the CPU arm (0 = auto)")
     ap.add_argument("--exchange", default="symm", choices=["nccl", "symm"],
                     help="vocab-parallel transport: NCCL, or this library's NVSwitch multicast kernels (SymmetricExchange)")
@@ -714,6 +715,31 @@ def vocab_parallel_record(args, dev, rank, world, tm: Timer, peaks) -> dict:
     return rec
 
 
+def weight_broadcast_record(dev, rank, world) -> dict:
+    """N>1: BASELINE config 5 -- Qwen2.5-7B bf16 parameters (15.2 GB, 339 tensors) from trainer rank 0 to the N-1 other GPUs
+    (the receive_weight_update path, vllm1.py:81-94): the reference's per-parameter loop, the bucketed NCCL path and the
+    scatter + relay kernels, every variant byte-checked on every receiver (tools/bench_weight_update.py has the full sweep)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from bench_weight_update import run_sweep
+    try:
+        lines = run_sweep(dev, rank, world, buckets_mb=(16, 256), multicast_mb=(), scatter_mb=(64,), iters=2)
+    except Exception as e:  # noqa: BLE001  -- a side record must never take the bench line down
+        return {"unavailable": repr(e)[:300]}
+    rec = {"workload": "C5: Qwen2.5-7B bf16 parameters, 339 tensors, trainer rank 0 -> %d receivers" % (world - 1), "unit": "GB/s",
+           "nvlink_egress_peak_GBps": 900.0, "variants": {}}
+    for ln in lines:
+        rec["variants"][ln["variant"]] = {k: ln[k] for k in ("value", "ms", "byte_exact", "n_broadcasts", "n_transfers", "unavailable") if k in ln}
+    ok = [v for v in rec["variants"].values() if v.get("byte_exact")]
+    if ok:
+        best = max(ok, key=lambda v: v["value"])
+        rec["best"] = {"variant": [k for k, v in rec["variants"].items() if v is best][0], "value": best["value"],
+                       "frac_of_nvlink_egress": best["value"] / 900.0}
+        ref = rec["variants"].get("reference_per_parameter")
+        if ref and ref.get("value"):
+            rec["best"]["speedup_vs_reference_loop"] = best["value"] / ref["value"]
+    return rec
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -726,7 +752,8 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep rank 0's stdout to the one JSON line
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("WARN", "VERSION"):
+            del os.environ["NCCL_DEBUG"]   # those levels print NCCL's version banner on stdout: rank 0's stdout is the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     for kv in args.tunable:
         name, val = kv.split("=")
@@ -865,6 +892,14 @@ def run_b200(args):
         torch.cuda.empty_cache()
         vp = vocab_parallel_record(args, dev, rank, world, tm, peaks)
         wl = None
+    wb = None
+    if world > 1 and not args.no_weight_record and args.parallelism == "dp":
+        if wl is not None:
+            config_desc = wl.desc
+            del wl
+            wl = None
+        torch.cuda.empty_cache()
+        wb = weight_broadcast_record(dev, rank, world)
 
     if rank == 0:
         is_vp = wl.vocab_parallel if wl is not None else False
@@ -885,7 +920,7 @@ def run_b200(args):
                        "tunables": args.tunable, "tokens_per_gpu_per_sec": value / world if not is_vp else value},
             "parity": parity, "roofline": roofline, ("recompute" if args.mode == "saved" else "saved"): other,
             "cpu_baseline": cpu, "torch_gpu_baseline": torch_gpu, "rl_step_api": api, "e2e": e2e,
-            "vocab_parallel": vp, "gpu_launches": int(round(launches_per_step * K)),
+            "vocab_parallel": vp, "weight_broadcast": wb, "gpu_launches": int(round(launches_per_step * K)),
             "gpu_launches_per_step": launches_per_step, "clocks": clocks.summary(),
         }
         print(json.dumps(line), flush=True)

@@ -244,6 +244,24 @@ int b200grpo_bucket_pack_multicast(const void* const* src_ptrs_host, const int64
                                    void* bucket_multicast_bf16, int64_t bucket_capacity, void* workspace,
                                    size_t workspace_bytes, void* stream);
 
+/* Scatter + relay: a 1 -> N broadcast at the line rate of one copy.  The bucket is cut into stripes of stripe_elems bf16
+ * elements (a multiple of 8).  b200grpo_bucket_pack_scatter (sender) packs like b200grpo_bucket_pack but stores stripe j
+ * into peer_buckets_host[j % n_peers] + offset -- device pointers to the receivers' copies of a symmetric slot, P2P
+ * mapped (plain st.global over NVLink; no staging buffer on the sender).  After a barrier every receiver calls
+ * b200grpo_bucket_relay_multicast: it re-emits the stripes it owns (j % n_peers == peer_index) from its local copy to
+ * the NVSwitch multicast address of the slot (multimem.st), which completes every other copy.  After a second barrier
+ * each receiver holds the whole bucket.  Sender egress = receiver ingress = one payload, for any N.
+ * Replaces the same per-parameter broadcast loop (finetune_loop.py:236-248, vllm1.py:81-94). */
+size_t b200grpo_bucket_scatter_workspace(int n_tensors, int n_peers);
+int b200grpo_bucket_pack_scatter(const void* const* src_ptrs_host, const int64_t* numel_host,
+                                 const uint8_t* src_is_f32_host, int n_tensors,
+                                 void* const* peer_buckets_host, int n_peers, int64_t stripe_elems,
+                                 int64_t bucket_capacity, void* workspace, size_t workspace_bytes,
+                                 void* stream);
+int b200grpo_bucket_relay_multicast(const void* local_bucket, void* bucket_multicast, int64_t numel,
+                                    int peer_index, int n_peers, int64_t stripe_elems, int ctas,
+                                    void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Host-buffer entry point (the end-to-end call): one GRPO logprob+loss forward/backward
  * over a packed row whose inputs live in PINNED HOST memory.  Copies inputs to the device

@@ -10,6 +10,14 @@
 // symmetric buffer that every rank of the update group owns, and the pack stores with multimem.st -- ONE kernel
 // reads the parameters once and the switch delivers the bf16 bytes into every receiver's copy: pack and
 // broadcast are the same pass, the sender's NVLink egress carries the payload once whatever the group size.
+//
+// Scatter + relay (b200grpo_bucket_pack_scatter / b200grpo_bucket_relay_multicast): the design that lets a 1 -> N broadcast
+// run at the line rate of ONE copy whatever N is.  The bucket is cut into stripes; the sender's pack kernel stores stripe j
+// straight into receiver (j mod N)'s copy of the symmetric slot over P2P NVLink stores (egress: the payload once, spread
+// over N peers -- no staging buffer on the sender at all), then every receiver re-emits the stripes it owns with
+// multimem.st, the switch replicating them into all other copies (egress per receiver: payload / N; ingress: the payload
+// once).  Sender egress and receiver ingress are both exactly one payload, and the two phases of consecutive transfers
+// overlap (two slots).
 #include "common.cuh"
 #include <vector>
 
@@ -79,6 +87,74 @@ __global__ void __launch_bounds__(BK_THREADS) bucket_multicast_kernel(const Buck
   __threadfence_system();  // the stores are performed at every peer before the grid is reported complete
 }
 
+// Scatter pack: like the multicast pack, but each 16-byte vector goes to exactly ONE peer -- the owner of its stripe --
+// with a plain st.global through the peer's P2P mapping.  peers[q] = base of peer q's copy of the slot.
+__global__ void __launch_bounds__(BK_THREADS) bucket_scatter_kernel(const BucketEntry* __restrict__ tab, int n, int64_t total_chunks,
+                                                                    __nv_bfloat16* const* __restrict__ peers, int n_peers,
+                                                                    int64_t stripe_elems) {
+  for (int64_t chunk = blockIdx.x; chunk < total_chunks; chunk += gridDim.x) {
+    const BucketEntry e = tab[find_entry(tab, n, chunk)];
+    const int64_t begin = (chunk - e.chunk_start) * BK_CHUNK;
+    const int64_t end = min(begin + (int64_t)BK_CHUNK, e.numel);
+    const bool vec_ok = ((uintptr_t)e.ptr & 15) == 0;
+    for (int64_t i = begin + threadIdx.x * 8LL; i < end; i += BK_THREADS * 8LL) {
+      uint4 out;
+      if (i + 8 <= end && vec_ok) {
+        if (!e.is_f32) {
+          out = __ldg((const uint4*)((const __nv_bfloat16*)e.ptr + i));
+        } else {
+          const float* p = (const float*)e.ptr;
+          const float4 x = __ldg((const float4*)(p + i)), y = __ldg((const float4*)(p + i + 4));
+          __nv_bfloat162 o[4] = {__floats2bfloat162_rn(x.x, x.y), __floats2bfloat162_rn(x.z, x.w),
+                                 __floats2bfloat162_rn(y.x, y.y), __floats2bfloat162_rn(y.z, y.w)};
+          out = *(uint4*)o;
+        }
+      } else {  // unaligned source or the last partial vector of the tensor (zero-padded to the 16-byte boundary)
+        __nv_bfloat16 o[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int64_t j = i + k;
+          o[k] = j < end ? (e.is_f32 ? __float2bfloat16_rn(((const float*)e.ptr)[j]) : ((const __nv_bfloat16*)e.ptr)[j])
+                         : __float2bfloat16_rn(0.f);
+        }
+        out = *(uint4*)o;
+      }
+      const int64_t off = e.bucket_off + i;                       // multiple of 8; stripes are multiples of 8 elements
+      __nv_bfloat16* dst = peers[(off / stripe_elems) % n_peers];
+      *(uint4*)(dst + off) = out;
+    }
+  }
+  __threadfence_system();  // the stores are performed at every peer before the grid is reported complete
+}
+
+// Relay: this receiver re-emits the stripes it owns (stripe j with j % n_peers == peer_index) from its local copy of the
+// slot to the multicast mapping of the same slot.  16 B per thread per trip, four loads in flight.
+constexpr int RL_UNROLL = 4;
+__global__ void __launch_bounds__(BK_THREADS) bucket_relay_kernel(const uint4* local, uint4* mc, int64_t n_vec,
+                                                                  int peer_index, int n_peers, int64_t stripe_vec) {
+  // enumerate only the owned vectors: owned index o -> stripe (o / stripe_vec) * n_peers + peer_index
+  const int64_t n_stripes = (n_vec + stripe_vec - 1) / stripe_vec;
+  const int64_t owned_stripes = n_stripes > peer_index ? (n_stripes - peer_index + n_peers - 1) / n_peers : 0;
+  const int64_t n_owned = owned_stripes * stripe_vec;
+  const int64_t stride = (int64_t)gridDim.x * BK_THREADS;
+  for (int64_t o = (int64_t)blockIdx.x * BK_THREADS + threadIdx.x; o < n_owned; o += stride * RL_UNROLL) {
+    uint4 v[RL_UNROLL];
+    int64_t idx[RL_UNROLL];
+#pragma unroll
+    for (int u = 0; u < RL_UNROLL; ++u) {
+      const int64_t oo = o + u * stride;
+      const int64_t st = oo / stripe_vec;
+      idx[u] = (st * n_peers + peer_index) * stripe_vec + (oo - st * stripe_vec);
+      if (oo >= n_owned || idx[u] >= n_vec) idx[u] = -1;
+      else v[u] = local[idx[u]];
+    }
+#pragma unroll
+    for (int u = 0; u < RL_UNROLL; ++u)
+      if (idx[u] >= 0) multimem_st_16(mc + idx[u], v[u]);
+  }
+  __threadfence_system();
+}
+
 template <bool PACK>
 __global__ void __launch_bounds__(BK_THREADS) bucket_kernel(const BucketEntry* __restrict__ tab, int n,
                                                             int64_t total_chunks, __nv_bfloat16* bucket) {
@@ -124,13 +200,18 @@ __global__ void __launch_bounds__(BK_THREADS) bucket_kernel(const BucketEntry* _
 }
 
 static int run_bucket(int mode, void* const* ptrs, const int64_t* numel, const uint8_t* is_f32, int n, void* bucket,
-                      int64_t capacity, void* workspace, size_t workspace_bytes, void* stream) {
+                      int64_t capacity, void* workspace, size_t workspace_bytes, void* stream, void* const* peers = nullptr,
+                      int n_peers = 0, int64_t stripe_elems = 0) {
   if (int e = check_device_sm100()) return e;
   B200_REQUIRE(n >= 0, "bucket: n_tensors < 0");
   if (n == 0) return B200GRPO_OK;
-  B200_REQUIRE(ptrs && numel && bucket && workspace, "bucket: null pointer");
+  B200_REQUIRE(ptrs && numel && (bucket || mode == 3) && workspace, "bucket: null pointer");
   B200_REQUIRE(((uintptr_t)bucket & 15) == 0, "bucket: bucket must be 16-byte aligned");
-  if (workspace_bytes < b200grpo_bucket_workspace(n)) { set_error("bucket: workspace too small"); return B200GRPO_EWORKSPACE; }
+  const size_t tab_bytes = b200grpo_bucket_workspace(n);
+  if (workspace_bytes < tab_bytes + (mode == 3 ? align_up(sizeof(void*) * (size_t)n_peers, 256) : 0)) {
+    set_error("bucket: workspace too small");
+    return B200GRPO_EWORKSPACE;
+  }
   std::vector<BucketEntry> tab(n);
   int64_t off = 0, chunks = 0;
   for (int i = 0; i < n; ++i) {
@@ -143,12 +224,15 @@ static int run_bucket(int mode, void* const* ptrs, const int64_t* numel, const u
   if (chunks == 0) return B200GRPO_OK;
   cudaStream_t st = (cudaStream_t)stream;
   B200_CUDA_OK(cudaMemcpyAsync(workspace, tab.data(), sizeof(BucketEntry) * n, cudaMemcpyHostToDevice, st));
+  __nv_bfloat16** peers_dev = (__nv_bfloat16**)((char*)workspace + tab_bytes);
+  if (mode == 3) B200_CUDA_OK(cudaMemcpyAsync(peers_dev, peers, sizeof(void*) * n_peers, cudaMemcpyHostToDevice, st));
   int64_t grid = chunks;
   const int64_t cap = (int64_t)sm_count() * 8;
   if (grid > cap) grid = cap;
   ProfScope ps(PROF_BUCKET, st);
   count_launch();
-  if (mode == 2) bucket_multicast_kernel<<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
+  if (mode == 3) bucket_scatter_kernel<<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, peers_dev, n_peers, stripe_elems);
+  else if (mode == 2) bucket_multicast_kernel<<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
   else if (mode == 1) bucket_kernel<true><<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
   else bucket_kernel<false><<<(int)grid, BK_THREADS, 0, st>>>((const BucketEntry*)workspace, n, chunks, (__nv_bfloat16*)bucket);
   B200_CUDA_OK(cudaGetLastError());
@@ -188,4 +272,43 @@ extern "C" int b200grpo_bucket_pack_multicast(const void* const* src_ptrs_host, 
                                               int64_t bucket_capacity, void* workspace, size_t workspace_bytes, void* stream) {
   return run_bucket(2, (void* const*)src_ptrs_host, numel_host, src_is_f32_host, n_tensors, bucket_multicast_bf16,
                     bucket_capacity, workspace, workspace_bytes, stream);
+}
+
+extern "C" size_t b200grpo_bucket_scatter_workspace(int n_tensors, int n_peers) {
+  return b200grpo_bucket_workspace(n_tensors) + align_up(sizeof(void*) * (size_t)(n_peers > 0 ? n_peers : 1), 256);
+}
+
+extern "C" int b200grpo_bucket_pack_scatter(const void* const* src_ptrs_host, const int64_t* numel_host,
+                                            const uint8_t* src_is_f32_host, int n_tensors, void* const* peer_buckets_host,
+                                            int n_peers, int64_t stripe_elems, int64_t bucket_capacity, void* workspace,
+                                            size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(peer_buckets_host && n_peers >= 1 && n_peers <= 64, "bucket_pack_scatter: n_peers=%d", n_peers);
+  B200_REQUIRE(stripe_elems >= 8 && stripe_elems % 8 == 0, "bucket_pack_scatter: stripe must be a multiple of 8 elements");
+  for (int q = 0; q < n_peers; ++q)
+    B200_REQUIRE(peer_buckets_host[q] && ((uintptr_t)peer_buckets_host[q] & 15) == 0, "bucket_pack_scatter: peer %d pointer", q);
+  return run_bucket(3, (void* const*)src_ptrs_host, numel_host, src_is_f32_host, n_tensors, nullptr, bucket_capacity, workspace,
+                    workspace_bytes, stream, peer_buckets_host, n_peers, stripe_elems);
+}
+
+extern "C" int b200grpo_bucket_relay_multicast(const void* local_bucket, void* bucket_multicast, int64_t numel, int peer_index,
+                                               int n_peers, int64_t stripe_elems, int ctas, void* stream) {
+  if (int e = check_device_sm100()) return e;
+  B200_REQUIRE(local_bucket && bucket_multicast && (((uintptr_t)local_bucket | (uintptr_t)bucket_multicast) & 15) == 0,
+               "bucket_relay: 16-byte aligned pointers");
+  B200_REQUIRE(numel >= 0 && numel % 8 == 0 && stripe_elems >= 8 && stripe_elems % 8 == 0, "bucket_relay: numel / stripe %% 8");
+  B200_REQUIRE(n_peers >= 1 && peer_index >= 0 && peer_index < n_peers, "bucket_relay: peer %d of %d", peer_index, n_peers);
+  if (numel == 0) return B200GRPO_OK;
+  const int64_t n_vec = numel / 8, stripe_vec = stripe_elems / 8;
+  const int64_t own = (n_vec / n_peers) + stripe_vec;
+  int64_t grid = (own + (int64_t)BK_THREADS * RL_UNROLL - 1) / ((int64_t)BK_THREADS * RL_UNROLL);
+  const int64_t cap = ctas > 0 ? ctas : (int64_t)sm_count() * 4;
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  ProfScope ps(PROF_BUCKET, st);
+  count_launch();
+  bucket_relay_kernel<<<(int)grid, BK_THREADS, 0, st>>>((const uint4*)local_bucket, (uint4*)bucket_multicast, n_vec, peer_index,
+                                                        n_peers, stripe_vec);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200GRPO_OK;
 }

@@ -262,6 +262,25 @@ def bucket_pack_multicast(tensors: Sequence[torch.Tensor], mc_ptr: int, capacity
     check(lib().b200grpo_bucket_pack_multicast(ptrs, numel, is_f32, n, C.c_void_p(mc_ptr), int(capacity), ws.data_ptr(), ws.numel(), _stream()))
 
 
+def bucket_pack_scatter(tensors: Sequence[torch.Tensor], peer_ptrs: Sequence[int], stripe_elems: int, capacity: int) -> None:
+    """K6 + scatter in one pass: stripe j of the packed bucket is stored into ``peer_ptrs[j % len(peer_ptrs)]`` (device
+    pointers to the receivers' copies of a symmetric slot, P2P-mapped) -- the first half of the scatter + relay broadcast."""
+    ptrs, numel, is_f32 = _tensor_table(tensors)
+    n, q = len(tensors), len(peer_ptrs)
+    peers = (C.c_void_p * q)(*[int(p) for p in peer_ptrs])
+    ws = _workspace(tensors[0].device, lib().b200grpo_bucket_scatter_workspace(n, q), "bucket")
+    check(lib().b200grpo_bucket_pack_scatter(ptrs, numel, is_f32, n, peers, q, int(stripe_elems), int(capacity), ws.data_ptr(),
+                                             ws.numel(), _stream()))
+
+
+def bucket_relay_multicast(local_ptr: int, mc_ptr: int, numel: int, peer_index: int, n_peers: int, stripe_elems: int,
+                           ctas: int = 0) -> None:
+    """Second half of scatter + relay: re-emit the stripes this receiver owns from its local copy through the NVSwitch
+    multicast address of the slot (multimem.st), completing every other rank's copy."""
+    check(lib().b200grpo_bucket_relay_multicast(C.c_void_p(local_ptr), C.c_void_p(mc_ptr), int(numel), int(peer_index), int(n_peers),
+                                                int(stripe_elems), int(ctas), _stream()))
+
+
 def bucket_unpack(bucket: torch.Tensor, tensors: Sequence[torch.Tensor]) -> None:
     """K6 inverse: scatter a received bucket into the destination parameters."""
     _req(bucket, torch.bfloat16, "bucket")

@@ -597,7 +597,7 @@ def test_row_chunked_backward_under_a_scratch_budget(save):
         for budget in (64 << 30, 2 << 30):
             LH.set_saved_logits_budget(budget)
             n_chunks = len(LH.row_chunks(M, V))
-            assert n_chunks == (1 if budget > (8 << 30) else 3)
+            assert (n_chunks == 1) if budget > (8 << 30) else (n_chunks == 4)   # 2 GiB / 304128 B per row -> 6656-row chunks
             ops._ws_cache.clear()
             torch.cuda.empty_cache()
             torch.cuda.reset_peak_memory_stats(d)

@@ -90,3 +90,20 @@ def test_vocab_parallel_two_gpus_equals_unsharded(transport):
         cmd.append("--exchange=symm")
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "VOCAB_PARALLEL" in out.stdout and " OK " in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+@pytest.mark.gpu
+def test_weight_update_call_shapes_and_transports_two_gpus():
+    """tools/check_weight_update.py under torchrun on 2 GPUs (skipped on a 1-GPU box): a second NCCL world built by
+    init_actor_update_group, WeightUpdateSender.send_weight_update(version) -> ActorUpdateWorker.receive_weight_update(request)
+    over the reference loop, the bucketed NCCL path (fp32 masters, an odd-sized fp32 'direct' tensor, a ZeRO-3 stand-in) and
+    the scatter + relay kernels; every received tensor bit-equal to param.data.bfloat16()."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29561", os.path.join(root, "tools", "check_weight_update.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "WEIGHT_UPDATE" in out.stdout and " OK " in out.stdout, out.stdout[-2000:] + out.stderr[-3000:]

@@ -98,6 +98,88 @@ def _weight_update_worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
+def _second_world_worker(rank, world, port, q):
+    """A second process group beside the default one (torch_utils.py:16-65) carrying the reference-shaped update calls:
+    WeightUpdateSender.send_weight_update(version) on rank 0 with a ZeRO-3 stand-in (parameters whole only inside gather),
+    ActorUpdateWorker.init_actor_update_group / receive_weight_update(request) on rank 1 (vllm1.py:52-94)."""
+    import contextlib
+    import types
+    _init(rank, world, port)                      # the process's OWN default world
+    from pipelinerl_swe_b200 import weight_update as wu
+    init_method = f"tcp://127.0.0.1:{port + 1}"
+    g = torch.Generator().manual_seed(2)
+    full = {"a.weight": torch.randn(33, 17, generator=g), "a.bias": torch.randn(17, generator=g).bfloat16(),
+            "b.weight": torch.randn(5, 3, generator=g)}
+    ok = True
+    got = {}
+    if rank != 0:   # the workers join the update group at start-up (vllm1.py:52-79), long before the first update
+        class Worker(wu.ActorUpdateWorker):
+            weight_update_transport = "reference"
+
+            def __init__(self):
+                self.rank, self.device = rank - 1, torch.device("cpu")
+                self.model_config = types.SimpleNamespace(dtype=torch.bfloat16)
+                self.model_runner = types.SimpleNamespace(model=types.SimpleNamespace(
+                    load_weights=lambda weights: [got.__setitem__(n, t.clone()) or n for n, t in weights]))
+
+        w = Worker()
+        orig = wu.init_actor_update_group
+        wu.init_actor_update_group = lambda *a, **k: orig(*a, **{**k, "backend": "gloo"})   # the worker mixin asks for NCCL
+        try:
+            w.init_actor_update_group(0, world - 1, init_method, world)
+        finally:
+            wu.init_actor_update_group = orig
+        ok = ok and w.pg_rank == rank
+    if rank == 0:
+        group = wu.init_actor_update_group(init_method, 0, world, backend="gloo")
+        ok = ok and dist.get_world_size(group) == world and group is not dist.group.WORLD
+
+        class Model(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.ps = [(n, torch.nn.Parameter(t.clone(), requires_grad=False)) for n, t in full.items()]
+
+            def named_parameters(self, *a, **k):
+                return self.ps
+
+        model = Model()
+        for _, p in model.ps:                     # sharded outside gather(): half the elements, full shape in ds_shape
+            p.ds_shape, p._full = p.shape, p.data
+            p.data = p.data.reshape(-1)[: p.numel() // 2].clone()
+        entered = []
+
+        @contextlib.contextmanager
+        def gather(params):
+            entered.append(len(params))
+            shards = [p.data for p in params]
+            for p in params:
+                p.data = p._full
+            try:
+                yield
+            finally:
+                for p, sh in zip(params, shards):
+                    p.data = sh
+
+        published = []
+
+        def publish(req):     # the HTTP POST of finetune_loop.py:160-172, here over the default world; precedes the data
+            published.append(req)
+            dist.broadcast_object_list([req], src=0)
+            return []
+
+        sender = wu.WeightUpdateSender(model, group, publish=publish, transport="reference", gather=gather)
+        req = sender.send_weight_update(version=11)
+        ok = ok and published == [req] and req.version == 11 and [i.shape for i in req.parameters_info] == [[33, 17], [17], [5, 3]]
+        ok = ok and entered == [1, 1, 1] and all(p.data.numel() == p._full.numel() // 2 for _, p in model.ps)   # re-sharded after
+    else:
+        box = [None]
+        dist.broadcast_object_list(box, src=0)
+        w.receive_weight_update(box[0])
+        ok = ok and set(got) == set(full) and all(torch.equal(got[n].view(torch.int16), full[n].bfloat16().view(torch.int16)) for n in full)
+    q.put((rank, ok, sorted(got)))
+    dist.destroy_process_group()
+
+
 def _fake_micro_batch_stats(rank, i, keys):
     """One micro-batch's stats dict as rl_step would return it (values are arbitrary but rank/step specific)."""
     g = torch.Generator().manual_seed(1000 * rank + i)
@@ -197,6 +279,11 @@ def test_weight_update_plan_world2():
     res = _run(_weight_update_worker)
     assert all(ok for _, ok, _ in res)
     assert res[0][2] == res[1][2]
+
+
+def test_second_process_group_and_reference_shaped_update_calls_world2():
+    res = _run(_second_world_worker)
+    assert res[1][2] == ["a.bias", "a.weight", "b.weight"]
 
 
 def test_step_metrics_reduce_world2():
