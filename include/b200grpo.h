@@ -261,6 +261,10 @@ int b200grpo_bucket_pack_scatter(const void* const* src_ptrs_host, const int64_t
 int b200grpo_bucket_relay_multicast(const void* local_bucket, void* bucket_multicast, int64_t numel,
                                     int peer_index, int n_peers, int64_t stripe_elems, int ctas,
                                     void* stream);
+/* The same relay over plain P2P stores (no multicast mapping needed): the owned stripes are written into every other
+ * receiver's copy, peer_buckets_host[q] (q != peer_index), n_peers <= 16. */
+int b200grpo_bucket_relay_p2p(const void* local_bucket, void* const* peer_buckets_host, int64_t numel,
+                              int peer_index, int n_peers, int64_t stripe_elems, int ctas, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Host-buffer entry point (the end-to-end call): one GRPO logprob+loss forward/backward

@@ -89,6 +89,7 @@ SIGNATURES = {
     "b200grpo_bucket_scatter_workspace": (_sz, [_i, _i]),
     "b200grpo_bucket_pack_scatter": (_i, [_p, _p, _p, _i, _p, _i, _i64, _i64, _p, _sz, _p]),
     "b200grpo_bucket_relay_multicast": (_i, [_p, _p, _i64, _i, _i, _i64, _i, _p]),
+    "b200grpo_bucket_relay_p2p": (_i, [_p, _p, _i64, _i, _i, _i64, _i, _p]),
     "b200grpo_bucket_unpack": (_i, [_p, _p, _p, _p, _i, _p, _sz, _p]),
     "b200grpo_rl_step_host_workspace": (_sz, [_i, _i, _i]),
     "b200grpo_rl_step_host_grad_hidden": (_p, [_p, _i, _i, _i]),

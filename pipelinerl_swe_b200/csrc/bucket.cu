@@ -155,6 +155,37 @@ __global__ void __launch_bounds__(BK_THREADS) bucket_relay_kernel(const uint4* l
   __threadfence_system();
 }
 
+// Relay over plain P2P stores instead of the multicast mapping: the owned stripes go to every OTHER receiver's copy with
+// st.global (egress per receiver: payload * (N-1)/N).  Same enumeration as bucket_relay_kernel.
+constexpr int RL_MAX_PEERS = 16;
+struct RelayPeers { uint4* p[RL_MAX_PEERS]; };
+__global__ void __launch_bounds__(BK_THREADS) bucket_relay_p2p_kernel(const uint4* local, const RelayPeers peers, int64_t n_vec,
+                                                                      int peer_index, int n_peers, int64_t stripe_vec) {
+  const int64_t n_stripes = (n_vec + stripe_vec - 1) / stripe_vec;
+  const int64_t owned_stripes = n_stripes > peer_index ? (n_stripes - peer_index + n_peers - 1) / n_peers : 0;
+  const int64_t n_owned = owned_stripes * stripe_vec;
+  const int64_t stride = (int64_t)gridDim.x * BK_THREADS;
+  for (int64_t o = (int64_t)blockIdx.x * BK_THREADS + threadIdx.x; o < n_owned; o += stride * RL_UNROLL) {
+    uint4 v[RL_UNROLL];
+    int64_t idx[RL_UNROLL];
+#pragma unroll
+    for (int u = 0; u < RL_UNROLL; ++u) {
+      const int64_t oo = o + u * stride;
+      const int64_t st = oo / stripe_vec;
+      idx[u] = (st * n_peers + peer_index) * stripe_vec + (oo - st * stripe_vec);
+      if (oo >= n_owned || idx[u] >= n_vec) idx[u] = -1;
+      else v[u] = local[idx[u]];
+    }
+    for (int q = 0; q < n_peers; ++q) {
+      if (q == peer_index) continue;
+#pragma unroll
+      for (int u = 0; u < RL_UNROLL; ++u)
+        if (idx[u] >= 0) peers.p[q][idx[u]] = v[u];
+    }
+  }
+  __threadfence_system();
+}
+
 template <bool PACK>
 __global__ void __launch_bounds__(BK_THREADS) bucket_kernel(const BucketEntry* __restrict__ tab, int n,
                                                             int64_t total_chunks, __nv_bfloat16* bucket) {
@@ -309,6 +340,32 @@ extern "C" int b200grpo_bucket_relay_multicast(const void* local_bucket, void* b
   count_launch();
   bucket_relay_kernel<<<(int)grid, BK_THREADS, 0, st>>>((const uint4*)local_bucket, (uint4*)bucket_multicast, n_vec, peer_index,
                                                         n_peers, stripe_vec);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200GRPO_OK;
+}
+
+extern "C" int b200grpo_bucket_relay_p2p(const void* local_bucket, void* const* peer_buckets_host, int64_t numel, int peer_index,
+                                         int n_peers, int64_t stripe_elems, int ctas, void* stream) {
+  if (int e = check_device_sm100()) return e;
+  B200_REQUIRE(local_bucket && peer_buckets_host && ((uintptr_t)local_bucket & 15) == 0, "bucket_relay_p2p: pointers");
+  B200_REQUIRE(numel >= 0 && numel % 8 == 0 && stripe_elems >= 8 && stripe_elems % 8 == 0, "bucket_relay_p2p: numel / stripe %% 8");
+  B200_REQUIRE(n_peers >= 1 && n_peers <= RL_MAX_PEERS && peer_index >= 0 && peer_index < n_peers, "bucket_relay_p2p: peer %d of %d", peer_index, n_peers);
+  if (numel == 0 || n_peers == 1) return B200GRPO_OK;
+  RelayPeers peers = {};
+  for (int q = 0; q < n_peers; ++q) {
+    B200_REQUIRE(peer_buckets_host[q] && ((uintptr_t)peer_buckets_host[q] & 15) == 0, "bucket_relay_p2p: peer %d pointer", q);
+    peers.p[q] = (uint4*)peer_buckets_host[q];
+  }
+  const int64_t n_vec = numel / 8, stripe_vec = stripe_elems / 8;
+  const int64_t own = (n_vec / n_peers) + stripe_vec;
+  int64_t grid = (own + (int64_t)BK_THREADS * RL_UNROLL - 1) / ((int64_t)BK_THREADS * RL_UNROLL);
+  const int64_t cap = ctas > 0 ? ctas : (int64_t)sm_count() * 4;
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  ProfScope ps(PROF_BUCKET, st);
+  count_launch();
+  bucket_relay_p2p_kernel<<<(int)grid, BK_THREADS, 0, st>>>((const uint4*)local_bucket, peers, n_vec, peer_index, n_peers, stripe_vec);
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
 }

@@ -281,6 +281,13 @@ def bucket_relay_multicast(local_ptr: int, mc_ptr: int, numel: int, peer_index: 
                                                 int(stripe_elems), int(ctas), _stream()))
 
 
+def bucket_relay_p2p(local_ptr: int, peer_ptrs: Sequence[int], numel: int, peer_index: int, stripe_elems: int, ctas: int = 0) -> None:
+    """The relay over plain P2P stores: the owned stripes are written into every other receiver's copy of the slot."""
+    q = len(peer_ptrs)
+    peers = (C.c_void_p * q)(*[int(p) for p in peer_ptrs])
+    check(lib().b200grpo_bucket_relay_p2p(C.c_void_p(local_ptr), peers, int(numel), int(peer_index), q, int(stripe_elems), int(ctas), _stream()))
+
+
 def bucket_unpack(bucket: torch.Tensor, tensors: Sequence[torch.Tensor]) -> None:
     """K6 inverse: scatter a received bucket into the destination parameters."""
     _req(bucket, torch.bfloat16, "bucket")

@@ -327,7 +327,8 @@ class ScatterChannel:
 
     Every rank of ``group`` constructs the channel collectively; rank ``src`` is the sender, the others are receivers."""
 
-    def __init__(self, group, device, slot_bytes: int, src: int = 0, stripe_bytes: int = 64 << 10, relay_ctas: int = 0):
+    def __init__(self, group, device, slot_bytes: int, src: int = 0, stripe_bytes: int = 64 << 10, relay_ctas: int = 0,
+                 relay: str = "multicast"):
         import torch.distributed._symmetric_memory as symm
         self.group = group if group is not None else dist.group.WORLD
         self.rank, self.world, self.src = dist.get_rank(self.group), dist.get_world_size(self.group), src
@@ -335,12 +336,12 @@ class ScatterChannel:
         self.device = torch.device(device)
         self.slot_elems = (int(slot_bytes) // 2 + 7) // 8 * 8
         self.stripe_elems = max(8, int(stripe_bytes) // 2 // 8 * 8)
-        self.relay_ctas = relay_ctas
+        self.relay_ctas, self.relay = relay_ctas, relay          # relay: "multicast" (multimem.st) or "p2p" (plain stores to each peer)
         self.buf = symm.empty(2 * self.slot_elems, dtype=torch.bfloat16, device=self.device)
         self.handle = symm.rendezvous(self.buf, self.group)
-        if not self.handle.has_multicast_support or not self.handle.multicast_ptr:
-            raise RuntimeError("ScatterChannel: this group has no NVSwitch multicast mapping; use send/receive_weight_update")
-        self.mc_ptr = int(self.handle.multicast_ptr)
+        if relay == "multicast" and (not self.handle.has_multicast_support or not self.handle.multicast_ptr):
+            raise RuntimeError("ScatterChannel: this group has no NVSwitch multicast mapping; use relay='p2p' or send/receive_weight_update")
+        self.mc_ptr = int(self.handle.multicast_ptr) if relay == "multicast" else 0
         self.receivers = [r for r in range(self.world) if r != src]            # peer index q -> rank
         self.peer_ptrs = [int(self.handle.buffer_ptrs[r]) for r in self.receivers]
         self.peer_index = self.receivers.index(self.rank) if self.rank != src else -1
@@ -380,8 +381,12 @@ class ScatterChannel:
             n = _bucket_elems(infos, idxs)
             base = (k % 2) * self.slot_elems
             self.handle.barrier(channel=0)                              # A(k): my stripes of transfer k have arrived
-            ops.bucket_relay_multicast(local_ptr + 2 * base, self.mc_ptr + 2 * base, n, self.peer_index, len(self.receivers),
-                                       self.stripe_elems, self.relay_ctas)
+            if self.relay == "multicast":
+                ops.bucket_relay_multicast(local_ptr + 2 * base, self.mc_ptr + 2 * base, n, self.peer_index, len(self.receivers),
+                                           self.stripe_elems, self.relay_ctas)
+            else:
+                ops.bucket_relay_p2p(local_ptr + 2 * base, [p + 2 * base for p in self.peer_ptrs], n, self.peer_index,
+                                     self.stripe_elems, self.relay_ctas)
             self.handle.barrier(channel=1)                              # B(k): everybody's stripes are in my slot
             off = 0
             for i in idxs:
@@ -415,7 +420,15 @@ def init_actor_update_group(init_method: str, rank: int, world_size: int, group_
     timeout = timeout if timeout is not None else c10d.default_pg_timeout
     if not isinstance(timeout, timedelta):
         timeout = timedelta(seconds=float(timeout))
-    store, rank, world_size = next(c10d.rendezvous(init_method, rank, world_size, timeout=timeout))
+    if init_method.startswith("tcp://"):
+        # Host the store explicitly on group rank 0.  torch's own tcp:// rendezvous handler makes EVERY rank a client of the
+        # launcher's agent store when the process runs under torchrun / accelerate launch (TORCHELASTIC_USE_AGENT_STORE), and
+        # nobody then listens on this second world's port.
+        from urllib.parse import urlparse
+        url = urlparse(init_method)
+        store = dist.TCPStore(url.hostname, int(url.port), world_size, rank == 0, timeout, wait_for_workers=True, multi_tenant=True)
+    else:
+        store, rank, world_size = next(c10d.rendezvous(init_method, rank, world_size, timeout=timeout))
     store.set_timeout(timeout)
     kw = {}
     if (device is not None and torch.device(device).type == "cuda" and torch.device(device).index is not None

@@ -121,14 +121,14 @@ def run_sweep(dev, rank: int, world: int, buckets_mb=(1, 4, 16, 64, 256, 1024), 
         staging[0] = None
         torch.cuda.empty_cache()
     # NVSwitch multicast: pack + broadcast in one kernel; scatter + relay: pack-scatter over P2P, then multicast relay
-    for kind, sizes in (("multicast", multicast_mb), ("scatter", scatter_mb)):
+    for kind, sizes in (("multicast", multicast_mb), ("scatter", scatter_mb), ("scatter_p2p", scatter_mb)):
         for mb in sizes:
             try:
                 if kind == "multicast":
                     ch = wu.MulticastChannel(None, dev, wu.MulticastChannel.slot_bytes_for(request.parameters_info, mb << 20))
                 else:
                     ch = wu.ScatterChannel(None, dev, wu.ScatterChannel.slot_bytes_for(request.parameters_info, mb << 20),
-                                           stripe_bytes=stripe_kb << 10)
+                                           stripe_bytes=stripe_kb << 10, relay="p2p" if kind == "scatter_p2p" else "multicast")
             except Exception as e:  # noqa: BLE001
                 out.append({"variant": f"{kind}_{mb}MB", "unavailable": repr(e)[:200]})
                 break
@@ -141,7 +141,7 @@ def run_sweep(dev, rank: int, world: int, buckets_mb=(1, 4, 16, 64, 256, 1024), 
 
             ms = timed(run_ch)
             emit(f"{kind}_{mb}MB", ms, check(), {"bucket_MB": mb, "n_transfers": len(wu.plan_multicast(request.parameters_info, mb << 20)),
-                                               "slot_MB": ch.slot_elems * 2 / 2 ** 20, **({"stripe_KB": stripe_kb} if kind == "scatter" else {})})
+                                               "slot_MB": ch.slot_elems * 2 / 2 ** 20, **({"stripe_KB": stripe_kb} if kind.startswith("scatter") else {})})
             del ch
             torch.cuda.empty_cache()
     del params, expect, by_name

@@ -24,6 +24,8 @@ sys.path.insert(0, ROOT)
 
 
 def main():
+    import faulthandler
+    faulthandler.dump_traceback_later(int(os.environ.get("WU_HANG_DUMP_S", "120")), exit=True)   # a hung collective names its line
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -113,6 +115,7 @@ def main():
         else:
             box = [None]
         dist.broadcast_object_list(box, src=0)
+        print(f"[rank {rank}] {transport} zero3={zero3} bucket={bucket_bytes}", file=sys.stderr, flush=True)
         ok = True
         try:
             if rank == 0:
