@@ -722,7 +722,7 @@ def weight_broadcast_record(dev, rank, world) -> dict:
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     from bench_weight_update import run_sweep
     try:
-        lines = run_sweep(dev, rank, world, buckets_mb=(16, 256), multicast_mb=(), scatter_mb=(64,), iters=2)
+        lines = run_sweep(dev, rank, world, buckets_mb=(64, 256), multicast_mb=(), scatter_mb=(256,), iters=2, scatter_p2p_mb=())
     except Exception as e:  # noqa: BLE001  -- a side record must never take the bench line down
         return {"unavailable": repr(e)[:300]}
     rec = {"workload": "C5: Qwen2.5-7B bf16 parameters, 339 tensors, trainer rank 0 -> %d receivers" % (world - 1), "unit": "GB/s",

@@ -42,7 +42,8 @@ def qwen25_7b_shapes(layers=28, hidden=3584, inter=18944, vocab=152064, kv=512):
 
 
 def run_sweep(dev, rank: int, world: int, buckets_mb=(1, 4, 16, 64, 256, 1024), multicast_mb=(64, 256), scatter_mb=(16, 64, 256),
-              iters: int = 3, fp32_masters: bool = False, layers: int = 28, stripe_kb: int = 64, reference: bool = True) -> list[dict]:
+              iters: int = 3, fp32_masters: bool = False, layers: int = 28, stripe_kb: int = 64, reference: bool = True,
+              scatter_p2p_mb=None) -> list[dict]:
     """Every transport over the default process group (rank 0 = trainer, the others = actor GPUs); returns one record per
     variant (identical on every rank).  GB/s = bf16 parameter bytes delivered per receiver / max-over-ranks device time."""
     from pipelinerl_swe_b200 import weight_update as wu
@@ -121,7 +122,8 @@ def run_sweep(dev, rank: int, world: int, buckets_mb=(1, 4, 16, 64, 256, 1024), 
         staging[0] = None
         torch.cuda.empty_cache()
     # NVSwitch multicast: pack + broadcast in one kernel; scatter + relay: pack-scatter over P2P, then multicast relay
-    for kind, sizes in (("multicast", multicast_mb), ("scatter", scatter_mb), ("scatter_p2p", scatter_mb)):
+    for kind, sizes in (("multicast", multicast_mb), ("scatter", scatter_mb),
+                        ("scatter_p2p", scatter_mb if scatter_p2p_mb is None else scatter_p2p_mb)):
         for mb in sizes:
             try:
                 if kind == "multicast":

@@ -7,7 +7,8 @@
 Every rank holds the same hidden/targets and its contiguous shard of lm_head rows; forward exchanges the
 16 B/token partials with one all-gather, backward all-reduces dH.  Compared on every rank against the
 unsharded kernels run locally on the full weight: logprob/entropy bit-identical across ranks and within
-1e-4 of unsharded, dW shard within 1e-2 (bf16) of the matching rows, dH within 1e-2.
+1e-4 of unsharded, dW shard within 1e-2 (bf16) of the matching rows, dH within 2e-2 (the north star's gradient
+tolerance: NCCL's ring sums the 8 bf16 partials in bf16, 1.4e-2 at 8 ranks; the multicast kernel accumulates in f32, 4.5e-3).
 """
 import os
 import sys
@@ -62,7 +63,7 @@ def main():
     e_out = float((out1 - out0).abs().max())
     e_dw = rel(w1.grad, w0.grad[v_off:v_off + w_shard.shape[0]])
     e_dh = rel(h1.grad, h0.grad)
-    ok = identical and e_out < 1e-4 and e_dw < 1e-2 and e_dh < 1e-2
+    ok = identical and e_out < 1e-4 and e_dw < 1e-2 and e_dh < 2e-2   # dH: the north star's 2e-2 (NCCL sums 8 bf16 partials in bf16)
 
     # ---- the drop-in itself: rl_step(model, batch, step, max_step, config, vocab_group=...) on a model whose lm_head holds
     #      only this rank's vocab rows == rl_step on the unsharded model (loss, all stats, dH, this rank's rows of dW)
@@ -90,7 +91,7 @@ def main():
     e_stats = max(abs(stats_s[k] - stats_f[k]) / (abs(stats_f[k]) + 0.1) for k in stats_f)   # 1e-3 relative with a 1e-4 absolute floor
     e_rl_dh = rel(shard.hidden.grad, full.hidden.grad)
     e_rl_dw = rel(shard.lm_head.weight.grad, full.lm_head.weight.grad[off:off + w_sh.shape[0]])
-    rl_ok = set(stats_s) == set(stats_f) and e_loss < 1e-5 + 1e-3 * abs(loss_f.item()) and e_stats < 1e-3 and e_rl_dh < 1e-2 and e_rl_dw < 1e-2
+    rl_ok = set(stats_s) == set(stats_f) and e_loss < 1e-5 + 1e-3 * abs(loss_f.item()) and e_stats < 1e-3 and e_rl_dh < 2e-2 and e_rl_dw < 1e-2
     ok = ok and rl_ok
     t = torch.tensor([int(ok)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
