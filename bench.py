@@ -525,7 +525,9 @@ class DeviceWorkload:
         saved = self.saved if self.save_logits else None
         lp, ent, lse = ops.lmhead_finalize(self.fwd_stats(h, tgt, saved))
         loss, metrics, coef_lp, coef_ent, _ = ops.token_loss(lp[None], ent[None], b, self.cfg)
-        args = (h, self.weight, tgt, lse, ent, coef_lp[0], coef_ent[0], 1.0, self.v_offset)
+        # no entropy bonus in this config: K3's dLoss/dentropy is identically zero and the backward is told so (as rl_step does)
+        c_ent = coef_ent[0] if self.cfg.entropy_coef != 0.0 else None
+        args = (h, self.weight, tgt, lse, ent, coef_lp[0], c_ent, 1.0, self.v_offset)
         if self.exchange is not None:   # dH partial into the symmetric buffer, in-switch all-reduce beside the dW GEMM
             from pipelinerl_swe_b200 import _abi
             x, M = self.exchange, h.shape[0]

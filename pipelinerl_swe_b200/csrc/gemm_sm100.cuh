@@ -60,12 +60,19 @@ struct GemmParams {
   int c_is_f32, accumulate;
   float* slab;              // [k_splits][M][N] f32 partial sums when k_splits > 1;
                             // [tail piece][tile_rows][256] when the tail split is on
+  // EPI_STORE, optional row epilogue (the entropy-free backward: dH = diag(row_scale) . (E . W) + row_coef * W[target]):
+  const float* row_scale;          // [M] multiplies the accumulator row (nullptr: 1)
+  const float* row_coef;           // [M] coefficient of the gathered row (nullptr: no gather)
+  const __nv_bfloat16* gather_src; // [*, gather_ld] rows indexed by targets[row] - v_offset (skipped when outside [0, gather_rows))
+  long long gather_ld;
+  int gather_rows;
   // EPI_FWD_STATS / EPI_BWD_DLOGITS
   const long long* targets;
   long long v_offset;
   float inv_temp;
-  float* part;              // [n_blocks][M][4]  per-tile (max z, sum e, sum e*z, z_target|0)
-  __nv_bfloat16* zsave;     // optional panels [n_blocks][M][256]: (z - tile max)/T saved for a recompute-free backward
+  const float* row_ref;     // EPI_FWD_STATS: [M] per-row reference r (in units of z/T); exponentials are taken relative to it
+  float* part;              // [n_blocks][M][4]  per-tile (unused, sum e, sum e*z/T.., z_target|0) with e = exp(z/T - r)
+  __nv_bfloat16* zsave;     // optional panels [n_blocks][M][256]: E = exp(z/T - r) saved for a recompute-free backward
   const float *lse, *entropy, *coef_lp, *coef_ent, *grad_scale;
   __nv_bfloat16* dlogits;   // panels [n_blocks][M][256]
 };
@@ -134,41 +141,42 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
-// Forward epilogue, pass 1: max over the valid columns of one 32-column chunk.
-__device__ __forceinline__ float chunk_max(const uint32_t (&v)[32], int n_valid) {
-  float cmax = -INFINITY;
-  if (n_valid >= 32) {
-#pragma unroll
-    for (int j = 0; j < 32; ++j) cmax = fmaxf(cmax, __uint_as_float(v[j]));
-  } else {
-#pragma unroll
-    for (int j = 0; j < 32; ++j) if (j < n_valid) cmax = fmaxf(cmax, __uint_as_float(v[j]));
-  }
-  return cmax;
-}
+struct FwdRowState { float neg2, s, u, tgt; int tcol; };
 
-struct FwdRowState { float m_raw, s, u, tgt; int tcol; };
-
-// Forward epilogue, pass 2: with the tile max known, accumulate sum e and sum e*z, pick the
-// target logit, and (optionally) save y = (z - tile max)/T as bf16 for the backward.
+// Forward epilogue, ONE pass: exponentials are taken relative to a per-row reference r known before the GEMM (a cheap lower
+// bound of the row maximum: the largest of the target logit and a few sampled logits, lmhead.cu row_ref_kernel), so no tile
+// maximum is needed: e = exp(z/T - r) accumulates sum e and sum e*z, the target logit is picked, and (optionally) e is saved
+// as bf16 -- bf16 has f32's exponent range, so e keeps 2^-9 relative precision whatever its magnitude, and every quantity
+// the backward needs is a ROW-scaled multiple of it: p = e * exp(r - lse).
 template <bool kSave>
 __device__ __forceinline__ void fwd_chunk(FwdRowState& st, const uint32_t (&v)[32], int col0, int n_valid, float scale2,
-                                          float inv_temp, __nv_bfloat16* zout) {  // zout: this row's 32 columns in the panel
-  const float neg = -st.m_raw * scale2;
+                                          __nv_bfloat16* zout) {  // zout: this row's 32 columns in the panel
   float s = 0.f, u = 0.f;
+  uint32_t packed[16];
   if (n_valid >= 32) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      const float a = __uint_as_float(v[j]);
-      const float e = fast_exp2(fmaf(a, scale2, neg));
-      s += e; u = fmaf(e, a, u);
+    for (int j = 0; j < 32; j += 2) {
+      const float a0 = __uint_as_float(v[j]), a1 = __uint_as_float(v[j + 1]);
+      const float e0 = fast_exp2(fmaf(a0, scale2, st.neg2)), e1 = fast_exp2(fmaf(a1, scale2, st.neg2));
+      s += e0; u = fmaf(e0, a0, u);
+      s += e1; u = fmaf(e1, a1, u);
+      if constexpr (kSave) {
+        const __nv_bfloat162 b = __floats2bfloat162_rn(e0, e1);
+        packed[j >> 1] = *reinterpret_cast<const uint32_t*>(&b);
+      }
     }
-  } else {
+  } else {  // vocab tail: columns past N contribute nothing and are saved as zeros (they are K-padding of the dH GEMM)
 #pragma unroll
-    for (int j = 0; j < 32; ++j) if (j < n_valid) {
-      const float a = __uint_as_float(v[j]);
-      const float e = fast_exp2(fmaf(a, scale2, neg));
-      s += e; u = fmaf(e, a, u);
+    for (int j = 0; j < 32; j += 2) {
+      const float a0 = __uint_as_float(v[j]), a1 = __uint_as_float(v[j + 1]);
+      const float e0 = j < n_valid ? fast_exp2(fmaf(a0, scale2, st.neg2)) : 0.f;
+      const float e1 = j + 1 < n_valid ? fast_exp2(fmaf(a1, scale2, st.neg2)) : 0.f;
+      s += e0; u = fmaf(e0, j < n_valid ? a0 : 0.f, u);
+      s += e1; u = fmaf(e1, j + 1 < n_valid ? a1 : 0.f, u);
+      if constexpr (kSave) {
+        const __nv_bfloat162 b = __floats2bfloat162_rn(e0, e1);
+        packed[j >> 1] = *reinterpret_cast<const uint32_t*>(&b);
+      }
     }
   }
   st.s += s; st.u += u;
@@ -178,19 +186,6 @@ __device__ __forceinline__ void fwd_chunk(FwdRowState& st, const uint32_t (&v)[3
     for (int j = 0; j < 32; ++j) if (j == t) st.tgt = __uint_as_float(v[j]);
   }
   if constexpr (kSave) {
-    uint32_t packed[16];
-    const float negm = -st.m_raw * inv_temp;
-#pragma unroll
-    for (int j = 0; j < 32; j += 2) {
-      const __nv_bfloat162 b = __floats2bfloat162_rn(fmaf(__uint_as_float(v[j]), inv_temp, negm),
-                                                     fmaf(__uint_as_float(v[j + 1]), inv_temp, negm));
-      packed[j >> 1] = *reinterpret_cast<const uint32_t*>(&b);
-    }
-    if (n_valid < 32) {  // vocab tail: columns past N stay zero (they are K-padding of the dH GEMM)
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (j >= n_valid) packed[j >> 1] &= (j & 1) ? 0x0000ffffu : 0xffff0000u;
-    }
     uint4* o = reinterpret_cast<uint4*>(zout);
 #pragma unroll
     for (int q = 0; q < 4; ++q) o[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
@@ -227,9 +222,47 @@ __device__ __forceinline__ void bwd_chunk(const BwdRowConst& rc, const uint32_t 
   for (int q = 0; q < 4; ++q) o[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
 }
 
+// Row epilogue of the entropy-free backward: x <- row_scale[row] * x + row_coef[row] * gather_src[target(row)][col]
+struct RowEpi { float scale, coef; const __nv_bfloat16* src; };
+__device__ __forceinline__ RowEpi load_row_epi(const GemmParams& p, int row) {
+  RowEpi r;
+  r.scale = p.row_scale ? __ldg(p.row_scale + row) : 1.0f;
+  r.coef = 0.f; r.src = nullptr;
+  if (p.row_coef) {
+    const float c = __ldg(p.row_coef + row);
+    const long long t = p.targets[row] - p.v_offset;
+    if (c != 0.f && t >= 0 && t < p.gather_rows) { r.coef = c; r.src = p.gather_src + t * p.gather_ld; }
+  }
+  return r;
+}
+__device__ __forceinline__ void apply_row_epi(const RowEpi& r, uint32_t (&v)[32], int col0, int n_valid) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) * r.scale);
+  if (r.src) {
+    if (n_valid >= 32 && ((reinterpret_cast<uintptr_t>(r.src + col0) & 15) == 0)) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint4 w = __ldg(reinterpret_cast<const uint4*>(r.src + col0) + q);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&w);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __bfloat1622float2(h[k]);
+          v[8 * q + 2 * k] = __float_as_uint(fmaf(r.coef, f.x, __uint_as_float(v[8 * q + 2 * k])));
+          v[8 * q + 2 * k + 1] = __float_as_uint(fmaf(r.coef, f.y, __uint_as_float(v[8 * q + 2 * k + 1])));
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < n_valid) v[j] = __float_as_uint(fmaf(r.coef, __bfloat162float(r.src[col0 + j]), __uint_as_float(v[j])));
+    }
+  }
+}
+
 // slot >= 0: tail piece, written whole (32 columns) at tile-local coordinates (r_local, c_local)
-__device__ __forceinline__ void store_chunk(const GemmParams& p, const uint32_t (&v)[32], int row, int col0, int n_valid, int ks,
-                                            int slot, int r_local, int c_local) {
+__device__ __forceinline__ void store_chunk(const GemmParams& p, uint32_t (&v)[32], int row, int col0, int n_valid, int ks,
+                                            int slot, int r_local, int c_local, const RowEpi& re) {
+  if (slot < 0 && p.k_splits <= 1 && (p.row_scale || p.row_coef)) apply_row_epi(re, v, col0, n_valid);   // pieces: applied by the reduce kernel
   if (slot >= 0) {
     float4* o4 = reinterpret_cast<float4*>(p.slab + ((long long)slot * p.tile_rows + r_local) * PANEL_W + c_local);
 #pragma unroll
@@ -441,8 +474,9 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         const bool row_ok = row < p.M;
         FwdRowState fs;
         BwdRowConst bc;
+        RowEpi re = {1.0f, 0.f, nullptr};
         if constexpr (kEpi == EPI_FWD_STATS) {
-          fs.m_raw = -INFINITY; fs.s = 0.f; fs.u = 0.f; fs.tgt = 0.f;
+          fs.neg2 = row_ok ? -p.row_ref[row] * LOG2E_F : 0.f; fs.s = 0.f; fs.u = 0.f; fs.tgt = 0.f;
           const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
           fs.tcol = (t >= n0 && t < min(p.N, n0 + BLOCK_N)) ? (int)t : -1000000;
         }
@@ -455,21 +489,12 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
           const long long t = row_ok ? p.targets[row] - p.v_offset : -1;
           bc.tcol = (t >= 0 && t < p.N) ? (int)t : -1000000;
         }
+        if constexpr (kEpi == EPI_STORE) {
+          if (row_ok && (p.row_scale || p.row_coef)) re = load_row_epi(p, row);
+        }
         ptx::mbar_wait(&tmem_full[as], aphase, 6);
         ptx::tc_fence_after();
         const uint32_t t_addr = tmem_base + lane_addr + as * ACC_COLS + rep * BLOCK_N;
-        if constexpr (kEpi == EPI_FWD_STATS) {   // pass 1: tile max per row
-#pragma unroll 1
-          for (int c = 0; c < BLOCK_N / 32; ++c) {
-            const int col0 = n0 + c * 32;
-            if (col0 >= p.N) break;                    // warp-uniform
-            uint32_t v[32];
-            __syncwarp();
-            ptx::tmem_ld_32x32(t_addr + c * 32, v);
-            ptx::tmem_ld_wait();
-            fs.m_raw = fmaxf(fs.m_raw, chunk_max(v, min(32, p.N - col0)));
-          }
-        }
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N / 32; ++c) {
           const int col0 = n0 + c * 32;
@@ -480,20 +505,19 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
           ptx::tmem_ld_wait();
           const int n_valid = min(32, p.N - col0);
           if constexpr (kEpi == EPI_FWD_STATS) {
-            if (kSave && !row_ok) continue;
-            fwd_chunk<kSave>(fs, v, col0, n_valid, scale2, p.inv_temp,
-                             kSave ? p.zsave + ((long long)it.nb * p.M + row) * PANEL_W + c * 32 : nullptr);
+            if (!row_ok) continue;
+            fwd_chunk<kSave>(fs, v, col0, n_valid, scale2, kSave ? p.zsave + ((long long)it.nb * p.M + row) * PANEL_W + c * 32 : nullptr);
           }
           if constexpr (kEpi == EPI_BWD_DLOGITS) {
             if (row_ok) bwd_chunk(bc, v, col0, n_valid, scale2, p.dlogits + ((long long)it.nb * p.M + row) * PANEL_W + c * 32);
           }
           if constexpr (kEpi == EPI_STORE) {
-            if (row_ok) store_chunk(p, v, row, col0, n_valid, it.ks, it.slot, (int)cta_rank * CTA_M + rep * GEMM_BLOCK_M + row_in_tile, c * 32);
+            if (row_ok) store_chunk(p, v, row, col0, n_valid, it.ks, it.slot, (int)cta_rank * CTA_M + rep * GEMM_BLOCK_M + row_in_tile, c * 32, re);
           }
         }
         if constexpr (kEpi == EPI_FWD_STATS) {
           if (row_ok) {
-            const float4 o = make_float4(fs.m_raw * p.inv_temp, fs.s, fs.u * p.inv_temp, fs.tgt * p.inv_temp);
+            const float4 o = make_float4(0.f, fs.s, fs.u * p.inv_temp, fs.tgt * p.inv_temp);
             reinterpret_cast<float4*>(p.part)[(long long)it.nb * p.M + row] = o;
           }
         }

@@ -195,22 +195,74 @@ static int ctas_for(int M) {
 static int mrep_for(int tunable, int ctas) { return (ctas == 2 && get_tunable(tunable)) ? 2 : 1; }
 
 // ---- small kernels around the GEMMs -----------------------------------------------------
-// merge the per-tile partials [n_blocks][M][4] -> stats [M][4] (online-softmax merge, fixed order).
+// Per-row reference r of the forward's exponentials (units of z/T): the largest of the target logit (when the target lies in
+// this rank's vocab rows) and four sampled logits.  Any value works for correctness -- e = exp(z/T - r) is kept in f32 / bf16,
+// whose exponent range is +-88 in these units, and every later use re-scales by exp(r - lse) -- r only has to sit within
+// that distance of the row's log-sum-exp, and a sampled token's own logit does (its log-prob would be < -80 otherwise; an
+// overflow surfaces as a non-finite log-prob, i.e. the reference's own assert at rl/__init__.py:209).
+// One warp per row: the hidden row is read once (16-byte vectors), dotted with up to five weight rows.
+constexpr int RR_COLS = 4;
+__global__ void __launch_bounds__(256) row_ref_kernel(const __nv_bfloat16* __restrict__ hidden, long long ldh,
+                                                      const __nv_bfloat16* __restrict__ weight, long long ldw,
+                                                      const long long* __restrict__ targets, int M, int H, int Vloc, long long v_offset,
+                                                      float inv_temp, float* __restrict__ row_ref) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const long long t = targets[row] - v_offset;
+  const bool has_t = t >= 0 && t < Vloc;
+  const __nv_bfloat16* wr[RR_COLS + 1];
+#pragma unroll
+  for (int c = 0; c < RR_COLS; ++c) wr[c] = weight + (long long)((long long)c * Vloc / RR_COLS) * ldw;
+  wr[RR_COLS] = weight + (has_t ? t : 0) * ldw;
+  float acc[RR_COLS + 1];
+#pragma unroll
+  for (int c = 0; c <= RR_COLS; ++c) acc[c] = 0.f;
+  const __nv_bfloat16* h = hidden + (long long)row * ldh;
+  const bool vec = ((ldh | ldw) & 7) == 0 && (((uintptr_t)hidden | (uintptr_t)weight) & 15) == 0;
+  if (vec) {
+    for (int k = lane * 8; k < H; k += 256) {
+      const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + k));
+      const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&hv);
+#pragma unroll
+      for (int c = 0; c <= RR_COLS; ++c) {
+        const uint4 wv = __ldg(reinterpret_cast<const uint4*>(wr[c] + k));
+        const __nv_bfloat162* wp = reinterpret_cast<const __nv_bfloat162*>(&wv);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 a = __bfloat1622float2(hp[q]), w = __bfloat1622float2(wp[q]);
+          acc[c] = fmaf(a.x, w.x, fmaf(a.y, w.y, acc[c]));
+        }
+      }
+    }
+  } else {
+    for (int k = lane; k < H; k += 32) {
+      const float a = __bfloat162float(h[k]);
+#pragma unroll
+      for (int c = 0; c <= RR_COLS; ++c) acc[c] = fmaf(a, __bfloat162float(wr[c][k]), acc[c]);
+    }
+  }
+  float r = -INFINITY;
+#pragma unroll
+  for (int c = 0; c <= RR_COLS; ++c) {
+    const float d = warp_sum(acc[c]);
+    if (c < RR_COLS || has_t) r = fmaxf(r, d);
+  }
+  if (lane == 0) row_ref[row] = r * inv_temp;
+}
+
+// merge the per-tile partials [n_blocks][M][4] -> stats [M][4] = (r, sum e, sum e*z, z_target): every tile of a row shares the
+// reference r, so the merge is three plain sums in a fixed order (deterministic).
 // Block = 32 rows x 8 tile slices: a warp reads 512 contiguous bytes per tile, 4 loads in flight.
 constexpr int MG_SLICES = 8;
-__device__ __forceinline__ void merge_one(float& m, float& sum, float& dot, float& tgt, const float4 q) {
-  if (q.x > m) { const float r = __expf(m - q.x); sum *= r; dot *= r; m = q.x; }
-  const float w = __expf(q.x - m);
-  sum = fmaf(q.y, w, sum); dot = fmaf(q.z, w, dot); tgt += q.w;
-}
 // kMulticast: `stats` is an NVSwitch multicast address (this rank's slot of a symmetric [R][M][4] buffer): the merged row is
 // stored with multimem.st, so the merge IS the all-gather of the vocab-parallel exchange -- every rank's copy of the slot is
 // written by the switch, no collective kernel follows (the caller only synchronises).
 template <bool kMulticast>
-__global__ void __launch_bounds__(32 * MG_SLICES) fwd_merge_kernel(const float4* __restrict__ part, int S, int M, float4* __restrict__ stats) {
+__global__ void __launch_bounds__(32 * MG_SLICES) fwd_merge_kernel(const float4* __restrict__ part, const float* __restrict__ row_ref, int S,
+                                                                   int M, float4* __restrict__ stats) {
   const int rx = threadIdx.x & 31, sy = threadIdx.x >> 5;
   const int row = blockIdx.x * 32 + rx;
-  float m = -INFINITY, sum = 0.f, dot = 0.f, tgt = 0.f;
+  float sum = 0.f, dot = 0.f, tgt = 0.f;
   if (row < M) {
     int s = sy;
     for (; s + 3 * MG_SLICES < S; s += 4 * MG_SLICES) {
@@ -218,21 +270,21 @@ __global__ void __launch_bounds__(32 * MG_SLICES) fwd_merge_kernel(const float4*
 #pragma unroll
       for (int j = 0; j < 4; ++j) q[j] = __ldg(&part[(long long)(s + j * MG_SLICES) * M + row]);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) merge_one(m, sum, dot, tgt, q[j]);
+      for (int j = 0; j < 4; ++j) { sum += q[j].y; dot += q[j].z; tgt += q[j].w; }
     }
-    for (; s < S; s += MG_SLICES) merge_one(m, sum, dot, tgt, __ldg(&part[(long long)s * M + row]));
+    for (; s < S; s += MG_SLICES) {
+      const float4 q = __ldg(&part[(long long)s * M + row]);
+      sum += q.y; dot += q.z; tgt += q.w;
+    }
   }
   __shared__ float4 sh[MG_SLICES][32];
-  sh[sy][rx] = make_float4(m, sum, dot, tgt);
+  sh[sy][rx] = make_float4(0.f, sum, dot, tgt);
   __syncthreads();
   if (sy == 0 && row < M) {
-    float M2 = -INFINITY, S2 = 0.f, D2 = 0.f, T2 = 0.f;
+    float S2 = 0.f, D2 = 0.f, T2 = 0.f;
 #pragma unroll
-    for (int j = 0; j < MG_SLICES; ++j) {
-      const float4 q = sh[j][rx];
-      if (q.x == -INFINITY) continue;  // slice saw no tile
-      merge_one(M2, S2, D2, T2, q);
-    }
+    for (int j = 0; j < MG_SLICES; ++j) { const float4 q = sh[j][rx]; S2 += q.y; D2 += q.z; T2 += q.w; }
+    const float M2 = row_ref[row];
     if constexpr (kMulticast) {
       asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(stats + row), "f"(M2), "f"(S2), "f"(D2), "f"(T2) : "memory");
     } else {
@@ -260,16 +312,17 @@ __global__ void __launch_bounds__(256) finalize_kernel(const float4* __restrict_
   if (lse_out) lse_out[row] = lse;
 }
 
-// Saved forward logits -> dlogits, in place (the recompute-free backward).  z holds y = (logit - tile max)/T
-// as bf16 in [n_blocks][M][256] panels; the tile max lives in part[nb][t].x.  HBM-bound: 4 B/element
-// (bf16 in + bf16 out), 16-byte vectors, 32 threads per panel row, fully contiguous traversal.
+// Saved forward exponentials -> dlogits, in place (the recompute-free backward WITH an entropy term; without one the
+// backward never forms dlogits at all, see lmhead_bwd_impl).  z holds E = exp(logit/T - r) as bf16 in [n_blocks][M][256]
+// panels; p = E * exp(r - lse).  HBM-bound: 4 B/element (bf16 in + bf16 out), 16-byte vectors, 32 threads per panel row,
+// fully contiguous traversal.
 constexpr int DL_THREADS = 256;
 constexpr int DL_ROWS = 32;   // panel rows per block: 32 rows x 256 columns = 16 KB in, 16 KB out
 __global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
-    __nv_bfloat16* __restrict__ z, const float4* __restrict__ part, int M, int N, const long long* __restrict__ targets,
+    __nv_bfloat16* __restrict__ z, const float* __restrict__ row_ref, int M, int N, const long long* __restrict__ targets,
     long long v_offset, const float* __restrict__ lse, const float* __restrict__ entropy, const float* __restrict__ coef_lp,
     const float* __restrict__ coef_ent, const float* __restrict__ grad_scale, float inv_temp) {
-  __shared__ float s_a[DL_ROWS], s_e[DL_ROWS], s_ent[DL_ROWS], s_shift[DL_ROWS];
+  __shared__ float s_a[DL_ROWS], s_e[DL_ROWS], s_ent[DL_ROWS], s_shift[DL_ROWS], s_c[DL_ROWS];
   __shared__ int s_t[DL_ROWS];
   const int nb = blockIdx.y, row0 = blockIdx.x * DL_ROWS;
   if (threadIdx.x < DL_ROWS) {   // per-row constants, loaded once per block
@@ -279,7 +332,9 @@ __global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
       s_a[threadIdx.x] = coef_lp[row] * gs;
       s_e[threadIdx.x] = coef_ent[row] * gs;
       s_ent[threadIdx.x] = entropy[row];
-      s_shift[threadIdx.x] = (__ldg(&part[(long long)nb * M + row]).x - lse[row]) * LOG2E_F;  // (tile max - lse) * log2 e
+      const float d = row_ref[row] - lse[row];             // log p = log E + (r - lse)
+      s_shift[threadIdx.x] = d * LOG2E_F;
+      s_c[threadIdx.x] = __expf(d);
       const long long tl = targets[row] - v_offset - (long long)nb * PANEL_W;
       s_t[threadIdx.x] = (tl >= 0 && tl < PANEL_W) ? (int)tl : -1000;
     }
@@ -300,7 +355,7 @@ __global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
   for (int j = 0; j < DL_ROWS / 8; ++j) {
     const int r = wr + 8 * j;
     if (row0 + r >= M) continue;
-    const float a = s_a[r], e = s_e[r], ent = s_ent[r], shift2 = s_shift[r];
+    const float a = s_a[r], e = s_e[r], ent = s_ent[r], shift2 = s_shift[r], c = s_c[r];
     const int t = s_t[r] - sub * 8;
     __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw[j]);
     float d[8];
@@ -309,9 +364,10 @@ __global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
       const float2 y = __bfloat1622float2(h[q]);
 #pragma unroll
       for (int w = 0; w < 2; ++w) {
-        const float y2 = fmaf(w ? y.y : y.x, LOG2E_F, shift2);   // log2 p
-        const float pr = fast_exp2(y2);
-        d[2 * q + w] = -pr * fmaf(e, fmaf(y2, LN2_F, ent), a);   // -p * (a + e*(logp + H))
+        const float ev = w ? y.y : y.x;
+        const float pr = ev * c;
+        const float lp = (__log2f(ev) + shift2) * LN2_F;                      // log p (-inf when E underflowed to 0)
+        d[2 * q + w] = pr > 0.f ? -pr * fmaf(e, lp + ent, a) : 0.f;          // -p * (a + e*(logp + H))
       }
     }
     if ((unsigned)t < 8u || n_valid < 8) {   // rare: the row's target column or the vocab tail is in this vector
@@ -324,6 +380,66 @@ __global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
 #pragma unroll
     for (int q = 0; q < 4; ++q) h[q] = __floats2bfloat162_rn(d[2 * q], d[2 * q + 1]);
     *reinterpret_cast<uint4*>(base + (long long)r * PANEL_W) = raw[j];
+  }
+}
+
+// ---- the entropy-free backward never forms dlogits: with coef_ent == 0, dlogits = a * (onehot - p) and p = E * exp(r - lse),
+// so   dH = diag(s) . (E . W) + a * W[target]          dW = E^T . (diag(s) . hidden) + scatter(a * hidden at the target rows)
+// with the per-row scale s = -a * exp(r - lse).  The two GEMMs read the forward's E panels as they are; what is left of the
+// 5 GB dlogits pass is this row kernel (scale + scaled copy of hidden, 2 x 58 MB at C3) and a sparse add of M rows into dW.
+__global__ void __launch_bounds__(256) bwd_rows_kernel(const __nv_bfloat16* __restrict__ hidden, long long ldh, const float* __restrict__ row_ref,
+                                                       const float* __restrict__ lse, const float* __restrict__ coef_lp,
+                                                       const float* __restrict__ grad_scale, float inv_temp, int M, int H,
+                                                       float* __restrict__ row_scale, float* __restrict__ row_coef,
+                                                       __nv_bfloat16* __restrict__ hs) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const float a = coef_lp[row] * (grad_scale ? *grad_scale : 1.0f) * inv_temp;
+  const float sc = a != 0.f ? -a * __expf(row_ref[row] - lse[row]) : 0.f;
+  if (lane == 0) { row_scale[row] = sc; row_coef[row] = a; }
+  if (!hs) return;
+  const __nv_bfloat16* h = hidden + (long long)row * ldh;
+  __nv_bfloat16* o = hs + (long long)row * H;
+  if ((ldh & 7) == 0 && ((uintptr_t)hidden & 15) == 0) {
+    for (int k = lane * 8; k < H; k += 256) {
+      uint4 v = sc != 0.f ? __ldg(reinterpret_cast<const uint4*>(h + k)) : make_uint4(0, 0, 0, 0);
+      __nv_bfloat162* p = reinterpret_cast<__nv_bfloat162*>(&v);
+      if (sc != 0.f) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { const float2 f = __bfloat1622float2(p[q]); p[q] = __floats2bfloat162_rn(f.x * sc, f.y * sc); }
+      }
+      *reinterpret_cast<uint4*>(o + k) = v;
+    }
+  } else {
+    for (int k = lane; k < H; k += 32) o[k] = __float2bfloat16_rn(sc != 0.f ? __bfloat162float(h[k]) * sc : 0.f);
+  }
+}
+
+// dW[target(t) - v_offset, :] += a_t * hidden[t, :]   for the rows whose target lies in this rank's vocab rows (the onehot term).
+// One warp per token row; f32 gradients take red.global.add (several tokens may share a target), bf16 gradients an atomic
+// bf16x2 add.
+__global__ void __launch_bounds__(256) dw_target_kernel(const __nv_bfloat16* __restrict__ hidden, long long ldh, const long long* __restrict__ targets,
+                                                        long long v_offset, int Vloc, const float* __restrict__ row_coef, int M, int H,
+                                                        void* grad_weight, long long ldgw, int gw_is_f32) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const float a = row_coef[row];
+  const long long t = targets[row] - v_offset;
+  if (a == 0.f || t < 0 || t >= Vloc) return;
+  const __nv_bfloat16* h = hidden + (long long)row * ldh;
+  if (gw_is_f32) {
+    float* g = reinterpret_cast<float*>(grad_weight) + t * ldgw;
+    for (int k = lane * 2; k < H; k += 64) {
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(h + k));
+      atomicAdd(g + k, a * f.x);
+      atomicAdd(g + k + 1, a * f.y);
+    }
+  } else {
+    __nv_bfloat16* g = reinterpret_cast<__nv_bfloat16*>(grad_weight) + t * ldgw;
+    for (int k = lane * 2; k < H; k += 64) {
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(h + k));
+      atomicAdd(reinterpret_cast<__nv_bfloat162*>(g + k), __floats2bfloat162_rn(a * f.x, a * f.y));
+    }
   }
 }
 
@@ -366,6 +482,14 @@ __global__ void __launch_bounds__(256) tail_reduce_kernel(const GemmParams p) {
     const float4 x = __ldg(reinterpret_cast<const float4*>(src + s * piece));
     acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
   }
+  if (p.row_scale || p.row_coef) {   // the row epilogue the full tiles apply in the GEMM (store_chunk)
+    const RowEpi re = load_row_epi(p, row);
+    acc.x *= re.scale; acc.y *= re.scale; acc.z *= re.scale; acc.w *= re.scale;
+    if (re.src) {
+      acc.x = fmaf(re.coef, __bfloat162float(re.src[col]), acc.x); acc.y = fmaf(re.coef, __bfloat162float(re.src[col + 1]), acc.y);
+      acc.z = fmaf(re.coef, __bfloat162float(re.src[col + 2]), acc.z); acc.w = fmaf(re.coef, __bfloat162float(re.src[col + 3]), acc.w);
+    }
+  }
   if (p.c_is_f32) {
     float* o = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + col;
     if (p.accumulate) { acc.x += o[0]; acc.y += o[1]; acc.z += o[2]; acc.w += o[3]; }
@@ -376,6 +500,17 @@ __global__ void __launch_bounds__(256) tail_reduce_kernel(const GemmParams p) {
     o[2] = __float2bfloat16_rn(acc.z); o[3] = __float2bfloat16_rn(acc.w);
   }
 }
+
+// optional row epilogue of a store GEMM (see GemmParams)
+struct RowEpiArgs {
+  const float* row_scale = nullptr;
+  const float* row_coef = nullptr;
+  const __nv_bfloat16* gather_src = nullptr;
+  long long gather_ld = 0;
+  int gather_rows = 0;
+  const long long* targets = nullptr;
+  long long v_offset = 0;
+};
 
 // C[M,N] (+)= A . B^T with optional k-splits; slab workspace is needed when k_splits > 1.
 static size_t store_gemm_slab_bytes(int M, int N, int K, int ctas, int forced_ksplit, int mrep = 1) {
@@ -392,9 +527,14 @@ static size_t store_gemm_slab_bytes(int M, int N, int K, int ctas, int forced_ks
 static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* C, long long ldc,
                           int c_is_f32, int accumulate, int M, int N, int K, int ctas, int group_m, int forced_ksplit,
                           void* slab, size_t slab_bytes, cudaStream_t st, int a_panel_rows = 0, int group_n = 0,
-                          int hint_a = 0, int hint_b = 0, int mrep = 1, int zigzag = 0) {
+                          int hint_a = 0, int hint_b = 0, int mrep = 1, int zigzag = 0, const RowEpiArgs* epi = nullptr) {
   GemmParams p = {};
   p.zigzag = zigzag;
+  if (epi) {
+    p.row_scale = epi->row_scale; p.row_coef = epi->row_coef; p.gather_src = epi->gather_src; p.gather_ld = epi->gather_ld;
+    p.gather_rows = epi->gather_rows; p.targets = epi->targets; p.v_offset = epi->v_offset;
+    if (forced_ksplit > 1) forced_ksplit = 0;   // the uniform split-K reduce does not carry the row epilogue: tail split instead
+  }
   if (ctas != 2) mrep = 1;   // the 256-row variant exists for CTA pairs only
   const int tiles = ceil_div(M, GEMM_BLOCK_M * mrep * ctas) * ceil_div(N, BN);
   // forced_ksplit >= 1: uniform k-splits (1 = none); <= 0: automatic = tail split of the last partial wave
@@ -455,16 +595,18 @@ static int clear_tail_panel(void* panels, int M, int Vloc, cudaStream_t st) {
   return 0;
 }
 static size_t part_bytes(int M, int Vloc) { return align_up((size_t)ceil_div(Vloc, BN) * M * 16, 256); }
+static size_t ref_bytes(int M) { return align_up((size_t)M * 4, 256); }
 
+// forward scratch: [per-tile partials][row references]
 extern "C" size_t b200grpo_lmhead_fwd_workspace(int M, int H, int Vloc) {
   (void)H;
-  return part_bytes(M, Vloc);
+  return part_bytes(M, Vloc) + ref_bytes(M);
 }
 
-// saved-forward state for the recompute-free backward: [per-tile partials][bf16 logits relative to the tile max]
+// saved-forward state for the recompute-free backward: [per-tile partials][row references r][bf16 E = exp(logit/T - r) panels]
 extern "C" size_t b200grpo_lmhead_saved_bytes(int M, int H, int Vloc) {
   (void)H;
-  return part_bytes(M, Vloc) + panel_bytes(M, Vloc);
+  return part_bytes(M, Vloc) + ref_bytes(M) + panel_bytes(M, Vloc);
 }
 
 static int lmhead_fwd_impl(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
@@ -480,26 +622,32 @@ static int lmhead_fwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   GemmParams p = {};
   fill_tiling(p, M, Vloc, H, ctas, max(1, get_tunable(TUNE_FWD_GROUP_M) / mrep), 1, 0, get_tunable(TUNE_HINT_RESIDENT),
               get_tunable(TUNE_HINT_STREAM), mrep);
-  const size_t need = part_bytes(M, Vloc);
+  const size_t n_part = part_bytes(M, Vloc), need = n_part + ref_bytes(M);
   if (!saved && workspace_bytes < need) { set_error("lmhead_fwd: workspace %zu < %zu", workspace_bytes, need); return B200GRPO_EWORKSPACE; }
   p.targets = (const long long*)targets; p.v_offset = v_offset; p.inv_temp = inv_temperature;
-  p.part = (float*)(saved ? saved : workspace);
+  char* base = (char*)(saved ? saved : workspace);
+  p.part = (float*)base;
+  float* row_ref = (float*)(base + n_part);
+  p.row_ref = row_ref;
   cudaStream_t st = (cudaStream_t)stream;
   if (saved) {
-    p.zsave = (__nv_bfloat16*)((char*)saved + need);
+    p.zsave = (__nv_bfloat16*)(base + need);
     if (int e = clear_tail_panel(p.zsave, M, Vloc, st)) return e;
   }
   CUtensorMap ta, tb;
   if (int e = make_ab_maps(&ta, &tb, hidden, ldh, 0, weight, ldw, 0, M, Vloc, H, ctas, mrep)) return e;
   {
     ProfScope ps(PROF_FWD_GEMM, st);
+    row_ref_kernel<<<ceil_div(M, 8), 256, 0, st>>>((const __nv_bfloat16*)hidden, ldh, (const __nv_bfloat16*)weight, ldw,
+                                                   (const long long*)targets, M, H, Vloc, v_offset, inv_temperature, row_ref);
+    count_launch();
     const int e = saved ? dispatch<EPI_FWD_STATS, true>(0, 0, ctas, ta, tb, p, st, mrep)
                         : dispatch<EPI_FWD_STATS, false>(0, 0, ctas, ta, tb, p, st, mrep);
     if (e) return e;
   }
   ProfScope ps(PROF_FWD_MERGE, st);
-  if (stats_multicast) fwd_merge_kernel<true><<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, p.n_blocks, M, (float4*)stats);
-  else fwd_merge_kernel<false><<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, p.n_blocks, M, (float4*)stats);
+  if (stats_multicast) fwd_merge_kernel<true><<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, row_ref, p.n_blocks, M, (float4*)stats);
+  else fwd_merge_kernel<false><<<ceil_div(M, 32), 32 * MG_SLICES, 0, st>>>((const float4*)p.part, row_ref, p.n_blocks, M, (float4*)stats);
   count_launch();
   B200_CUDA_OK(cudaGetLastError());
   return B200GRPO_OK;
@@ -529,17 +677,25 @@ extern "C" int b200grpo_lmhead_finalize(const float* stats, int R, int M, float*
   return B200GRPO_OK;
 }
 
+// backward scratch: [dlogits panels (recompute mode only)][row scale, row coefficient, scaled hidden (saved mode: the
+// entropy-free path)][tail-split / split-K slab]
+static size_t rows_scratch_bytes(int M, int H) { return 2 * align_up((size_t)M * 4, 256) + align_up((size_t)M * H * 2, 256); }
+
 extern "C" size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc, int with_saved) {
   const int ctas = ctas_for(M);
   size_t slab = store_gemm_slab_bytes(M, H, Vloc, ctas, get_tunable(TUNE_DH_KSPLIT), mrep_for(TUNE_DH_BIG_M, ctas));
+  size_t slab_t = store_gemm_slab_bytes(M, H, Vloc, ctas, 0, mrep_for(TUNE_DH_BIG_M, ctas));   // the row-epilogue path forces the tail split
+  if (slab_t > slab) slab = slab_t;
   const size_t slab_dw = store_gemm_slab_bytes(Vloc, H, M, ctas, get_tunable(TUNE_DW_KSPLIT), mrep_for(TUNE_DW_BIG_M, ctas));
   if (slab_dw > slab) slab = slab_dw;   // the two GEMMs run back to back on one stream and share it
-  return (with_saved ? 0 : panel_bytes(M, Vloc)) + slab + 256;
+  return (with_saved ? rows_scratch_bytes(M, H) : panel_bytes(M, Vloc)) + slab + 256;
 }
 
-// stages: B200GRPO_BWD_DLOGITS (form dlogits: in place from the saved logits, or by recomputing them into the
-// workspace), _DH, _DW.  A caller that splits the backward in two calls passes the same saved / workspace buffers to
-// both and B200GRPO_BWD_DLOGITS only to the first.
+// stages: B200GRPO_BWD_DLOGITS (prepare: per-row scales + scaled hidden for the entropy-free path; dlogits in place from the
+// saved exponentials when there is an entropy term; or the recompute GEMM into the workspace), _DH, _DW.  A caller that
+// splits the backward in two calls passes the same saved / workspace buffers to both and B200GRPO_BWD_DLOGITS only to the first.
+// coef_ent == nullptr declares "no gradient through the entropy" (entropy_bonus == 0): with saved exponentials the backward
+// then never forms dlogits (see bwd_rows_kernel).
 static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, int64_t ldw, const int64_t* targets,
                            const float* lse, const float* entropy, const float* coef_lp, const float* coef_ent,
                            const float* grad_scale, int M, int H, int Vloc, int64_t v_offset, float inv_temperature,
@@ -549,8 +705,10 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   const bool form = stages & B200GRPO_BWD_DLOGITS;
   if (!(stages & B200GRPO_BWD_DH)) grad_hidden = nullptr;
   if (!(stages & B200GRPO_BWD_DW)) grad_weight = nullptr;
-  B200_REQUIRE(hidden && weight && workspace, "lmhead_bwd: null pointer");
-  B200_REQUIRE(!form || (targets && lse && entropy && coef_lp && coef_ent), "lmhead_bwd: null per-token input");
+  const bool rows_path = saved && !coef_ent;     // entropy-free + saved exponentials: GEMMs straight on E
+  B200_REQUIRE(hidden && weight && workspace && targets, "lmhead_bwd: null pointer");
+  B200_REQUIRE(!form || (lse && coef_lp && (rows_path || (entropy && coef_ent))), "lmhead_bwd: null per-token input");
+  B200_REQUIRE(saved || coef_ent || !form, "lmhead_bwd: the recompute backward needs coef_ent (pass zeros)");
   B200_REQUIRE(M >= 1 && H >= 8 && Vloc >= 1 && H % 8 == 0, "lmhead_bwd: M=%d H=%d Vloc=%d", M, H, Vloc);
   B200_REQUIRE(!accumulate || grad_weight_is_f32, "lmhead_bwd: accumulate needs an f32 grad_weight");
   const size_t need = b200grpo_lmhead_bwd_workspace(M, H, Vloc, saved != nullptr);
@@ -559,20 +717,32 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   cudaStream_t st = (cudaStream_t)stream;
   __nv_bfloat16* dlog;
   char* slab;
-  if (saved) {  // 1a. saved logits -> dlogits in place (no recompute GEMM)
-    dlog = (__nv_bfloat16*)((char*)saved + part_bytes(M, Vloc));
-    slab = (char*)workspace;
+  float *row_scale = nullptr, *row_coef = nullptr;
+  __nv_bfloat16* hs = nullptr;
+  const float* row_ref = nullptr;
+  if (saved) {
+    row_ref = (const float*)((char*)saved + part_bytes(M, Vloc));
+    dlog = (__nv_bfloat16*)((char*)saved + part_bytes(M, Vloc) + ref_bytes(M));
+    row_scale = (float*)workspace;
+    row_coef = (float*)((char*)workspace + align_up((size_t)M * 4, 256));
+    hs = (__nv_bfloat16*)((char*)workspace + 2 * align_up((size_t)M * 4, 256));
+    slab = (char*)workspace + rows_scratch_bytes(M, H);
   } else {
     dlog = (__nv_bfloat16*)workspace;
     slab = (char*)workspace + panel_bytes(M, Vloc);
   }
-  if (saved && form) {
+  if (rows_path && form) {   // 1a. per-row scale s = -a exp(r - lse), coefficient a, scaled copy of hidden (operand B of dW)
+    ProfScope ps(PROF_DLOGITS_EW, st);
+    bwd_rows_kernel<<<ceil_div(M, 8), 256, 0, st>>>((const __nv_bfloat16*)hidden, ldh, row_ref, lse, coef_lp, grad_scale, inv_temperature,
+                                                    M, H, row_scale, row_coef, hs); count_launch();
+    B200_CUDA_OK(cudaGetLastError());
+  } else if (saved && form) {  // 1b. entropy term present: saved exponentials -> dlogits in place (no recompute GEMM)
     ProfScope ps(PROF_DLOGITS_EW, st);
     dim3 grid(ceil_div(M, DL_ROWS), ceil_div(Vloc, PANEL_W));
-    dlogits_from_saved_kernel<<<grid, DL_THREADS, 0, st>>>(dlog, (const float4*)saved, M, Vloc, (const long long*)targets, v_offset, lse,
+    dlogits_from_saved_kernel<<<grid, DL_THREADS, 0, st>>>(dlog, row_ref, M, Vloc, (const long long*)targets, v_offset, lse,
                                                            entropy, coef_lp, coef_ent, grad_scale, inv_temperature); count_launch();
     B200_CUDA_OK(cudaGetLastError());
-  } else if (form) {      // 1b. recompute logits tile by tile -> bf16 dlogits
+  } else if (form) {      // 1c. recompute logits tile by tile -> bf16 dlogits
     if (int e = clear_tail_panel(dlog, M, Vloc, st)) return e;
     GemmParams p = {};
     fill_tiling(p, M, Vloc, H, ctas, get_tunable(TUNE_FWD_GROUP_M), 1, 0, get_tunable(TUNE_HINT_RESIDENT), get_tunable(TUNE_HINT_STREAM));
@@ -587,15 +757,25 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   const size_t slab_bytes = (char*)workspace + workspace_bytes - slab;
   if (grad_hidden) {  // 2. dH[M,H] = dlogits[M,V] . W[V,H]   (B is MN-major: vocab rows are the K axis)
     ProfScope ps(PROF_BWD_DH, st);
+    RowEpiArgs epi;   // rows path: dH = diag(s) . (E . W) + a * W[target]
+    epi.row_scale = row_scale; epi.row_coef = row_coef; epi.gather_src = (const __nv_bfloat16*)weight; epi.gather_ld = ldw;
+    epi.gather_rows = Vloc; epi.targets = (const long long*)targets; epi.v_offset = v_offset;
     if (int e = run_store_gemm(dlog, 0, 0, weight, ldw, 1, grad_hidden, ldgh, 0, 0, M, H, Vloc, ctas,
                                get_tunable(TUNE_DH_GROUP_M), get_tunable(TUNE_DH_KSPLIT), slab, slab_bytes, st, M, 0,
-                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_STREAM), mrep_for(TUNE_DH_BIG_M, ctas))) return e;
+                               get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_STREAM), mrep_for(TUNE_DH_BIG_M, ctas), 0,
+                               rows_path ? &epi : nullptr)) return e;
   }
   if (grad_weight) {  // 3. dW[V,H] = dlogits^T[V,M] . hidden[M,H]   (both operands MN-major: tokens are the K axis)
     ProfScope ps(PROF_BWD_DW, st);
-    if (int e = run_store_gemm(dlog, 0, 1, hidden, ldh, 1, grad_weight, ldgw, grad_weight_is_f32, accumulate, Vloc, H, M,
+    const void* b_op = rows_path ? (const void*)hs : hidden;        // rows path: dW = E^T . (diag(s) . hidden) + onehot term
+    if (int e = run_store_gemm(dlog, 0, 1, b_op, rows_path ? (long long)H : ldh, 1, grad_weight, ldgw, grad_weight_is_f32, accumulate, Vloc, H, M,
                                ctas, get_tunable(TUNE_DW_GROUP_M), get_tunable(TUNE_DW_KSPLIT), slab, slab_bytes, st, M, get_tunable(TUNE_DW_GROUP_N),
                                get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT), mrep_for(TUNE_DW_BIG_M, ctas), get_tunable(TUNE_DW_ZIGZAG))) return e;
+    if (rows_path) {
+      dw_target_kernel<<<ceil_div(M, 8), 256, 0, st>>>((const __nv_bfloat16*)hidden, ldh, (const long long*)targets, v_offset, Vloc, row_coef,
+                                                       M, H, grad_weight, ldgw, grad_weight_is_f32); count_launch();
+      B200_CUDA_OK(cudaGetLastError());
+    }
   }
   return B200GRPO_OK;
 }

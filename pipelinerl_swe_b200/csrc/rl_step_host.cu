@@ -76,7 +76,8 @@ extern "C" int b200grpo_rl_step_host(const b200grpo_host_batch* b, int L, int H,
   if (e) return e;
   if (grad_weight || grad_hidden_host_bf16) {
     e = b200grpo_lmhead_bwd(w + o.hidden, H, weight, ldw, targets, (const float*)(w + o.lse), (const float*)(w + o.entropy),
-                            (const float*)(w + o.coef_lp), (const float*)(w + o.coef_ent), nullptr, M, H, V, 0,
+                            (const float*)(w + o.coef_lp), (cfg->entropy_coef != 0.f || !o.save) ? (const float*)(w + o.coef_ent) : nullptr,
+                            nullptr, M, H, V, 0,
                             1.0f / temperature, o.save ? (void*)(w + o.saved) : nullptr, (void*)(w + o.ghid), H, grad_weight, H,
                             grad_weight_is_f32, accumulate, w + o.ws_bwd, o.n_bwd, stream);
     if (e) return e;

@@ -133,7 +133,8 @@ class LMHeadLogprobFunction(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, hidden, weight, targets, inv_temperature: float, group=None, v_offset: int = 0, sink: _GradSink | None = None):
+    def forward(ctx, hidden, weight, targets, inv_temperature: float, group=None, v_offset: int = 0, sink: _GradSink | None = None,
+                entropy_grad: bool = True):
         M, H = hidden.shape
         Vloc = weight.shape[0]
         need_bwd = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
@@ -165,14 +166,16 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         logprob, entropy, lse = ops.lmhead_finalize(stats)
         ctx.save_for_backward(hidden, weight, targets, lse, entropy)
         ctx.inv_temperature, ctx.group, ctx.v_offset = inv_temperature, group, v_offset
-        ctx.saved, ctx.chunks, ctx.sink = saved, chunks, sink
+        ctx.saved, ctx.chunks, ctx.sink, ctx.entropy_grad = saved, chunks, sink, bool(entropy_grad)
         return torch.stack((logprob, entropy), dim=1)
 
     @staticmethod
     def backward(ctx, grad_out):
         hidden, weight, targets, lse, entropy = ctx.saved_tensors
         g = grad_out.float()
-        coef_lp, coef_ent = g[:, 0].contiguous(), g[:, 1].contiguous()
+        # entropy_grad False (rl_step with entropy_bonus == 0: K3's dLoss/dentropy is identically zero): the backward runs
+        # its GEMMs straight on the saved exponentials, no [tokens x vocab] dlogits pass
+        coef_lp, coef_ent = g[:, 0].contiguous(), (g[:, 1].contiguous() if ctx.entropy_grad else None)
         need_h, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         saved, ctx.saved = ctx.saved, None  # consumed in place by the backward; a second backward recomputes
         chunks, group = ctx.chunks, ctx.group
@@ -199,8 +202,8 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         overlap = group is not None and need_h and need_w
         pending = done = None
         for ci, (r0, r1) in enumerate(chunks):
-            a = (hidden[r0:r1], weight, targets[r0:r1], lse[r0:r1], entropy[r0:r1], coef_lp[r0:r1], coef_ent[r0:r1],
-                 ctx.inv_temperature, ctx.v_offset)
+            a = (hidden[r0:r1], weight, targets[r0:r1], lse[r0:r1], entropy[r0:r1], coef_lp[r0:r1],
+                 None if coef_ent is None else coef_ent[r0:r1], ctx.inv_temperature, ctx.v_offset)
             kw = dict(saved=saved if ci == 0 else None, grad_hidden_out=gh[r0:r1] if need_h else None, grad_weight_out=gw)
             acc = need_w and (acc_first or ci > 0)
             if overlap and ci == len(chunks) - 1:
@@ -226,12 +229,12 @@ class LMHeadLogprobFunction(torch.autograd.Function):
             gh = gh.clone()   # the symmetric buffer is reused by the next micro-batch
         if need_w and not acc_first:
             gw_ret = gw if gw.dtype == torch.bfloat16 else gw.to(torch.bfloat16)
-        return gh, gw_ret, None, None, None, None, None
+        return gh, gw_ret, None, None, None, None, None, None
 
 
 def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch.Tensor, temperature: float, group=None,
                     v_offset: int = 0, labels: torch.Tensor | None = None, boundary_ids: torch.Tensor | None = None,
-                    boundary_labels: torch.Tensor | None = None) -> torch.Tensor:
+                    boundary_labels: torch.Tensor | None = None, entropy_grad: bool = True) -> torch.Tensor:
     """hidden [B,L,H], input_ids [B,L] -> f32 [B,L,2]: (logprob of input_ids[t+1], entropy) per position.
 
     Position L-1 of every row has no next token: it is scored against token 0 and the
@@ -257,10 +260,10 @@ def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch
         out = torch.zeros(B * L, 2, dtype=torch.float32, device=hidden.device)
         if idx.numel() > 0:
             part = LMHeadLogprobFunction.apply(h2.index_select(0, idx), w.contiguous(), targets.index_select(0, idx), inv_t, group,
-                                               v_offset, sink)
+                                               v_offset, sink, entropy_grad)
             out = out.index_copy(0, idx, part)               # autograd scatters the gradient rows back (zeros elsewhere)
         return out.reshape(B, L, 2)
-    out = LMHeadLogprobFunction.apply(h2.contiguous(), w.contiguous(), targets, inv_t, group, v_offset, sink)
+    out = LMHeadLogprobFunction.apply(h2.contiguous(), w.contiguous(), targets, inv_t, group, v_offset, sink, entropy_grad)
     return out.reshape(B, L, 2)
 
 
@@ -274,6 +277,7 @@ class LogprobRequest:
     labels: torch.Tensor | None = None   # only read when set_skip_masked_tokens(True)
     boundary_ids: torch.Tensor | None = None      # [B] next-slice first token (types.make_slices(carry_boundary_target=True))
     boundary_labels: torch.Tensor | None = None
+    entropy_grad: bool = True                     # False: the caller guarantees dLoss/dentropy == 0 (entropy_bonus == 0)
 
 
 _tls = threading.local()
@@ -323,7 +327,7 @@ class FusedLMHead(nn.Module):
         if group is None and getattr(self, "vocab_group", None) is not None:   # sharded head declared at install time
             group, v_offset = self.vocab_group, self.v_offset
         return lmhead_logprobs(hidden, self.weight, req.input_ids, req.temperature, group, v_offset, req.labels,
-                               req.boundary_ids, req.boundary_labels)
+                               req.boundary_ids, req.boundary_labels, req.entropy_grad)
 
 
 def _check_fusable(linear: nn.Module) -> None:

@@ -91,11 +91,17 @@ def lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, inv_tem
                grad_hidden_out: torch.Tensor | None = None):
     """K2: (grad_hidden bf16 [M,H] | None, grad_weight [V,H] | None).  ``saved`` (from the forward) is consumed.
 
+    ``coef_ent=None`` declares that no gradient flows through the entropy (``entropy_bonus == 0``): with ``saved`` the
+    backward then runs its two GEMMs straight on the forward's saved exponentials (no [tokens x vocab] dlogits pass).
+
     ``stages`` (``_abi.BWD_*`` bits) splits the backward: a first call with ``BWD_DLOGITS | BWD_DH`` and a second with
     ``BWD_DW`` (same ``saved``, nothing re-formed) let the caller put a collective on grad_hidden in between."""
     _req(hidden, torch.bfloat16, "hidden"); _req(weight, torch.bfloat16, "weight"); _req(targets, torch.int64, "targets")
+    if coef_ent is None and saved is None:
+        coef_ent = torch.zeros_like(coef_lp)     # the recompute GEMM's epilogue takes the coefficient explicitly
     for name, t in (("lse", lse), ("entropy", entropy), ("coef_lp", coef_lp), ("coef_ent", coef_ent)):
-        _req(t, torch.float32, name)
+        if t is not None:
+            _req(t, torch.float32, name)
     M, H = hidden.shape
     V = weight.shape[0]
     if stages is not None:
@@ -111,7 +117,7 @@ def lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, inv_tem
     n = lib().b200grpo_lmhead_bwd_workspace(M, H, V, int(saved is not None))
     ws = _workspace(hidden.device, n, "dlogits")
     args = (hidden.data_ptr(), H, weight.data_ptr(), H, targets.data_ptr(), lse.data_ptr(), entropy.data_ptr(), coef_lp.data_ptr(),
-            coef_ent.data_ptr(), _ptr(grad_scale), M, H, V, v_offset, float(inv_temperature), _ptr(saved), _ptr(gh), H, _ptr(gw), H,
+            _ptr(coef_ent), _ptr(grad_scale), M, H, V, v_offset, float(inv_temperature), _ptr(saved), _ptr(gh), H, _ptr(gw), H,
             int(gw is not None and gw.dtype == torch.float32), int(accumulate))
     if stages is None:
         check(lib().b200grpo_lmhead_bwd(*args, ws.data_ptr(), ws.numel(), _stream()))

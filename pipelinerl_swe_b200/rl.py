@@ -158,7 +158,8 @@ def _forward_loss(model, batch, current_step: int, max_step: int, config, vocab_
     req = LogprobRequest(b["input_ids"], float(config.temperature), labels=b["labels"],
                          group=getattr(head, "vocab_group", None), v_offset=getattr(head, "v_offset", 0),
                          boundary_ids=None if b["boundary"] is None else b["boundary"]["input_ids"].reshape(-1),
-                         boundary_labels=None if b["boundary"] is None else b["boundary"]["labels"].reshape(-1))
+                         boundary_labels=None if b["boundary"] is None else b["boundary"]["labels"].reshape(-1),
+                         entropy_grad=cfg.entropy_coef != 0.0)   # K3's dLoss/dentropy = -w * entropy_coef: identically zero without a bonus
     with logprob_request(req):
         outputs = model(**model_inputs)
     lp_ent = outputs.logits

@@ -106,7 +106,8 @@ def check_lmhead_at_shape(hidden, weight_full, targets, inv_temp, c_lp, c_ent, *
                           accumulate_steps=2, ref=None) -> dict:
     """Run K1 -> finalize -> K2 of this library with the DEFAULT tunables on (a vocab shard of) the given problem and
     compare with ``reference_lmhead``.  ``accumulate_steps`` backward passes add into a non-zero f32 gradient
-    (``red.global.add`` path).  Returns the error record; ``ok`` applies the north-star tolerances."""
+    (``red.global.add`` path).  ``c_ent=None``: the entropy-free backward (GEMMs straight on the saved exponentials); ``ref``
+    must then come from zero entropy coefficients.  Returns the error record; ``ok`` applies the north-star tolerances."""
     from pipelinerl_swe_b200 import ops
     M, H = hidden.shape
     V = weight_full.shape[0]
@@ -115,7 +116,8 @@ def check_lmhead_at_shape(hidden, weight_full, targets, inv_temp, c_lp, c_ent, *
     dev = hidden.device
     w = weight_full[v_lo:v_hi] if not sharded else weight_full[v_lo:v_hi].contiguous()
     if ref is None:
-        ref = reference_lmhead(hidden, weight_full, targets, inv_temp, c_lp, c_ent, v_lo, v_hi)
+        ref = reference_lmhead(hidden, weight_full, targets, inv_temp, c_lp, c_ent if c_ent is not None else torch.zeros_like(c_lp),
+                               v_lo, v_hi)
     g = torch.Generator(device=dev).manual_seed(17)
     scale = float(ref["dW"].abs().max())
     g0 = torch.randn(v_hi - v_lo, H, device=dev, generator=g) * scale      # the gradient already in .grad
@@ -145,7 +147,7 @@ def check_lmhead_at_shape(hidden, weight_full, targets, inv_temp, c_lp, c_ent, *
     out["dW_first_tile_rel"] = float((got_dw[:256] - ref["dW"][:256]).abs().max() / (ref["dW"].abs().max() + 1e-30))
     out["dH_tail_rows_rel"] = float((gh[-512:].float() - ref["dH"][-512:]).abs().max() / (ref["dH"].abs().max() + 1e-30))
     out["accumulate_steps"] = accumulate_steps
-    out["mode"] = "saved" if save else "recompute"
+    out["mode"] = ("saved" if save else "recompute") + ("" if c_ent is not None else ", entropy-free backward")
     ok = out["dH_rel"] < GRAD_RTOL and out["dW_rel"] < GRAD_RTOL
     if not sharded:
         ok = ok and out["lp_rel"] < LP_RTOL and out["ent_rel"] < LP_RTOL

@@ -86,11 +86,13 @@ def test_rl_step_vs_reference_golden(name):
 # ---------------------------------------------------------------------------------------------
 # K1 / K2 at the real vocab size vs the oracle (fp32 math on the same bf16 values)
 # ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("save", [False, True])
+@pytest.mark.parametrize("save", [False, True, "no_entropy"])
 @pytest.mark.parametrize("two_cta", [0, 1])
 @pytest.mark.parametrize("T,H,V,temp", [(513, 896, 151936, 1.0), (300, 1536, 152064, 0.7), (260, 256, 1000 + 8, 1.3)])
 def test_lmhead_fwd_bwd_vs_oracle(T, H, V, temp, two_cta, save):
-    """save=False: backward recomputes the logits; save=True: forward keeps bf16 logits (tile-max relative)."""
+    """save=False: backward recomputes the logits; save=True: forward keeps bf16 exponentials (relative to a per-row reference)
+    and the backward turns them into dlogits in place; "no_entropy": no gradient through the entropy -> the backward's GEMMs
+    read the saved exponentials directly (row-scale epilogue, scaled hidden, sparse target rows; bf16 atomic path of dW)."""
     from pipelinerl_swe_b200 import _abi, ops
     _abi.set_tunable("two_cta", two_cta)
     try:
@@ -101,7 +103,8 @@ def test_lmhead_fwd_bwd_vs_oracle(T, H, V, temp, two_cta, save):
         hr, wr = hidden.float().requires_grad_(True), weight.float().requires_grad_(True)
         lp_ref, ent_ref = oracle.oracle_logprobs_entropy(hr, wr, ids, temp)
         c_lp = torch.randn(T - 1, generator=g) * 0.1
-        c_ent = torch.randn(T - 1, generator=g) * 0.01
+        c_lp[::7] = 0.0                                                     # unlabelled positions carry a zero coefficient
+        c_ent = torch.randn(T - 1, generator=g) * 0.01 * (save != "no_entropy")
         ((lp_ref * c_lp).sum() + (ent_ref * c_ent).sum()).backward()
 
         d = _dev()
@@ -111,9 +114,11 @@ def test_lmhead_fwd_bwd_vs_oracle(T, H, V, temp, two_cta, save):
         lp, ent, lse = ops.lmhead_finalize(stats)
         assert float((lp.cpu() - lp_ref.detach()).abs().max()) <= LP_RTOL * float(lp_ref.detach().abs().max())
         assert float((ent.cpu() - ent_ref.detach()).abs().max()) <= LP_RTOL * float(ent_ref.detach().abs().max())
-        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp.to(d), c_ent.to(d), 1.0 / temp, saved=saved)
+        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp.to(d), None if save == "no_entropy" else c_ent.to(d), 1.0 / temp, saved=saved)
         assert _rel(gh, hr.grad[:-1]) < GRAD_RTOL
         assert _rel(gw, wr.grad) < GRAD_RTOL
+        if save == "no_entropy":
+            assert torch.count_nonzero(gh[::7]) == 0                       # zero coefficient -> exactly zero gradient row
     finally:
         _abi.set_tunable("two_cta", 1)
 

@@ -48,19 +48,27 @@ def test_fast_reference_is_the_fp32_reference(name):
     assert sp.fast_reference_is_fp32(p["hidden"], p["weight"], p["targets"], p["inv_temp"]) < 2e-4   # |logprob| ~ 12: 2e-5 relative, the summation-order noise of the plain fp32 matmul itself
 
 
-@pytest.mark.parametrize("mode", ["saved", "recompute"])
+@pytest.mark.parametrize("mode", ["saved", "saved_no_entropy", "recompute"])
 @pytest.mark.parametrize("name", ["c3", "c4"])
 def test_lmhead_fwd_bwd_at_benchmarked_shape(name, mode):
+    """saved: entropy coefficients present -> dlogits pass on the saved exponentials + two GEMMs; saved_no_entropy: what the
+    benchmarked config runs (entropy_bonus == 0) -> the GEMMs read the saved exponentials directly (row-scale epilogue in dH,
+    pre-scaled hidden + sparse target rows in dW); recompute: third GEMM."""
     p = _problem(name)
-    rec = sp.check_lmhead_at_shape(p["hidden"], p["weight"], p["targets"], p["inv_temp"], p["c_lp"], p["c_ent"],
-                                   save=(mode == "saved"), ref=p["ref"])
+    if mode == "saved_no_entropy":
+        if "ref0" not in p:
+            p["ref0"] = sp.reference_lmhead(p["hidden"], p["weight"], p["targets"], p["inv_temp"], p["c_lp"], torch.zeros_like(p["c_lp"]))
+        rec = sp.check_lmhead_at_shape(p["hidden"], p["weight"], p["targets"], p["inv_temp"], p["c_lp"], None, save=True, ref=p["ref0"])
+    else:
+        rec = sp.check_lmhead_at_shape(p["hidden"], p["weight"], p["targets"], p["inv_temp"], p["c_lp"], p["c_ent"],
+                                       save=(mode == "saved"), ref=p["ref"])
     print(name, mode, rec)
     assert rec["lp_rel"] < sp.LP_RTOL and rec["ent_rel"] < sp.LP_RTOL, rec
     assert rec["dH_rel"] < sp.GRAD_RTOL and rec["dW_rel"] < sp.GRAD_RTOL, rec
     assert rec["ok"], rec
 
 
-@pytest.mark.parametrize("mode", ["saved", "recompute"])
+@pytest.mark.parametrize("mode", ["saved", "saved_no_entropy", "recompute"])
 @pytest.mark.parametrize("rank", [0, 7])
 def test_lmhead_c4_vocab_shard_of_eight(rank, mode):
     """Config 4's per-rank problem (Vloc = 19008 rows at v_offset = rank * 19008): shard dW and the dH partial against the
@@ -69,9 +77,11 @@ def test_lmhead_c4_vocab_shard_of_eight(rank, mode):
     p = _problem("c4")
     V = p["weight"].shape[0]
     lo, hi = shard_range(V, 8, rank)
-    ref = sp.reference_lmhead(p["hidden"], p["weight"], p["targets"], p["inv_temp"], p["c_lp"], p["c_ent"], lo, hi)
-    rec = sp.check_lmhead_at_shape(p["hidden"], p["weight"], p["targets"], p["inv_temp"], p["c_lp"], p["c_ent"],
-                                   save=(mode == "saved"), v_lo=lo, v_hi=hi, ref=ref)
+    c_ent = None if mode == "saved_no_entropy" else p["c_ent"]
+    ref = sp.reference_lmhead(p["hidden"], p["weight"], p["targets"], p["inv_temp"], p["c_lp"],
+                              c_ent if c_ent is not None else torch.zeros_like(p["c_lp"]), lo, hi)
+    rec = sp.check_lmhead_at_shape(p["hidden"], p["weight"], p["targets"], p["inv_temp"], p["c_lp"], c_ent,
+                                   save=(mode != "recompute"), v_lo=lo, v_hi=hi, ref=ref)
     print("c4 shard", rank, mode, rec)
     assert rec["ok"], rec
 
