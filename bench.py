@@ -916,8 +916,9 @@ def run_b200(args):
                        **({"exchange": "nvswitch multicast kernels (SymmetricExchange)" if ex else "nccl"} if is_vp else {}),
                        "grad_weight": "f32 accumulated across steps", "l2": "inputs exceed L2 (lm_head weight %.2f GB)" % (wbytes / 1e9),
                        "bwd_mode": args.mode,
-                       "bwd_mode_note": ("saved: the forward keeps bf16 logits (relative to their tile max) until the backward: %.2f GB at this T, "
-                                         "so 'logits never materialised' holds for the `recompute` record, not for this headline" % ((-(-V // 256) * 512 * (T - 1)) / 1e9))
+                       "bwd_mode_note": ("saved: the forward keeps bf16 exp(logit/T - row reference) until the backward: %.2f GB at this T, so 'logits never "
+                                         "materialised' holds for the `recompute` record, not for this headline; with entropy_bonus == 0 (this config) "
+                                         "the backward's two GEMMs read those panels directly -- no dlogits pass" % ((-(-V // 256) * 512 * (T - 1)) / 1e9))
                        if args.mode == "saved" else "recompute: nothing of size T x V survives the forward",
                        "tunables": args.tunable, "tokens_per_gpu_per_sec": value / world if not is_vp else value},
             "parity": parity, "roofline": roofline, ("recompute" if args.mode == "saved" else "saved"): other,

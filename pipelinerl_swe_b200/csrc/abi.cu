@@ -59,10 +59,12 @@ int check_device_sm100() {
 //   dw_zigzag: odd tiles of a cluster walk the token (K) axis of dW backwards, so a wave starts on the rows of `hidden`
 //   the previous wave touched last (L2 reuse instead of a DRAM re-read).  Ships on: dW DRAM reads 12.0 -> 10.4 GB, dW -1 %
 //   same-box (profiles/r01/dw_zigzag_ab.md).
+//   rows_path: 1 = an entropy-free backward (coef_ent == NULL) runs its GEMMs on the saved exponentials; 0 = it forms dlogits
+//   in place first like the entropy path (A/B switch).
 static const char* const g_tunable_names[TUNE_COUNT] = {"two_cta", "dh_ksplit", "dw_ksplit", "tail_split", "fwd_group_m", "dh_group_m",
                                                         "dw_group_m", "dw_group_n", "save_logits", "hint_resident", "hint_stream",
-                                                        "dh_big_m", "dw_big_m", "gemm_big_m", "fwd_big_m", "dw_zigzag"};
-static int g_tunables[TUNE_COUNT] = {1, 0, 0, 1, 16, 4, 1, 0, 1, 0, 0, 1, 0, 0, 0, 1};
+                                                        "dh_big_m", "dw_big_m", "gemm_big_m", "fwd_big_m", "dw_zigzag", "rows_path"};
+static int g_tunables[TUNE_COUNT] = {1, 0, 0, 1, 16, 4, 1, 0, 1, 0, 0, 1, 0, 0, 0, 1, 1};
 int get_tunable(int id) { return g_tunables[id]; }
 
 // ---- profiling ring (diagnostic; single-threaded use) -------------------------------------

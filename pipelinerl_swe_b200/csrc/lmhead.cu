@@ -415,30 +415,53 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const __nv_bfloat16* __re
   }
 }
 
-// dW[target(t) - v_offset, :] += a_t * hidden[t, :]   for the rows whose target lies in this rank's vocab rows (the onehot term).
-// One warp per token row; f32 gradients take red.global.add (several tokens may share a target), bf16 gradients an atomic
-// bf16x2 add.
+// dW[v, :] += sum over the tokens t with target(t) == v of a_t * hidden[t, :]   (the onehot term of the entropy-free backward).
+// Deterministic: one warp per token row scans the target column (64 KB at T=8192, L2 resident); the FIRST token of every
+// distinct target is its leader and folds all tokens of that target in token order into an f32 row in shared memory, then
+// updates the gradient row once -- every element of dW is touched at most once per launch, whatever the multiplicity of a
+// token in the micro-batch (hot tokens repeat hundreds of times in real text), and no atomics are involved.
 __global__ void __launch_bounds__(256) dw_target_kernel(const __nv_bfloat16* __restrict__ hidden, long long ldh, const long long* __restrict__ targets,
                                                         long long v_offset, int Vloc, const float* __restrict__ row_coef, int M, int H,
                                                         void* grad_weight, long long ldgw, int gw_is_f32) {
-  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  extern __shared__ float dwt_acc[];                      // [warps][H]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + warp;
   if (row >= M) return;
-  const float a = row_coef[row];
-  const long long t = targets[row] - v_offset;
-  if (a == 0.f || t < 0 || t >= Vloc) return;
-  const __nv_bfloat16* h = hidden + (long long)row * ldh;
+  const long long tg = targets[row];
+  const long long t = tg - v_offset;
+  if (row_coef[row] == 0.f || t < 0 || t >= Vloc) return;
+  float* acc = dwt_acc + (size_t)warp * H;
+  bool zeroed = false;
+  for (int j0 = 0; j0 < M; j0 += 32) {                    // warp-uniform control flow throughout
+    const int j = j0 + lane;
+    const bool hit = j < M && __ldg(targets + j) == tg && __ldg(row_coef + j) != 0.f;
+    unsigned m = __ballot_sync(0xffffffffu, hit);
+    if (!m) continue;
+    if (!zeroed) {
+      if (j0 + __ffs(m) - 1 != row) return;               // an earlier token owns this target
+      for (int k = lane; k < H; k += 32) acc[k] = 0.f;
+      zeroed = true;
+    }
+    while (m) {
+      const int jj = j0 + __ffs(m) - 1;
+      m &= m - 1;
+      const float a = __ldg(row_coef + jj);
+      const __nv_bfloat16* h = hidden + (long long)jj * ldh;
+      for (int k = lane * 2; k < H; k += 64) {
+        const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(h + k));
+        acc[k] = fmaf(a, f.x, acc[k]);
+        acc[k + 1] = fmaf(a, f.y, acc[k + 1]);
+      }
+    }
+  }
   if (gw_is_f32) {
     float* g = reinterpret_cast<float*>(grad_weight) + t * ldgw;
-    for (int k = lane * 2; k < H; k += 64) {
-      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(h + k));
-      atomicAdd(g + k, a * f.x);
-      atomicAdd(g + k + 1, a * f.y);
-    }
+    for (int k = lane * 2; k < H; k += 64) { g[k] += acc[k]; g[k + 1] += acc[k + 1]; }
   } else {
     __nv_bfloat16* g = reinterpret_cast<__nv_bfloat16*>(grad_weight) + t * ldgw;
     for (int k = lane * 2; k < H; k += 64) {
-      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(h + k));
-      atomicAdd(reinterpret_cast<__nv_bfloat162*>(g + k), __floats2bfloat162_rn(a * f.x, a * f.y));
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(g + k));
+      *reinterpret_cast<__nv_bfloat162*>(g + k) = __floats2bfloat162_rn(f.x + acc[k], f.y + acc[k + 1]);
     }
   }
 }
@@ -705,9 +728,9 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   const bool form = stages & B200GRPO_BWD_DLOGITS;
   if (!(stages & B200GRPO_BWD_DH)) grad_hidden = nullptr;
   if (!(stages & B200GRPO_BWD_DW)) grad_weight = nullptr;
-  const bool rows_path = saved && !coef_ent;     // entropy-free + saved exponentials: GEMMs straight on E
+  const bool rows_path = saved && !coef_ent && get_tunable(TUNE_ROWS_PATH);   // entropy-free + saved exponentials: GEMMs straight on E
   B200_REQUIRE(hidden && weight && workspace && targets, "lmhead_bwd: null pointer");
-  B200_REQUIRE(!form || (lse && coef_lp && (rows_path || (entropy && coef_ent))), "lmhead_bwd: null per-token input");
+  B200_REQUIRE(!form || (lse && coef_lp && ((saved && !coef_ent) || (entropy && coef_ent))), "lmhead_bwd: null per-token input");
   B200_REQUIRE(saved || coef_ent || !form, "lmhead_bwd: the recompute backward needs coef_ent (pass zeros)");
   B200_REQUIRE(M >= 1 && H >= 8 && Vloc >= 1 && H % 8 == 0, "lmhead_bwd: M=%d H=%d Vloc=%d", M, H, Vloc);
   B200_REQUIRE(!accumulate || grad_weight_is_f32, "lmhead_bwd: accumulate needs an f32 grad_weight");
@@ -730,6 +753,11 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   } else {
     dlog = (__nv_bfloat16*)workspace;
     slab = (char*)workspace + panel_bytes(M, Vloc);
+  }
+  if (saved && !coef_ent && !rows_path) {   // A/B switch: the entropy path with zero entropy coefficients (row_coef region as zeros)
+    if (form) B200_CUDA_OK(cudaMemsetAsync(row_coef, 0, (size_t)M * 4, st));
+    coef_ent = row_coef;
+    if (!entropy) entropy = row_coef;
   }
   if (rows_path && form) {   // 1a. per-row scale s = -a exp(r - lse), coefficient a, scaled copy of hidden (operand B of dW)
     ProfScope ps(PROF_DLOGITS_EW, st);
@@ -772,8 +800,17 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
                                ctas, get_tunable(TUNE_DW_GROUP_M), get_tunable(TUNE_DW_KSPLIT), slab, slab_bytes, st, M, get_tunable(TUNE_DW_GROUP_N),
                                get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT), mrep_for(TUNE_DW_BIG_M, ctas), get_tunable(TUNE_DW_ZIGZAG))) return e;
     if (rows_path) {
-      dw_target_kernel<<<ceil_div(M, 8), 256, 0, st>>>((const __nv_bfloat16*)hidden, ldh, (const long long*)targets, v_offset, Vloc, row_coef,
-                                                       M, H, grad_weight, ldgw, grad_weight_is_f32); count_launch();
+      int warps = 8;                                          // f32 row per warp in shared memory: 8 x H x 4 B (115 KB at H = 3584)
+      while (warps > 1 && (size_t)warps * H * 4 > 200 * 1024) warps >>= 1;
+      B200_REQUIRE((size_t)warps * H * 4 <= 200 * 1024, "lmhead_bwd: hidden size %d too large for the target-row kernel", H);
+      static bool configured = false;
+      if (!configured) {
+        B200_CUDA_OK(cudaFuncSetAttribute(dw_target_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = true;
+      }
+      dw_target_kernel<<<ceil_div(M, warps), warps * 32, (size_t)warps * H * 4, st>>>(
+          (const __nv_bfloat16*)hidden, ldh, (const long long*)targets, v_offset, Vloc, row_coef, M, H, grad_weight, ldgw,
+          grad_weight_is_f32); count_launch();
       B200_CUDA_OK(cudaGetLastError());
     }
   }
