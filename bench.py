@@ -64,6 +64,7 @@ def parse_args():
     ap.add_argument("--no-recompute", action="store_true", help="skip the recompute-mode sub-record")
     ap.add_argument("--no-vocab-record", action="store_true", help="N>1: skip the config-4 vocab-parallel sub-record")
     ap.add_argument("--no-weight-record", action="store_true", help="N>1: skip the config-5 weight-broadcast sub-record")
+    ap.add_argument("--no-other-configs", action="store_true", help="N=1: skip the short C1 / C2 / C4-unsharded records")
     ap.add_argument("--cpu-budget-s", type=float, default=0.0, help="wall-clock budget of the CPU arm (0 = auto)")
     ap.add_argument("--exchange", default="symm", choices=["nccl", "symm"],
                     help="vocab-parallel transport: NCCL, or this library's NVSwitch multicast kernels (SymmetricExchange)")
@@ -717,6 +718,31 @@ def vocab_parallel_record(args, dev, rank, world, tm: Timer, peaks) -> dict:
     return rec
 
 
+def other_configs_record(args, dev, tm, peaks) -> dict:
+    """N=1: the other BASELINE configs that fit one GPU (C1 0.5B shape, C2 1.5B shape, C4 32B shape unsharded), each gated on
+    the same parity check and timed for a short run, so that one bench line carries every single-GPU configuration."""
+    import torch
+    out = {}
+    for name in ("c1", "c2", "c4"):
+        if name == args.config:
+            continue
+        try:
+            wl = DeviceWorkload(name, dev, 0, 1, mode=args.mode, keep_full=True)
+            par = None if args.no_parity else wl.parity()
+            K = min(args.steps, 16)
+            ms_total, per_tag, n_launch, metrics, _, _ = tm.time_steps(wl, K, 3)
+            r = roofline_record(per_tag, ms_total / K, wl.T, wl.H, wl.Vloc, peaks, 1)
+            out[name] = {"workload": wl.desc, "value": wl.T * K / (ms_total * 1e-3), "unit": "tokens/s", "ms_per_step": ms_total / K, "steps": K,
+                         "frac": r["frac"], "frac_of_burst_peak": r["frac_of_burst_peak"], "achieved_tflops": r["achieved"],
+                         "kernels_ms_per_step": r["kernels_ms_per_step"],
+                         "parity": None if par is None else {k: par[k] for k in ("lp_rel", "ent_rel", "dH_rel", "dW_rel", "ok")}}
+            del wl
+        except Exception as e:  # noqa: BLE001  -- a side record must never take the bench line down
+            out[name] = {"unavailable": repr(e)[:200]}
+        torch.cuda.empty_cache()
+    return out
+
+
 def weight_broadcast_record(dev, rank, world) -> dict:
     """N>1: BASELINE config 5 -- Qwen2.5-7B bf16 parameters (15.2 GB, 339 tensors) from trainer rank 0 to the N-1 other GPUs
     (the receive_weight_update path, vllm1.py:81-94): the reference's per-parameter loop, the bucketed NCCL path and the
@@ -886,6 +912,13 @@ def run_b200(args):
         cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "tokens_per_step_sample", "same_config")}
         del arm
 
+    # ---------------- N=1: the other single-GPU configurations, short runs ----------------
+    others = None
+    if world == 1 and not args.no_other_configs:
+        wl.saved = None
+        torch.cuda.empty_cache()
+        others = other_configs_record(args, dev, tm, peaks)
+
     # ---------------- N>1: config 4 vocab-parallel (the path that communicates) ----------------
     vp = None
     if world > 1 and not wl.vocab_parallel and not args.no_vocab_record:
@@ -923,7 +956,7 @@ def run_b200(args):
                        "tunables": args.tunable, "tokens_per_gpu_per_sec": value / world if not is_vp else value},
             "parity": parity, "roofline": roofline, ("recompute" if args.mode == "saved" else "saved"): other,
             "cpu_baseline": cpu, "torch_gpu_baseline": torch_gpu, "rl_step_api": api, "e2e": e2e,
-            "vocab_parallel": vp, "weight_broadcast": wb, "gpu_launches": int(round(launches_per_step * K)),
+            "other_configs": others, "vocab_parallel": vp, "weight_broadcast": wb, "gpu_launches": int(round(launches_per_step * K)),
             "gpu_launches_per_step": launches_per_step, "clocks": clocks.summary(),
         }
         print(json.dumps(line), flush=True)

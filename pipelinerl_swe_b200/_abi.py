@@ -12,7 +12,7 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200grpo.so")
+LIB_PATH = os.environ.get("B200GRPO_LIB_PATH") or os.path.join(_HERE, "libb200grpo.so")   # the override serves same-box A/B runs of two builds
 M_COUNT = 40  # B200GRPO_M_COUNT
 
 # metric slots (enum in include/b200grpo.h)

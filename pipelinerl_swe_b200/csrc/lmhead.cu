@@ -390,13 +390,18 @@ __global__ void __launch_bounds__(DL_THREADS) dlogits_from_saved_kernel(
 __global__ void __launch_bounds__(256) bwd_rows_kernel(const __nv_bfloat16* __restrict__ hidden, long long ldh, const float* __restrict__ row_ref,
                                                        const float* __restrict__ lse, const float* __restrict__ coef_lp,
                                                        const float* __restrict__ grad_scale, float inv_temp, int M, int H,
-                                                       float* __restrict__ row_scale, float* __restrict__ row_coef,
+                                                       const long long* __restrict__ targets, long long v_offset, int Vloc,
+                                                       float* __restrict__ row_scale, float* __restrict__ row_coef, int* __restrict__ row_key,
                                                        __nv_bfloat16* __restrict__ hs) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= M) return;
   const float a = coef_lp[row] * (grad_scale ? *grad_scale : 1.0f) * inv_temp;
   const float sc = a != 0.f ? -a * __expf(row_ref[row] - lse[row]) : 0.f;
-  if (lane == 0) { row_scale[row] = sc; row_coef[row] = a; }
+  if (lane == 0) {
+    row_scale[row] = sc; row_coef[row] = a;
+    const long long t = targets[row] - v_offset;          // key of the onehot term: local target row, or -1 when there is none
+    row_key[row] = (a != 0.f && t >= 0 && t < Vloc) ? (int)t : -1;
+  }
   if (!hs) return;
   const __nv_bfloat16* h = hidden + (long long)row * ldh;
   __nv_bfloat16* o = hs + (long long)row * H;
@@ -415,50 +420,102 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const __nv_bfloat16* __re
   }
 }
 
-// dW[v, :] += sum over the tokens t with target(t) == v of a_t * hidden[t, :]   (the onehot term of the entropy-free backward).
-// Deterministic: one warp per token row scans the target column (64 KB at T=8192, L2 resident); the FIRST token of every
-// distinct target is its leader and folds all tokens of that target in token order into an f32 row in shared memory, then
-// updates the gradient row once -- every element of dW is touched at most once per launch, whatever the multiplicity of a
-// token in the micro-batch (hot tokens repeat hundreds of times in real text), and no atomics are involved.
-__global__ void __launch_bounds__(256) dw_target_kernel(const __nv_bfloat16* __restrict__ hidden, long long ldh, const long long* __restrict__ targets,
-                                                        long long v_offset, int Vloc, const float* __restrict__ row_coef, int M, int H,
-                                                        void* grad_weight, long long ldgw, int gw_is_f32) {
-  extern __shared__ float dwt_acc[];                      // [warps][H]
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * (blockDim.x >> 5) + warp;
-  if (row >= M) return;
-  const long long tg = targets[row];
-  const long long t = tg - v_offset;
-  if (row_coef[row] == 0.f || t < 0 || t >= Vloc) return;
-  float* acc = dwt_acc + (size_t)warp * H;
-  bool zeroed = false;
-  for (int j0 = 0; j0 < M; j0 += 32) {                    // warp-uniform control flow throughout
-    const int j = j0 + lane;
-    const bool hit = j < M && __ldg(targets + j) == tg && __ldg(row_coef + j) != 0.f;
-    unsigned m = __ballot_sync(0xffffffffu, hit);
-    if (!m) continue;
-    if (!zeroed) {
-      if (j0 + __ffs(m) - 1 != row) return;               // an earlier token owns this target
-      for (int k = lane; k < H; k += 32) acc[k] = 0.f;
-      zeroed = true;
-    }
-    while (m) {
-      const int jj = j0 + __ffs(m) - 1;
-      m &= m - 1;
-      const float a = __ldg(row_coef + jj);
-      const __nv_bfloat16* h = hidden + (long long)jj * ldh;
-      for (int k = lane * 2; k < H; k += 64) {
-        const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(h + k));
-        acc[k] = fmaf(a, f.x, acc[k]);
-        acc[k + 1] = fmaf(a, f.y, acc[k + 1]);
+// dW[v, :] += sum over the tokens t with key(t) == v of a_t * hidden[t, :]   (the onehot term of the entropy-free backward;
+// key = local target row, -1 for tokens without one).  Deterministic and atomic-free: one warp per token row; the block
+// stages the key column through shared memory (8192 keys per trip, every load in flight at once) and each warp scans it four
+// keys per lane; the FIRST token of every distinct key is its leader and folds all tokens of that key, in token order, into
+// an f32 row in shared memory, then updates the gradient row once -- every element of dW is touched at most once per
+// launch whatever the multiplicity of a token in the micro-batch (hot tokens repeat hundreds of times in real text).
+constexpr int DWT_CHUNK = 8192;
+__global__ void __launch_bounds__(256) dw_target_kernel(const __nv_bfloat16* __restrict__ hidden, long long ldh, const int* __restrict__ row_key,
+                                                        const float* __restrict__ row_coef, int M, int H, void* grad_weight,
+                                                        long long ldgw, int gw_is_f32) {
+  extern __shared__ __align__(16) unsigned char dwt_smem[];
+  int* keys = reinterpret_cast<int*>(dwt_smem);                                        // [DWT_CHUNK]
+  float* acc = reinterpret_cast<float*>(dwt_smem + DWT_CHUNK * sizeof(int));           // [warps][H]
+  const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * warps + warp;
+  const int key = row < M ? row_key[row] : -1;
+  acc += (size_t)warp * H;
+  const bool vec = (ldh & 7) == 0 && ((uintptr_t)hidden & 15) == 0 && (H & 7) == 0;
+  int state = key >= 0 ? 0 : 2;                            // 0: no match seen yet, 1: leader (accumulating), 2: nothing to do
+  for (int c0 = 0; c0 < M; c0 += DWT_CHUNK) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < DWT_CHUNK; i += blockDim.x) keys[i] = c0 + i < M ? __ldg(row_key + c0 + i) : -2;
+    __syncthreads();
+    if (state == 2) continue;
+    const int len = min(DWT_CHUNK, M - c0);
+    for (int j0 = 0; j0 < len && state != 2; j0 += 128) {
+      const int4 k4 = *reinterpret_cast<const int4*>(keys + j0 + lane * 4);
+      const unsigned m0 = __ballot_sync(0xffffffffu, k4.x == key), m1 = __ballot_sync(0xffffffffu, k4.y == key);
+      const unsigned m2 = __ballot_sync(0xffffffffu, k4.z == key), m3 = __ballot_sync(0xffffffffu, k4.w == key);
+      unsigned any = m0 | m1 | m2 | m3;
+      while (any && state != 2) {                          // matches in increasing token order: lane-major, then the four keys
+        const int l = __ffs(any) - 1;
+        any &= any - 1;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const unsigned mq = q == 0 ? m0 : q == 1 ? m1 : q == 2 ? m2 : m3;
+          if (!((mq >> l) & 1u)) continue;
+          const int jj = c0 + j0 + l * 4 + q;
+          if (state == 0) {
+            if (jj != row) { state = 2; break; }           // an earlier token owns this key
+            for (int k = lane; k < H; k += 32) acc[k] = 0.f;
+            state = 1;
+          }
+          const float a = __ldg(row_coef + jj);
+          const __nv_bfloat16* h = hidden + (long long)jj * ldh;
+          if (vec) {   // 16-byte loads, four in flight per lane
+            for (int k0 = lane * 8; k0 < H; k0 += 4 * 256) {
+              uint4 hv[4];
+#pragma unroll
+              for (int u = 0; u < 4; ++u)
+                if (k0 + u * 256 < H) hv[u] = __ldg(reinterpret_cast<const uint4*>(h + k0 + u * 256));
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                const int k = k0 + u * 256;
+                if (k >= H) break;
+                const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&hv[u]);
+                float4 x = *reinterpret_cast<float4*>(acc + k), y = *reinterpret_cast<float4*>(acc + k + 4);
+                const float2 f0 = __bfloat1622float2(hp[0]), f1 = __bfloat1622float2(hp[1]), f2 = __bfloat1622float2(hp[2]),
+                             f3 = __bfloat1622float2(hp[3]);
+                x.x = fmaf(a, f0.x, x.x); x.y = fmaf(a, f0.y, x.y); x.z = fmaf(a, f1.x, x.z); x.w = fmaf(a, f1.y, x.w);
+                y.x = fmaf(a, f2.x, y.x); y.y = fmaf(a, f2.y, y.y); y.z = fmaf(a, f3.x, y.z); y.w = fmaf(a, f3.y, y.w);
+                *reinterpret_cast<float4*>(acc + k) = x; *reinterpret_cast<float4*>(acc + k + 4) = y;
+              }
+            }
+          } else {
+            for (int k = lane * 2; k < H; k += 64) {
+              const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(h + k));
+              acc[k] = fmaf(a, f.x, acc[k]);
+              acc[k + 1] = fmaf(a, f.y, acc[k + 1]);
+            }
+          }
+        }
       }
     }
   }
+  if (state != 1) return;
   if (gw_is_f32) {
-    float* g = reinterpret_cast<float*>(grad_weight) + t * ldgw;
-    for (int k = lane * 2; k < H; k += 64) { g[k] += acc[k]; g[k + 1] += acc[k + 1]; }
+    float* g = reinterpret_cast<float*>(grad_weight) + (long long)key * ldgw;
+    if ((ldgw & 3) == 0 && ((uintptr_t)grad_weight & 15) == 0 && (H & 3) == 0) {
+      for (int k0 = lane * 4; k0 < H; k0 += 4 * 128) {     // four independent 16-byte read-modify-writes per lane
+        float4 gv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) if (k0 + u * 128 < H) gv[u] = *reinterpret_cast<const float4*>(g + k0 + u * 128);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int k = k0 + u * 128;
+          if (k >= H) break;
+          const float4 x = *reinterpret_cast<const float4*>(acc + k);
+          *reinterpret_cast<float4*>(g + k) = make_float4(gv[u].x + x.x, gv[u].y + x.y, gv[u].z + x.z, gv[u].w + x.w);
+        }
+      }
+    } else {
+      for (int k = lane * 2; k < H; k += 64) { g[k] += acc[k]; g[k + 1] += acc[k + 1]; }
+    }
   } else {
-    __nv_bfloat16* g = reinterpret_cast<__nv_bfloat16*>(grad_weight) + t * ldgw;
+    __nv_bfloat16* g = reinterpret_cast<__nv_bfloat16*>(grad_weight) + (long long)key * ldgw;
     for (int k = lane * 2; k < H; k += 64) {
       const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(g + k));
       *reinterpret_cast<__nv_bfloat162*>(g + k) = __floats2bfloat162_rn(f.x + acc[k], f.y + acc[k + 1]);
@@ -702,7 +759,7 @@ extern "C" int b200grpo_lmhead_finalize(const float* stats, int R, int M, float*
 
 // backward scratch: [dlogits panels (recompute mode only)][row scale, row coefficient, scaled hidden (saved mode: the
 // entropy-free path)][tail-split / split-K slab]
-static size_t rows_scratch_bytes(int M, int H) { return 2 * align_up((size_t)M * 4, 256) + align_up((size_t)M * H * 2, 256); }
+static size_t rows_scratch_bytes(int M, int H) { return 3 * align_up((size_t)M * 4, 256) + align_up((size_t)M * H * 2, 256); }
 
 extern "C" size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc, int with_saved) {
   const int ctas = ctas_for(M);
@@ -741,6 +798,7 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   __nv_bfloat16* dlog;
   char* slab;
   float *row_scale = nullptr, *row_coef = nullptr;
+  int* row_key = nullptr;
   __nv_bfloat16* hs = nullptr;
   const float* row_ref = nullptr;
   if (saved) {
@@ -748,7 +806,8 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
     dlog = (__nv_bfloat16*)((char*)saved + part_bytes(M, Vloc) + ref_bytes(M));
     row_scale = (float*)workspace;
     row_coef = (float*)((char*)workspace + align_up((size_t)M * 4, 256));
-    hs = (__nv_bfloat16*)((char*)workspace + 2 * align_up((size_t)M * 4, 256));
+    row_key = (int*)((char*)workspace + 2 * align_up((size_t)M * 4, 256));
+    hs = (__nv_bfloat16*)((char*)workspace + 3 * align_up((size_t)M * 4, 256));
     slab = (char*)workspace + rows_scratch_bytes(M, H);
   } else {
     dlog = (__nv_bfloat16*)workspace;
@@ -762,7 +821,8 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   if (rows_path && form) {   // 1a. per-row scale s = -a exp(r - lse), coefficient a, scaled copy of hidden (operand B of dW)
     ProfScope ps(PROF_DLOGITS_EW, st);
     bwd_rows_kernel<<<ceil_div(M, 8), 256, 0, st>>>((const __nv_bfloat16*)hidden, ldh, row_ref, lse, coef_lp, grad_scale, inv_temperature,
-                                                    M, H, row_scale, row_coef, hs); count_launch();
+                                                    M, H, (const long long*)targets, v_offset, Vloc, row_scale, row_coef, row_key, hs);
+    count_launch();
     B200_CUDA_OK(cudaGetLastError());
   } else if (saved && form) {  // 1b. entropy term present: saved exponentials -> dlogits in place (no recompute GEMM)
     ProfScope ps(PROF_DLOGITS_EW, st);
@@ -800,17 +860,17 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
                                ctas, get_tunable(TUNE_DW_GROUP_M), get_tunable(TUNE_DW_KSPLIT), slab, slab_bytes, st, M, get_tunable(TUNE_DW_GROUP_N),
                                get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT), mrep_for(TUNE_DW_BIG_M, ctas), get_tunable(TUNE_DW_ZIGZAG))) return e;
     if (rows_path) {
-      int warps = 8;                                          // f32 row per warp in shared memory: 8 x H x 4 B (115 KB at H = 3584)
-      while (warps > 1 && (size_t)warps * H * 4 > 200 * 1024) warps >>= 1;
-      B200_REQUIRE((size_t)warps * H * 4 <= 200 * 1024, "lmhead_bwd: hidden size %d too large for the target-row kernel", H);
+      int warps = 4;                                          // f32 row per warp in shared memory: 4 x H x 4 B + 32 KB of keys (89 KB at H = 3584: two blocks per SM)
+      const size_t fixed = DWT_CHUNK * sizeof(int), cap = 200 * 1024;
+      while (warps > 1 && fixed + (size_t)warps * H * 4 > cap) warps >>= 1;
+      B200_REQUIRE(fixed + (size_t)warps * H * 4 <= cap, "lmhead_bwd: hidden size %d too large for the target-row kernel", H);
       static bool configured = false;
       if (!configured) {
-        B200_CUDA_OK(cudaFuncSetAttribute(dw_target_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        B200_CUDA_OK(cudaFuncSetAttribute(dw_target_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap));
         configured = true;
       }
-      dw_target_kernel<<<ceil_div(M, warps), warps * 32, (size_t)warps * H * 4, st>>>(
-          (const __nv_bfloat16*)hidden, ldh, (const long long*)targets, v_offset, Vloc, row_coef, M, H, grad_weight, ldgw,
-          grad_weight_is_f32); count_launch();
+      dw_target_kernel<<<ceil_div(M, warps), warps * 32, fixed + (size_t)warps * H * 4, st>>>(
+          (const __nv_bfloat16*)hidden, ldh, row_key, row_coef, M, H, grad_weight, ldgw, grad_weight_is_f32); count_launch();
       B200_CUDA_OK(cudaGetLastError());
     }
   }
