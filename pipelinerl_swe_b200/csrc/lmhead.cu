@@ -421,47 +421,48 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const __nv_bfloat16* __re
 }
 
 // dW[v, :] += sum over the tokens t with key(t) == v of a_t * hidden[t, :]   (the onehot term of the entropy-free backward;
-// key = local target row, -1 for tokens without one).  Deterministic and atomic-free: one warp per token row; the block
-// stages the key column through shared memory (8192 keys per trip, every load in flight at once) and each warp scans it four
-// keys per lane; the FIRST token of every distinct key is its leader and folds all tokens of that key, in token order, into
-// an f32 row in shared memory, then updates the gradient row once -- every element of dW is touched at most once per
-// launch whatever the multiplicity of a token in the micro-batch (hot tokens repeat hundreds of times in real text).
-constexpr int DWT_CHUNK = 8192;
-__global__ void __launch_bounds__(256) dw_target_kernel(const __nv_bfloat16* __restrict__ hidden, long long ldh, const int* __restrict__ row_key,
+// key = local target row, -1 for tokens without one).  Deterministic and atomic-free: one warp per token row scans the key
+// column (32 KB at T = 8192: L1-resident after the first touch; four 16-byte loads in flight per lane, 512 keys per trip);
+// the FIRST token of every distinct key is its leader and folds all tokens of that key, in token order, into an f32 row in
+// shared memory, then updates the gradient row once -- every element of dW is touched at most once per launch whatever the
+// multiplicity of a token in the micro-batch (hot tokens repeat hundreds of times in real text).  row_key is padded to a
+// multiple of 512 entries with -2 by bwd_rows_kernel's launch (see lmhead_bwd_impl).
+constexpr int DWT_TRIP = 512;
+__global__ void __launch_bounds__(128) dw_target_kernel(const __nv_bfloat16* __restrict__ hidden, long long ldh, const int* __restrict__ row_key,
                                                         const float* __restrict__ row_coef, int M, int H, void* grad_weight,
                                                         long long ldgw, int gw_is_f32) {
   extern __shared__ __align__(16) unsigned char dwt_smem[];
-  int* keys = reinterpret_cast<int*>(dwt_smem);                                        // [DWT_CHUNK]
-  float* acc = reinterpret_cast<float*>(dwt_smem + DWT_CHUNK * sizeof(int));           // [warps][H]
   const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * warps + warp;
-  const int key = row < M ? row_key[row] : -1;
-  acc += (size_t)warp * H;
+  if (row >= M) return;
+  const int key = row_key[row];
+  if (key < 0) return;
+  float* acc = reinterpret_cast<float*>(dwt_smem) + (size_t)warp * H;
   const bool vec = (ldh & 7) == 0 && ((uintptr_t)hidden & 15) == 0 && (H & 7) == 0;
-  int state = key >= 0 ? 0 : 2;                            // 0: no match seen yet, 1: leader (accumulating), 2: nothing to do
-  for (int c0 = 0; c0 < M; c0 += DWT_CHUNK) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < DWT_CHUNK; i += blockDim.x) keys[i] = c0 + i < M ? __ldg(row_key + c0 + i) : -2;
-    __syncthreads();
-    if (state == 2) continue;
-    const int len = min(DWT_CHUNK, M - c0);
-    for (int j0 = 0; j0 < len && state != 2; j0 += 128) {
-      const int4 k4 = *reinterpret_cast<const int4*>(keys + j0 + lane * 4);
-      const unsigned m0 = __ballot_sync(0xffffffffu, k4.x == key), m1 = __ballot_sync(0xffffffffu, k4.y == key);
-      const unsigned m2 = __ballot_sync(0xffffffffu, k4.z == key), m3 = __ballot_sync(0xffffffffu, k4.w == key);
+  bool leader = false;
+  const int M_pad = (M + DWT_TRIP - 1) / DWT_TRIP * DWT_TRIP;
+  for (int j0 = 0; j0 < M_pad; j0 += DWT_TRIP) {           // warp-uniform control flow throughout
+    int4 k4[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) k4[u] = __ldg(reinterpret_cast<const int4*>(row_key + j0 + u * 128) + lane);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const unsigned m0 = __ballot_sync(0xffffffffu, k4[u].x == key), m1 = __ballot_sync(0xffffffffu, k4[u].y == key);
+      const unsigned m2 = __ballot_sync(0xffffffffu, k4[u].z == key), m3 = __ballot_sync(0xffffffffu, k4[u].w == key);
       unsigned any = m0 | m1 | m2 | m3;
-      while (any && state != 2) {                          // matches in increasing token order: lane-major, then the four keys
+      while (any) {                                        // matches in increasing token order: lane-major, then the four keys
         const int l = __ffs(any) - 1;
         any &= any - 1;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const unsigned mq = q == 0 ? m0 : q == 1 ? m1 : q == 2 ? m2 : m3;
           if (!((mq >> l) & 1u)) continue;
-          const int jj = c0 + j0 + l * 4 + q;
-          if (state == 0) {
-            if (jj != row) { state = 2; break; }           // an earlier token owns this key
-            for (int k = lane; k < H; k += 32) acc[k] = 0.f;
-            state = 1;
+          const int jj = j0 + u * 128 + l * 4 + q;
+          if (!leader) {
+            if (jj != row) return;                         // an earlier token owns this key
+            if (vec) for (int k = lane * 4; k < H; k += 128) *reinterpret_cast<float4*>(acc + k) = make_float4(0.f, 0.f, 0.f, 0.f);
+            else for (int k = lane; k < H; k += 32) acc[k] = 0.f;
+            leader = true;
           }
           const float a = __ldg(row_coef + jj);
           const __nv_bfloat16* h = hidden + (long long)jj * ldh;
@@ -469,13 +470,13 @@ __global__ void __launch_bounds__(256) dw_target_kernel(const __nv_bfloat16* __r
             for (int k0 = lane * 8; k0 < H; k0 += 4 * 256) {
               uint4 hv[4];
 #pragma unroll
-              for (int u = 0; u < 4; ++u)
-                if (k0 + u * 256 < H) hv[u] = __ldg(reinterpret_cast<const uint4*>(h + k0 + u * 256));
+              for (int w = 0; w < 4; ++w)
+                if (k0 + w * 256 < H) hv[w] = __ldg(reinterpret_cast<const uint4*>(h + k0 + w * 256));
 #pragma unroll
-              for (int u = 0; u < 4; ++u) {
-                const int k = k0 + u * 256;
+              for (int w = 0; w < 4; ++w) {
+                const int k = k0 + w * 256;
                 if (k >= H) break;
-                const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&hv[u]);
+                const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&hv[w]);
                 float4 x = *reinterpret_cast<float4*>(acc + k), y = *reinterpret_cast<float4*>(acc + k + 4);
                 const float2 f0 = __bfloat1622float2(hp[0]), f1 = __bfloat1622float2(hp[1]), f2 = __bfloat1622float2(hp[2]),
                              f3 = __bfloat1622float2(hp[3]);
@@ -495,7 +496,8 @@ __global__ void __launch_bounds__(256) dw_target_kernel(const __nv_bfloat16* __r
       }
     }
   }
-  if (state != 1) return;
+  if (!leader) return;
+  __syncwarp();
   if (gw_is_f32) {
     float* g = reinterpret_cast<float*>(grad_weight) + (long long)key * ldgw;
     if ((ldgw & 3) == 0 && ((uintptr_t)grad_weight & 15) == 0 && (H & 3) == 0) {
@@ -759,7 +761,8 @@ extern "C" int b200grpo_lmhead_finalize(const float* stats, int R, int M, float*
 
 // backward scratch: [dlogits panels (recompute mode only)][row scale, row coefficient, scaled hidden (saved mode: the
 // entropy-free path)][tail-split / split-K slab]
-static size_t rows_scratch_bytes(int M, int H) { return 3 * align_up((size_t)M * 4, 256) + align_up((size_t)M * H * 2, 256); }
+static size_t key_bytes(int M) { return align_up((size_t)ceil_div(M, DWT_TRIP) * DWT_TRIP * 4, 256); }   // padded for the 512-key trips of dw_target_kernel
+static size_t rows_scratch_bytes(int M, int H) { return 2 * align_up((size_t)M * 4, 256) + key_bytes(M) + align_up((size_t)M * H * 2, 256); }
 
 extern "C" size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc, int with_saved) {
   const int ctas = ctas_for(M);
@@ -807,7 +810,7 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
     row_scale = (float*)workspace;
     row_coef = (float*)((char*)workspace + align_up((size_t)M * 4, 256));
     row_key = (int*)((char*)workspace + 2 * align_up((size_t)M * 4, 256));
-    hs = (__nv_bfloat16*)((char*)workspace + 3 * align_up((size_t)M * 4, 256));
+    hs = (__nv_bfloat16*)((char*)workspace + 2 * align_up((size_t)M * 4, 256) + key_bytes(M));
     slab = (char*)workspace + rows_scratch_bytes(M, H);
   } else {
     dlog = (__nv_bfloat16*)workspace;
@@ -820,6 +823,7 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   }
   if (rows_path && form) {   // 1a. per-row scale s = -a exp(r - lse), coefficient a, scaled copy of hidden (operand B of dW)
     ProfScope ps(PROF_DLOGITS_EW, st);
+    B200_CUDA_OK(cudaMemsetAsync(row_key + M, 0xfe, key_bytes(M) - (size_t)M * 4, st));   // pad keys: 0xfefefefe < 0, never a match
     bwd_rows_kernel<<<ceil_div(M, 8), 256, 0, st>>>((const __nv_bfloat16*)hidden, ldh, row_ref, lse, coef_lp, grad_scale, inv_temperature,
                                                     M, H, (const long long*)targets, v_offset, Vloc, row_scale, row_coef, row_key, hs);
     count_launch();
@@ -860,16 +864,16 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
                                ctas, get_tunable(TUNE_DW_GROUP_M), get_tunable(TUNE_DW_KSPLIT), slab, slab_bytes, st, M, get_tunable(TUNE_DW_GROUP_N),
                                get_tunable(TUNE_HINT_STREAM), get_tunable(TUNE_HINT_RESIDENT), mrep_for(TUNE_DW_BIG_M, ctas), get_tunable(TUNE_DW_ZIGZAG))) return e;
     if (rows_path) {
-      int warps = 4;                                          // f32 row per warp in shared memory: 4 x H x 4 B + 32 KB of keys (89 KB at H = 3584: two blocks per SM)
-      const size_t fixed = DWT_CHUNK * sizeof(int), cap = 200 * 1024;
-      while (warps > 1 && fixed + (size_t)warps * H * 4 > cap) warps >>= 1;
-      B200_REQUIRE(fixed + (size_t)warps * H * 4 <= cap, "lmhead_bwd: hidden size %d too large for the target-row kernel", H);
+      int warps = 4;                                          // f32 row per warp in shared memory: 4 x H x 4 B (57 KB at H = 3584: three blocks per SM)
+      const size_t cap = 200 * 1024;
+      while (warps > 1 && (size_t)warps * H * 4 > cap) warps >>= 1;
+      B200_REQUIRE((size_t)warps * H * 4 <= cap, "lmhead_bwd: hidden size %d too large for the target-row kernel", H);
       static bool configured = false;
       if (!configured) {
         B200_CUDA_OK(cudaFuncSetAttribute(dw_target_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap));
         configured = true;
       }
-      dw_target_kernel<<<ceil_div(M, warps), warps * 32, fixed + (size_t)warps * H * 4, st>>>(
+      dw_target_kernel<<<ceil_div(M, warps), warps * 32, (size_t)warps * H * 4, st>>>(
           (const __nv_bfloat16*)hidden, ldh, row_key, row_coef, M, H, grad_weight, ldgw, grad_weight_is_f32); count_launch();
       B200_CUDA_OK(cudaGetLastError());
     }
