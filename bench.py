@@ -912,6 +912,16 @@ def run_b200(args):
         cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "tokens_per_step_sample", "same_config")}
         del arm
 
+    # ---------------- N=1: the advantage step (populate_rl_data) against the reference's pandas path on the host cores ----------------
+    adv = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            from bench_advantage import run as advantage_run
+            adv = advantage_run(groups=64, attempts=16, tokens=2048, iters=2)     # 1024 rollouts, ~1.6 M tokens
+        except Exception as e:  # noqa: BLE001
+            adv = {"unavailable": repr(e)[:200]}
+
     # ---------------- N=1: the other single-GPU configurations, short runs ----------------
     others = None
     if world == 1 and not args.no_other_configs:
@@ -956,7 +966,7 @@ def run_b200(args):
                        "tunables": args.tunable, "tokens_per_gpu_per_sec": value / world if not is_vp else value},
             "parity": parity, "roofline": roofline, ("recompute" if args.mode == "saved" else "saved"): other,
             "cpu_baseline": cpu, "torch_gpu_baseline": torch_gpu, "rl_step_api": api, "e2e": e2e,
-            "other_configs": others, "vocab_parallel": vp, "weight_broadcast": wb, "gpu_launches": int(round(launches_per_step * K)),
+            "advantage_step": adv, "other_configs": others, "vocab_parallel": vp, "weight_broadcast": wb, "gpu_launches": int(round(launches_per_step * K)),
             "gpu_launches_per_step": launches_per_step, "clocks": clocks.summary(),
         }
         print(json.dumps(line), flush=True)
