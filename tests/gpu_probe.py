@@ -278,7 +278,9 @@ def probe_gemm_fuzz(seed, n_cases=24):
 
 
 def probe_lmhead_fuzz(seed, n_cases=16):
-    """Random (M, H, V, temperature, tile variant, saved / recompute) forward + backward against torch autograd in fp32."""
+    """Random (M, H, V, temperature, tile variant, saved / recompute, with / without an entropy gradient, f32-accumulate / bf16
+    gradient output) forward + backward against torch autograd in fp32.  Targets are drawn from a small pool in half of the
+    cases so that many tokens share a target (the leader logic of the sparse target-row kernel)."""
     import random
     from pipelinerl_swe_b200 import _abi, ops
     rnd = random.Random(seed)
@@ -290,14 +292,16 @@ def probe_lmhead_fuzz(seed, n_cases=16):
         V = rnd.choice([8, 100, 256, 264, 1000, 5000, 20008])
         temp = rnd.choice([0.6, 1.0, 1.4])
         save, two = rnd.randint(0, 1), rnd.randint(0, 1)
+        no_ent, f32_acc, hot = rnd.randint(0, 1), rnd.randint(0, 1), rnd.randint(0, 1)
         for name in ("dh_big_m", "dw_big_m", "tail_split"):
             _abi.set_tunable(name, rnd.randint(0, 1))
         _abi.set_tunable("two_cta", two)
         h = torch.randn(M, H, device="cuda", generator=g).bfloat16()
         w = (torch.randn(V, H, device="cuda", generator=g) * (1.0 / H ** 0.5)).bfloat16()
-        tgt = torch.randint(0, V, (M,), device="cuda", generator=g)
+        tgt = torch.randint(0, min(V, 5) if hot else V, (M,), device="cuda", generator=g)
         c_lp = torch.randn(M, device="cuda", generator=g) * 0.1
-        c_ent = torch.randn(M, device="cuda", generator=g) * 0.01
+        c_lp[::3] = 0.0
+        c_ent = torch.randn(M, device="cuda", generator=g) * (0.0 if no_ent else 0.01)
         hr, wr = h.float().requires_grad_(True), w.float().requires_grad_(True)
         logp = torch.log_softmax((hr @ wr.t()) / temp, -1)
         lp = logp.gather(1, tgt[:, None]).squeeze(1)
@@ -306,13 +310,17 @@ def probe_lmhead_fuzz(seed, n_cases=16):
         saved = ops.lmhead_saved_buffer(M, H, V, h.device) if save else None
         stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp, saved=saved)
         lp2, ent2, lse = ops.lmhead_finalize(stats)
-        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent2, c_lp, c_ent, 1.0 / temp, saved=saved)
+        g0 = torch.randn(V, H, device="cuda", generator=g) if f32_acc else None
+        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent2, c_lp, None if no_ent else c_ent, 1.0 / temp, saved=saved,
+                                grad_weight_out=g0.clone() if f32_acc else None, accumulate=bool(f32_acc))
         torch.cuda.synchronize()
+        if f32_acc:
+            gw = gw - g0
         e = [float((lp2 - lp).abs().max() / (lp.abs().max() + 1e-9)), float((ent2 - ent).abs().max() / (ent.abs().max() + 1e-3)),
              _rel(gh, hr.grad), _rel(gw, wr.grad)]
         worst = max(worst, max(e))
         if not (e[0] < 1e-3 and e[1] < 2e-3 and e[2] < 2e-2 and e[3] < 2e-2):
-            bad.append((M, H, V, temp, save, two, [round(x, 5) for x in e]))
+            bad.append((M, H, V, temp, save, two, no_ent, f32_acc, hot, [round(x, 5) for x in e]))
     for name, v in (("dh_big_m", 1), ("dw_big_m", 0), ("tail_split", 1), ("two_cta", 1)):
         _abi.set_tunable(name, v)
     return not bad, f"{n_cases} cases worst={worst:.2e} bad={bad[:3]}"
