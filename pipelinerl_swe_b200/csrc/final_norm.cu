@@ -332,8 +332,11 @@ extern "C" int b200grpo_final_norm_bwd(const void* x, int64_t ldx, const void* g
     else FN_BWD_ONE(N, TH, false);     \
   } while (0)
   // every thread owns one or two 8-column chunks: 256-thread blocks (two per SM) up to H = 4096, 512-thread blocks above
+  // (H in (4096, 5120]: 640 threads with ONE chunk each -- 512 threads x 2 chunks leaves three quarters of the block idle in its
+  //  second round at H = 5120, the Qwen2.5-32B width)
   if (H <= 2048) FN_BWD(1, 256);
   else if (H <= 4096) FN_BWD(2, 256);
+  else if (H <= 5120) FN_BWD(1, 640);
   else FN_BWD(2, 512);
 #undef FN_BWD
 #undef FN_BWD_ONE
