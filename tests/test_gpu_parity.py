@@ -690,3 +690,36 @@ def test_entropy_free_backward_is_deterministic_with_repeated_targets(f32):
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
     got = outs[0][1] - 0.25 if f32 else outs[0][1]
     assert _rel(got, wr.grad) < (1e-3 if f32 else 1e-2) and _rel(outs[0][0], hr.grad) < GRAD_RTOL
+
+
+def test_forward_reference_range_is_exact_to_60_nats_and_fails_loudly_beyond_88():
+    """K1 takes its exponentials relative to a per-row reference r = max(target logit, four sampled logits).  A target 60 nats
+    below the row maximum (probability 1e-26) is still exact; one 100 nats below (probability 1e-44, outside f32's exponent range
+    in these units) gives a NON-FINITE log-prob -- which rl_step turns into the reference's own assert (rl/__init__.py:209) --
+    never a silently wrong number.  Rows next to it are unaffected."""
+    from pipelinerl_swe_b200 import ops
+    d = _dev()
+    M, H, V = 64, 64, 4096
+    g = torch.Generator(device=d).manual_seed(3)
+    u = torch.zeros(H, device=d)
+    u[0] = 1.0
+    w = (torch.randn(V, H, device=d, generator=g) * 0.05)
+    w[:, 0] = 0.0
+    hot, tgt_tok = 7, 11                                      # neither is one of the sampled columns {0, V/4, V/2, 3V/4}
+    for gap_half, finite in ((30.0, True), (50.0, False)):
+        ww = w.clone()
+        ww[hot] = gap_half * u                                # logit +gap/2 on the hot token ...
+        ww[tgt_tok] = -gap_half * u                           # ... and -gap/2 on the target of row 0
+        h = torch.randn(M, H, device=d, generator=g) * 0.5
+        h[0] = u                                              # row 0 sees the extreme pair; the other rows see a zero first component
+        h[1:, 0] = 0.0
+        tgt = torch.randint(0, V, (M,), device=d, generator=g)
+        tgt[0] = tgt_tok
+        hb, wb = h.bfloat16(), ww.bfloat16()
+        lp, ent, lse = ops.lmhead_finalize(ops.lmhead_fwd_stats(hb, wb, tgt, 1.0))
+        ref = torch.log_softmax(hb.float() @ wb.float().t(), -1).gather(1, tgt[:, None]).squeeze(1)
+        assert float((lp[1:] - ref[1:]).abs().max()) < 1e-3   # neighbours are exact either way
+        if finite:
+            assert abs(float(lp[0] - ref[0])) < 1e-3 * abs(float(ref[0])) and float(ref[0]) < -55.0
+        else:
+            assert not bool(torch.isfinite(lp[0]))            # loud, not wrong
