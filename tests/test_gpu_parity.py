@@ -693,10 +693,12 @@ def test_entropy_free_backward_is_deterministic_with_repeated_targets(f32):
 
 
 def test_forward_reference_range_is_exact_to_60_nats_and_fails_loudly_beyond_88():
-    """K1 takes its exponentials relative to a per-row reference r = max(target logit, four sampled logits).  A target 60 nats
-    below the row maximum (probability 1e-26) is still exact; one 100 nats below (probability 1e-44, outside f32's exponent range
-    in these units) gives a NON-FINITE log-prob -- which rl_step turns into the reference's own assert (rl/__init__.py:209) --
-    never a silently wrong number.  Rows next to it are unaffected."""
+    """K1 takes its exponentials relative to a per-row reference r = max(target logit, four sampled logits).  A target 60 or
+    even 100 nats below the row maximum is exact as long as ONE of the five logits is within 88 nats of the maximum (here the
+    sampled columns are, at logit 0).  Only when the target AND every sampled column sit more than 88 nats below the maximum
+    (probabilities below 1e-38, outside f32's exponent range in these units) does the row give a NON-FINITE log-prob -- which
+    rl_step turns into the reference's own assert (rl/__init__.py:209) -- never a silently wrong number.  Neighbouring rows are
+    unaffected in every case."""
     from pipelinerl_swe_b200 import ops
     d = _dev()
     M, H, V = 64, 64, 4096
@@ -705,11 +707,13 @@ def test_forward_reference_range_is_exact_to_60_nats_and_fails_loudly_beyond_88(
     u[0] = 1.0
     w = (torch.randn(V, H, device=d, generator=g) * 0.05)
     w[:, 0] = 0.0
-    hot, tgt_tok = 7, 11                                      # neither is one of the sampled columns {0, V/4, V/2, 3V/4}
-    for gap_half, finite in ((30.0, True), (50.0, False)):
+    hot, tgt_tok, sampled = 7, 11, [0, V // 4, V // 2, 3 * V // 4]
+    for gap_half, sink_samples, finite in ((30.0, False, True), (50.0, False, True), (50.0, True, False)):
         ww = w.clone()
         ww[hot] = gap_half * u                                # logit +gap/2 on the hot token ...
         ww[tgt_tok] = -gap_half * u                           # ... and -gap/2 on the target of row 0
+        if sink_samples:
+            ww[sampled] = -gap_half * u                       # contrived: the sampled columns are as unlikely as the target
         h = torch.randn(M, H, device=d, generator=g) * 0.5
         h[0] = u                                              # row 0 sees the extreme pair; the other rows see a zero first component
         h[1:, 0] = 0.0
