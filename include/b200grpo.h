@@ -143,6 +143,19 @@ int b200grpo_segment_bounds(const int64_t* position_ids, int T, int32_t* bounds,
                             int32_t* n_bounds, void* workspace, size_t workspace_bytes,
                             void* stream);
 
+/* Allocation-free variant of b200grpo_segment_bounds.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same kernels and the same outputs,
+ * bit for bit; the scratch (per-block counts + the 1-bit start mask, ~520 KB) is a file-scope
+ * __device__ array inside the library, which every GPU that loads the library holds until exit.
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *   T > B200GRPO_SEGMENT_BOUNDS_STATIC_MAX_T  ->  B200GRPO_EWORKSPACE with a message.
+ * All calls on a device share the one array: calls that overlap on the GPU (different
+ * streams or threads) race -- serialise them.  Nothing in it needs clearing between calls. */
+#define B200GRPO_SEGMENT_BOUNDS_STATIC_MAX_T (1 << 22) /* 4,194,304 tokens */
+int b200grpo_segment_bounds_static(const int64_t* position_ids, int T, int32_t* bounds,
+                                   int32_t* n_bounds, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * K2  lm_head backward.  Replaces autograd through rl/__init__.py:197-208:
  *   dlogit[t,j] = (s/temperature) * ( coef_lp[t]*(1[j==target_t] - p[t,j])

@@ -74,6 +74,7 @@ SIGNATURES = {
     "b200grpo_token_loss": (_i, [_p] * 12 + [_i, _i, C.POINTER(LossCfg)] + [_p] * 6 + [_sz, _p]),
     "b200grpo_segment_bounds_workspace": (_sz, [_i]),
     "b200grpo_segment_bounds": (_i, [_p, _i, _p, _p, _p, _sz, _p]),
+    "b200grpo_segment_bounds_static": (_i, [_p, _i, _p, _p, _p]),   # scratch inside the library; allocates nothing
     "b200grpo_lmhead_bwd_workspace": (_sz, [_i, _i, _i, _i]),
     "b200grpo_lmhead_bwd": (_i, [_p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i64, _f, _p, _p, _i64, _p, _i64, _i, _i,
                                  _p, _sz, _p]),

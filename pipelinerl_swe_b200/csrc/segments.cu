@@ -5,6 +5,7 @@
 // eight independent coalesced loads in flight per thread): the count pass also leaves a 1-bit-per-token start mask
 // (one ballot word per warp and trip, 1/8 B per token) and the scatter pass works from that mask alone.
 #include "common.cuh"
+#include <mutex>
 
 namespace b200grpo {
 
@@ -113,6 +114,64 @@ extern "C" int b200grpo_segment_bounds(const int64_t* position_ids, int T, int32
   int* counts = (int*)workspace;
   uint32_t* mask = (uint32_t*)((char*)workspace + seg_counts_bytes(T));
   ProfScope ps(PROF_SEGMENTS, st);
+  seg_count_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts, mask);
+  seg_scan_kernel<<<1, 1024, 0, st>>>(counts, n_blocks, n_bounds);
+  seg_scatter_kernel<<<n_blocks, SB_WORDS, 0, st>>>(mask, T, counts, n_bounds, bounds); count_launch(3);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200GRPO_OK;
+}
+
+// ---- allocation-free variant -------------------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same three kernels, scratch (per-block counts +
+// the 1-bit start mask) in a file-scope __device__ array sized for B200GRPO_SEGMENT_BOUNDS_STATIC_MAX_T tokens; every GPU
+// that loads the library holds those ~520 KB until exit.  In host code the array's NAME is a host-side stand-in, not a
+// device address: its address on the current device comes from cudaGetSymbolAddress, once per device, below.
+// Every call shares the one array: calls that overlap on the GPU (two streams, two threads) race.  Nothing in it has to
+// start at zero -- each count and each mask word that a call reads is written by that call's own count pass first.
+namespace b200grpo {
+constexpr int SEG_STATIC_BLOCKS = B200GRPO_SEGMENT_BOUNDS_STATIC_MAX_T / (SB_THREADS * SB_ITEMS);
+static_assert(B200GRPO_SEGMENT_BOUNDS_STATIC_MAX_T % (SB_THREADS * SB_ITEMS) == 0, "static scratch: whole blocks");
+constexpr size_t SEG_STATIC_COUNTS_BYTES = ((size_t)SEG_STATIC_BLOCKS * sizeof(int) + 255) / 256 * 256;
+constexpr size_t SEG_STATIC_MASK_BYTES = (size_t)SEG_STATIC_BLOCKS * SB_WORDS * sizeof(uint32_t);
+static __device__ __align__(256) unsigned char g_seg_static_scratch[SEG_STATIC_COUNTS_BYTES + SEG_STATIC_MASK_BYTES];
+
+constexpr int SEG_STATIC_MAX_DEVICES = 64;
+static std::mutex g_seg_static_mu;
+static void* g_seg_static_addr[SEG_STATIC_MAX_DEVICES] = {};
+
+// device address of the scratch array on the CURRENT device (resolved once per device, with that device current)
+static int seg_static_scratch(void** out) {
+  int dev = -1;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < SEG_STATIC_MAX_DEVICES, "segment_bounds_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_seg_static_mu);
+  if (!g_seg_static_addr[dev]) {
+    void* p = nullptr;
+    B200_CUDA_OK(cudaGetSymbolAddress(&p, g_seg_static_scratch));
+    B200_REQUIRE(p != nullptr, "segment_bounds_static: cudaGetSymbolAddress returned a null address");
+    g_seg_static_addr[dev] = p;
+  }
+  *out = g_seg_static_addr[dev];
+  return B200GRPO_OK;
+}
+}  // namespace b200grpo
+
+extern "C" int b200grpo_segment_bounds_static(const int64_t* position_ids, int T, int32_t* bounds, int32_t* n_bounds,
+                                              void* stream) {
+  if (int e = check_device_sm100()) return e;
+  B200_REQUIRE(position_ids && bounds && n_bounds && T >= 1, "segment_bounds_static: bad argument");
+  if (T > B200GRPO_SEGMENT_BOUNDS_STATIC_MAX_T) {
+    set_error("segment_bounds_static: T = %d exceeds the built-in scratch (at most %d tokens); use b200grpo_segment_bounds "
+              "with a caller-provided workspace", T, B200GRPO_SEGMENT_BOUNDS_STATIC_MAX_T);
+    return B200GRPO_EWORKSPACE;
+  }
+  void* scratch = nullptr;
+  if (int e = seg_static_scratch(&scratch)) return e;
+  const int n_blocks = ceil_div(T, SB_THREADS * SB_ITEMS);
+  cudaStream_t st = (cudaStream_t)stream;
+  int* counts = (int*)scratch;
+  uint32_t* mask = (uint32_t*)((char*)scratch + SEG_STATIC_COUNTS_BYTES);
   seg_count_kernel<<<n_blocks, SB_THREADS, 0, st>>>(position_ids, T, counts, mask);
   seg_scan_kernel<<<1, 1024, 0, st>>>(counts, n_blocks, n_bounds);
   seg_scatter_kernel<<<n_blocks, SB_WORDS, 0, st>>>(mask, T, counts, n_bounds, bounds); count_launch(3);
