@@ -372,6 +372,15 @@ def test_lmhead_random_shapes_and_variants(seed):
     assert ok, msg
 
 
+@pytest.mark.parametrize("seed", [300, 301, 302])
+def test_rl_step_random_configs_vs_the_reference_rl_step(seed):
+    """Whole drop-in (rl_step + backward) against the reference's own rl_step (oracle/_ref) over random batches and RLConfigs."""
+    from fuzz_rl_step import fuzz
+    ok, msg = fuzz(seed, n_cases=10)
+    print(msg)
+    assert ok, msg
+
+
 @pytest.mark.parametrize("tied", [False, True])
 def test_rl_step_through_a_real_hf_causal_lm(tied):
     """Drop-in check on an unmodified transformers model (random tiny Qwen2): the lm_head swap inside HF's own forward,
