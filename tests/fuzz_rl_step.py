@@ -208,3 +208,43 @@ if __name__ == "__main__":
         print("FUZZ", "OK" if ok else "FAIL", msg, flush=True)
     print(f"FUZZ SUMMARY seeds {first}..{first + n - 1} x {cases} cases: {n_bad} failing seeds")
     sys.exit(1 if n_bad else 0)
+
+
+# ---- error behaviour: the reference raises (rl/__init__.py:209,222,237,264,283,313); the drop-in must raise the same type ----------
+def error_cases():
+    """(name, mutate(case) -> None) pairs; each makes the reference's rl_step raise."""
+    def gt_zero(c):
+        c["cfg"]["group_normalization"] = True
+        c["batch"]["group_tokens"][:, 3] = 0.0
+    def ref_inf(c):
+        c["batch"]["ref_logprobs"][:, -1] = float("inf")
+    def ref_nan_on_masked_token(c):      # the reference's isfinite().all() covers masked positions too (:237)
+        c["batch"]["labels"][:, 1] = -100
+        c["batch"]["ref_logprobs"][:, 1] = float("nan")
+    def hidden_nan(c):
+        c["hidden"][:, 2, 0] = float("nan")
+    def unknown_policy(c):
+        c["cfg"]["policy_loss"] = "grpo_v9"
+    def loss_overflow(c):
+        c["cfg"].update(policy_loss="ppo", use_advantages=True, relu_log_p_weights=False)
+        c["batch"]["advantages"][:, -1] = float("inf")
+        c["batch"]["labels"][:, -1] = c["batch"]["input_ids"][:, -1]
+    return [("group_tokens_zero", gt_zero), ("ref_logprob_inf", ref_inf), ("ref_logprob_nan_masked", ref_nan_on_masked_token),
+            ("hidden_nan", hidden_nan), ("unknown_policy_loss", unknown_policy), ("non_finite_loss", loss_overflow)]
+
+
+def check_error_case(name, mutate, dev="cuda:0"):
+    """Returns (reference exception type, our exception type)."""
+    out = []
+    for run in (run_reference, run_ours):
+        case = draw_case(random.Random(77), 77000)
+        case["cfg"].update(group_normalization=False, overlong_filtering=False)
+        case["values"] = None
+        case["cfg"]["value_loss_coef"] = 0.0
+        mutate(case)
+        try:
+            run(case, dev)
+            out.append(None)
+        except Exception as e:  # noqa: BLE001
+            out.append(type(e))
+    return tuple(out)

@@ -381,6 +381,15 @@ def test_rl_step_random_configs_vs_the_reference_rl_step(seed):
     assert ok, msg
 
 
+def test_rl_step_raises_what_the_reference_raises():
+    """Non-finite inputs, group_tokens <= 0, unknown policy_loss: the same exception TYPE as the reference's rl_step (rl/__init__.py:209-313)."""
+    from fuzz_rl_step import check_error_case, error_cases
+    for name, mutate in error_cases():
+        ref_exc, our_exc = check_error_case(name, mutate)
+        assert ref_exc is not None, f"{name}: the reference did not raise"
+        assert our_exc is not None and issubclass(our_exc, ref_exc), f"{name}: reference raised {ref_exc}, drop-in raised {our_exc}"
+
+
 @pytest.mark.parametrize("tied", [False, True])
 def test_rl_step_through_a_real_hf_causal_lm(tied):
     """Drop-in check on an unmodified transformers model (random tiny Qwen2): the lm_head swap inside HF's own forward,
