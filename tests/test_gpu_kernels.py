@@ -213,6 +213,16 @@ def test_populate_rl_data_large_vs_oracle():
 
 
 # ---- K6: bucket pack / unpack round trip, byte-exact --------------------------------------------
+@pytest.mark.parametrize("seed", [400, 401])
+def test_populate_rl_data_random_datasets_bit_exact_vs_the_reference_pandas(seed):
+    """Shuffled rows, single-member / zero-variance groups, odd rewards, several step_index per group: every output list == the
+    reference's own populate_rl_data (oracle/_ref, pandas) as Python floats."""
+    from fuzz_advantage import fuzz
+    ok, msg = fuzz(seed)
+    print(msg)
+    assert ok, msg
+
+
 def test_bucket_roundtrip_bit_exact():
     from pipelinerl_swe_b200 import ops
     d = _dev()
