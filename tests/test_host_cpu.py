@@ -391,3 +391,66 @@ def test_make_slices_can_carry_the_boundary_target():
             pairs.append((ids[-1], int(s.boundary["input_ids"][0, 0])))
     full = pbe.input_ids[0].tolist()
     assert pairs == list(zip(full[:-1], full[1:]))
+
+
+def test_batch_type_behaves_like_the_reference_batch_type():
+    """PipelineBatchEncoding (validators, make_slices, to_device, error messages) against the reference's own class staged in
+    oracle/_ref (finetune/types.py:48-178), on random packed rows built from lists / ndarrays / tensors of the wrong dtype."""
+    import random
+
+    import numpy as np
+    from oracle import build_ref
+    if not build_ref.available():
+        pytest.skip("oracle/_ref is not staged on this machine")
+    build_ref.load()
+    import sys as _sys
+    RefPBE = _sys.modules["pipelinerl.finetune.types"].PipelineBatchEncoding
+    from pipelinerl_swe_b200.types import PipelineBatchEncoding as OurPBE
+    long_f = ("input_ids", "attention_mask", "labels", "position_ids")
+    float_f = ("rewards", "advantages", "ref_logprobs", "old_logprobs", "group_tokens", "num_labels", "overflow")
+    rnd = random.Random(5)
+    for case in range(24):
+        n_slices = rnd.choice([1, 2, 4, 8])
+        T = n_slices * rnd.randint(1, 40)
+        b = synthetic_packed_batch([T], 500, seed=case)
+        form = rnd.choice(["tensor", "list", "ndarray", "wrong_dtype"])
+        kw = {}
+        for k in long_f + float_f:
+            v = b[k]
+            if form == "list":
+                v = v.tolist()
+            elif form == "ndarray":
+                v = v.numpy()
+            elif form == "wrong_dtype":
+                v = v.double() if k in float_f else v.int()
+            kw[k] = v
+        kw.update(model_version=case, is_packed=True, seq_boundaries=[0, T], padding=rnd.randint(0, 3), sentinel=bool(case % 5 == 0))
+        ours, ref = OurPBE(**kw), RefPBE(**kw)
+        for k in long_f + float_f + ("seq_boundaries",):
+            a, r = getattr(ours, k), getattr(ref, k)
+            assert a.dtype == r.dtype and a.shape == r.shape and torch.equal(a, r), k
+        so, sr = ours.make_slices(n_slices), ref.make_slices(n_slices)
+        assert len(so) == len(sr) == n_slices
+        for x, y in zip(so, sr):
+            for k in long_f + float_f:
+                assert torch.equal(getattr(x, k), getattr(y, k)), k
+            for k in ("model_version", "sentinel", "is_packed", "padding"):
+                assert getattr(x, k) == getattr(y, k), k
+            assert torch.equal(x.seq_boundaries, y.seq_boundaries)
+            assert getattr(x, "boundary", None) is None          # the carried boundary target is opt-in
+        assert ours.to_device("cpu") is ours
+    # the three ways make_slices refuses, with the reference's exception type and text
+    b = synthetic_packed_batch([12], 50, seed=1)
+    base = {k: b[k] for k in long_f + float_f}
+    for mutate, n in ((lambda d: d.update(position_ids=None), 2), (lambda d: None, 13), (lambda d: None, 5)):
+        d = dict(base, model_version=0, is_packed=True)
+        mutate(d)
+        msgs = []
+        for cls in (OurPBE, RefPBE):
+            with pytest.raises(ValueError) as ei:
+                cls(**d).make_slices(n)
+            msgs.append(str(ei.value))
+        assert msgs[0] == msgs[1], msgs
+    for cls in (OurPBE, RefPBE):     # unsupported input type
+        with pytest.raises(Exception):
+            cls(**dict(base, model_version=0, input_ids="abc"))
