@@ -61,7 +61,10 @@ static int make_tmap_panel(CUtensorMap* tm, const void* ptr, long long rows, lon
 
 // ---- tiling --------------------------------------------------------------------------------
 constexpr int BN = 256;
-constexpr int STAGES_1CTA = 4, STAGES_2CTA = 6, STAGES_BIGM = 4;   // 32 KB, 32 KB(pair: 2 x 16+16) and 48 KB stages
+#ifndef B200_STAGES_2CTA
+#define B200_STAGES_2CTA 6
+#endif
+constexpr int STAGES_1CTA = 4, STAGES_2CTA = B200_STAGES_2CTA, STAGES_BIGM = 4;   // 32 KB, 32 KB(pair: 2 x 16+16) and 48 KB stages
 
 // k-splits for an EPI_STORE GEMM: smallest split count whose wave efficiency is within 1% of the
 // best reachable with <= 8 splits (each split costs an f32 slab round trip through HBM).
