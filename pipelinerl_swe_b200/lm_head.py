@@ -77,7 +77,7 @@ def fold_main_grad(model: nn.Module, zero: bool = True) -> None:
         if mg is None:
             continue
         if p.grad is None:
-            p.grad = mg.to(p.dtype)
+            p.grad = mg.to(p.dtype, copy=True)   # copy: an f32 parameter would otherwise alias the buffer zeroed below
         else:
             p.grad.add_(mg.to(p.dtype))
         if zero:
@@ -120,8 +120,9 @@ def row_chunks(M: int, Vloc: int, budget: int | None = None) -> list[tuple[int, 
 class _GradSink:
     """Carries the weight Parameter into the autograd Function without making it a differentiable input twice."""
 
-    def __init__(self, param):
+    def __init__(self, param, force_w: bool = False):
         self.param = param
+        self.force_w = force_w    # the operand handed to the Function is a detached cast of ``param``: dW must go to main_grad
 
 
 class LMHeadLogprobFunction(torch.autograd.Function):
@@ -137,7 +138,10 @@ class LMHeadLogprobFunction(torch.autograd.Function):
                 entropy_grad: bool = True):
         M, H = hidden.shape
         Vloc = weight.shape[0]
-        need_bwd = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+        # an fp32 (or fp16) master weight under fused accumulation: the bf16 operand is a detached cast, the f32 gradient goes
+        # straight to the master's main_grad through the sink, autograd sees no weight gradient at all
+        ctx.sink_forces_w = bool(sink is not None and sink.force_w)
+        need_bwd = ctx.needs_input_grad[0] or ctx.needs_input_grad[1] or ctx.sink_forces_w
         chunks = row_chunks(M, Vloc)
         # keep bf16 logits for a recompute-free backward when a backward will follow: the whole micro-batch when it fits
         # the budget, else its first row chunk (the other chunks are recomputed in the backward)
@@ -176,7 +180,7 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         # entropy_grad False (rl_step with entropy_bonus == 0: K3's dLoss/dentropy is identically zero): the backward runs
         # its GEMMs straight on the saved exponentials, no [tokens x vocab] dlogits pass
         coef_lp, coef_ent = g[:, 0].contiguous(), (g[:, 1].contiguous() if ctx.entropy_grad else None)
-        need_h, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        need_h, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1] or ctx.sink_forces_w
         saved, ctx.saved = ctx.saved, None  # consumed in place by the backward; a second backward recomputes
         chunks, group = ctx.chunks, ctx.group
         M, H = hidden.shape
@@ -188,7 +192,7 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         gw, gw_ret, acc_first = None, None, False
         if need_w:
             sink = ctx.sink
-            if sink is not None and fused_grad_accumulation_enabled():
+            if sink is not None and (fused_grad_accumulation_enabled() or ctx.sink_forces_w):
                 p = sink.param
                 if getattr(p, "main_grad", None) is None:
                     p.main_grad = torch.zeros(weight.shape, dtype=torch.float32, device=weight.device)
@@ -250,9 +254,19 @@ def lmhead_logprobs(hidden: torch.Tensor, weight: torch.Tensor, input_ids: torch
     h2 = hidden.reshape(B * L, H)
     if h2.dtype != torch.bfloat16:
         h2 = h2.to(torch.bfloat16)
-    w = weight if weight.dtype == torch.bfloat16 else weight.to(torch.bfloat16)
     inv_t = 1.0 / float(temperature)
-    sink = _GradSink(weight) if (isinstance(weight, nn.Parameter) and w is weight) else None   # fused f32 accumulate target
+    is_param = isinstance(weight, nn.Parameter)
+    if weight.dtype == torch.bfloat16:
+        w = weight
+        sink = _GradSink(weight) if is_param else None       # fused f32 accumulate target
+    elif is_param and weight.requires_grad and hidden.requires_grad and fused_grad_accumulation_enabled() and torch.is_grad_enabled():
+        # fp32 master weights (torch AMP / accelerate mixed precision): the GEMMs read a bf16 cast made per call -- what autocast
+        # does for F.linear -- and dW is accumulated in f32 straight into weight.main_grad; no bf16 [V,H] gradient, no cast back
+        w = weight.detach().to(torch.bfloat16)
+        sink = _GradSink(weight, force_w=True)
+    else:
+        w = weight.to(torch.bfloat16)                        # autograd casts the bf16 gradient back to the parameter's dtype
+        sink = None
     if labels is not None and skip_masked_tokens_enabled():
         keep = torch.roll(labels, shifts=-1, dims=1) != -100
         keep[:, -1] = False if boundary_labels is None else (boundary_labels != -100)   # no next token unless it is carried

@@ -372,6 +372,45 @@ def test_lmhead_random_shapes_and_variants(seed):
     assert ok, msg
 
 
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
+def test_rl_step_with_master_weights_in_another_dtype(dtype, fused):
+    """fp32 (torch AMP / accelerate mixed precision) or fp16 parameters: the GEMMs read a bf16 cast, exactly what a bf16 model
+    holding those cast values computes; gradients come back in the parameter's dtype, or -- fused accumulation -- as f32
+    ``main_grad`` on the master weight with no bf16 [V,H] temporary."""
+    from pipelinerl_swe_b200 import RLConfig, fold_main_grad, rl_step, set_fused_grad_accumulation
+    T, H, V = 300, 136, 1032
+    batch = _to_dev(synthetic_packed_batch([100, 120, 80], V, seed=11))
+    cfg = RLConfig(batch_size=4, kl_coef=0.05, final_kl_coef=0.05)
+    md = StubLM(H, V, T, seed=3, dtype=dtype).to(_dev())
+    mb = StubLM(H, V, T, seed=3).to(_dev())
+    with torch.no_grad():
+        mb.hidden.copy_(md.hidden.to(torch.bfloat16))
+        mb.lm_head.weight.copy_(md.lm_head.weight.to(torch.bfloat16))
+    set_fused_grad_accumulation(fused)
+    try:
+        out = []
+        for m in (md, mb):
+            for _ in range(2):                       # two micro-batches accumulate
+                loss, stats = rl_step(m, batch, 0, 1, cfg)
+                loss.backward()
+            out.append((loss.item(), stats))
+        assert out[0][0] == out[1][0] and out[0][1] == out[1][1]      # same kernels on the same bf16 values
+        assert md.hidden.grad.dtype == dtype
+        assert _rel(md.hidden.grad, mb.hidden.grad) < 2e-3            # the bf16 dH cast to the parameter's dtype
+        if fused:
+            assert md.lm_head.weight.grad is None and md.lm_head.weight.main_grad.dtype == torch.float32
+            assert torch.equal(md.lm_head.weight.main_grad, mb.lm_head.weight.main_grad)
+            fold_main_grad(md)
+            assert md.lm_head.weight.grad.dtype == dtype and float(md.lm_head.weight.main_grad.abs().max()) == 0.0
+            assert _rel(md.lm_head.weight.grad, mb.lm_head.weight.main_grad) < (1e-6 if dtype == torch.float32 else 2e-3)
+        else:
+            assert md.lm_head.weight.grad.dtype == dtype
+            assert _rel(md.lm_head.weight.grad, mb.lm_head.weight.grad) < 1e-2   # two bf16 micro-batch gradients summed in dtype vs in bf16
+    finally:
+        set_fused_grad_accumulation(False)
+
+
 @pytest.mark.parametrize("seed", [300, 301, 302])
 def test_rl_step_random_configs_vs_the_reference_rl_step(seed):
     """Whole drop-in (rl_step + backward) against the reference's own rl_step (oracle/_ref) over random batches and RLConfigs."""
