@@ -40,6 +40,21 @@ enum { TUNE_TWO_CTA = 0, TUNE_DH_KSPLIT, TUNE_DW_KSPLIT, TUNE_TAIL_SPLIT, TUNE_F
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 int sm_count();  // multiprocessors of the current device (cached)
+// One-time set-up that is PER DEVICE (kernel function attributes such as the dynamic shared-memory limit belong to the
+// device's context): first() is true the first time it is asked on the current device.  A process that drives several
+// GPUs configures each of them; a racing second thread at worst repeats a harmless cudaFuncSetAttribute.
+struct PerDeviceOnce {
+  unsigned long long done = 0;
+  bool first() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+    const unsigned long long bit = 1ull << dev;
+    if (done & bit) return false;
+    done |= bit;
+    return true;
+  }
+};
+
 void count_launch(int n = 1);  // kernel launches issued by this library (b200grpo_launch_count)
 
 // ---- optional per-launch timing (b200grpo_profile_*): CUDA events on the launching stream ----

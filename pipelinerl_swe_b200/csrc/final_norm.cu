@@ -318,11 +318,10 @@ extern "C" int b200grpo_final_norm_bwd(const void* x, int64_t ldx, const void* g
   const size_t ring_bytes = (size_t)FN_DEPTH * 2 * H * sizeof(__nv_bfloat16);
 #define FN_BWD_ONE(N, TH, V)                                                                                                    \
   do {                                                                                                                          \
-    static bool configured = false;                                                                                             \
-    if (!configured) {                                                                                                          \
+    static PerDeviceOnce configured;                                                                                                   \
+    if (configured.first()) {                                                                                                          \
       B200_CUDA_OK(cudaFuncSetAttribute(final_norm_bwd_kernel<N, TH, V>, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
                                         FN_DEPTH * 2 * 8 * TH * N * (int)sizeof(__nv_bfloat16)));                               \
-      configured = true;                                                                                                        \
     }                                                                                                                           \
     final_norm_bwd_kernel<N, TH, V><<<grid, TH, ring_bytes, st>>>(xp, ldx, gp, rstd, dp, lddy, dvalue, wp, T, H, op, lddx, part, part_b); \
   } while (0)

@@ -89,10 +89,9 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   static_assert(BN == PANEL_W, "panels are one N tile wide");
   static_assert(L::TOTAL <= 227 * 1024, "shared memory budget");
   auto kern = gemm_sm100_kernel<kEpi, kAMajor, kBMajor, kCtas, BN, kStages, kSave, kAPanel, kMRep>;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;
+  if (configured.first()) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-    configured = true;
   }
   B200_REQUIRE((long long)p.m_blocks * p.n_blocks * p.k_splits < (1ll << 30), "gemm: too many tiles");
   const long long n_items = p.n_items;
@@ -871,10 +870,9 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
       const size_t cap = 200 * 1024;
       while (warps > 1 && (size_t)warps * H * 4 > cap) warps >>= 1;
       B200_REQUIRE((size_t)warps * H * 4 <= cap, "lmhead_bwd: hidden size %d too large for the target-row kernel", H);
-      static bool configured = false;
-      if (!configured) {
+      static PerDeviceOnce configured;
+      if (configured.first()) {
         B200_CUDA_OK(cudaFuncSetAttribute(dw_target_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap));
-        configured = true;
       }
       dw_target_kernel<<<ceil_div(M, warps), warps * 32, (size_t)warps * H * 4, st>>>(
           (const __nv_bfloat16*)hidden, ldh, row_key, row_coef, M, H, grad_weight, ldgw, grad_weight_is_f32); count_launch();

@@ -17,6 +17,40 @@ from ._abi import LossCfg, M_COUNT, check, lib
 _ws_cache: dict[tuple[int, str], torch.Tensor] = {}
 
 
+def _first_cuda_tensor(args):
+    for a in args:
+        if isinstance(a, torch.Tensor):
+            if a.is_cuda:
+                return a
+        elif isinstance(a, (list, tuple)):
+            t = _first_cuda_tensor(a)
+            if t is not None:
+                return t
+        elif isinstance(a, dict):
+            t = _first_cuda_tensor(a.values())
+            if t is not None:
+                return t
+    return None
+
+
+def _on_tensor_device(fn):
+    """Run ``fn`` with the device of its first CUDA tensor argument current: the library launches on the CURRENT device and
+    stream, so a caller that holds tensors on cuda:1 while cuda:0 is current (one process driving several GPUs, a model moved
+    without ``torch.cuda.set_device``) is served like torch serves it.  One integer comparison when the device already is current."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        t = _first_cuda_tensor(args)
+        if t is None:
+            t = _first_cuda_tensor(kwargs.values())
+        if t is None or t.device.index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(t.device):
+            return fn(*args, **kwargs)
+    return wrapper
+
+
 def _workspace(device: torch.device, nbytes: int, tag: str = "main") -> torch.Tensor:
     """Grow-only per-device scratch; calls are stream-ordered so one buffer per tag suffices."""
     key = (device.index if device.index is not None else torch.cuda.current_device(), tag)
@@ -51,6 +85,7 @@ def lmhead_saved_buffer(M: int, H: int, V: int, device) -> torch.Tensor:
     return torch.empty(n, dtype=torch.uint8, device=device)
 
 
+@_on_tensor_device
 def lmhead_fwd_stats(hidden: torch.Tensor, weight: torch.Tensor, targets: torch.Tensor, inv_temperature: float,
                      v_offset: int = 0, saved: torch.Tensor | None = None, stats_mc: int | None = None) -> torch.Tensor | None:
     """K1: per-row (max, sumexp, sum e*z, z_target) over this rank's vocab rows -> f32 [M,4].
@@ -74,6 +109,7 @@ def lmhead_fwd_stats(hidden: torch.Tensor, weight: torch.Tensor, targets: torch.
     return stats
 
 
+@_on_tensor_device
 def lmhead_finalize(stats: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
     """stats f32 [R,M,4] (or [M,4]) -> (logprob, entropy, lse) f32 [M]."""
     _req(stats, torch.float32, "stats")
@@ -85,6 +121,7 @@ def lmhead_finalize(stats: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, to
     return out[0], out[1], out[2]
 
 
+@_on_tensor_device
 def lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, inv_temperature, v_offset=0, grad_scale=None,
                need_grad_hidden=True, need_grad_weight=True, grad_weight_out: torch.Tensor | None = None,
                accumulate: bool = False, saved: torch.Tensor | None = None, stages: int | None = None,
@@ -126,6 +163,7 @@ def lmhead_bwd(hidden, weight, targets, lse, entropy, coef_lp, coef_ent, inv_tem
     return gh, gw
 
 
+@_on_tensor_device
 def token_loss(logprob, entropy, batch: dict, cfg: LossCfg, values=None):
     """K3 -> (loss f32[1], metrics f64[M_COUNT], coef_lp, coef_ent, coef_value|None)."""
     labels = _req(batch["labels"], torch.int64, "labels")
@@ -154,6 +192,7 @@ def token_loss(logprob, entropy, batch: dict, cfg: LossCfg, values=None):
     return loss, metrics, coef[0], coef[1], coef_v
 
 
+@_on_tensor_device
 def segment_bounds(position_ids: torch.Tensor) -> torch.Tensor:
     """int32 boundaries [S+1] of a packed row, as rl/__init__.py:159-170 (one D2H sync for S)."""
     pos = _req(position_ids.reshape(-1), torch.int64, "position_ids")
@@ -165,6 +204,7 @@ def segment_bounds(position_ids: torch.Tensor) -> torch.Tensor:
     return bounds[: int(n.item())]
 
 
+@_on_tensor_device
 def gemm_bf16(A: torch.Tensor, B: torch.Tensor, a_mn_major=False, b_mn_major=False, out_dtype=torch.float32,
               out: torch.Tensor | None = None, accumulate=False, group_m: int = 0, k_splits: int = 1) -> torch.Tensor:
     """C[M,N] = A.B^T on the tcgen05 mainloop (test surface).  MN-major operands are given as [K, M|N]."""
@@ -182,6 +222,7 @@ def gemm_bf16(A: torch.Tensor, B: torch.Tensor, a_mn_major=False, b_mn_major=Fal
     return out
 
 
+@_on_tensor_device
 def group_order(group_key: torch.Tensor, n_groups: int) -> tuple[torch.Tensor, torch.Tensor]:
     """(row_order i32[n_rows], group_starts i32[n_groups+1]): rows stably sorted by dense group key -- the CSR K4 walks."""
     order = torch.argsort(group_key, stable=True).to(torch.int32)
@@ -191,6 +232,7 @@ def group_order(group_key: torch.Tensor, n_groups: int) -> tuple[torch.Tensor, t
     return order, starts
 
 
+@_on_tensor_device
 def group_advantage(row_reward: torch.Tensor, group_key: torch.Tensor, row_offsets: torch.Tensor, n_labels: torch.Tensor,
                     has_eos: torch.Tensor, n_groups: int, divide_by_std: bool, token_rewards: torch.Tensor | None = None,
                     row_order: torch.Tensor | None = None, group_starts: torch.Tensor | None = None, want_f64: bool = False):
@@ -216,6 +258,7 @@ def group_advantage(row_reward: torch.Tensor, group_key: torch.Tensor, row_offse
     return (out, adv64) if want_f64 else out
 
 
+@_on_tensor_device
 def group_advantage_rows(row_reward: torch.Tensor, group_key: torch.Tensor, row_offsets: torch.Tensor, n_groups: int,
                          divide_by_std: bool, row_order: torch.Tensor | None = None,
                          group_starts: torch.Tensor | None = None) -> torch.Tensor:
@@ -251,6 +294,7 @@ def bucket_numel(tensors: Sequence[torch.Tensor]) -> int:
     return int(lib().b200grpo_bucket_numel(numel, n))
 
 
+@_on_tensor_device
 def bucket_pack(tensors: Sequence[torch.Tensor], bucket: torch.Tensor) -> None:
     """K6: gather parameters (bf16, or f32 cast on the fly) into one contiguous bf16 bucket."""
     _req(bucket, torch.bfloat16, "bucket")
@@ -260,6 +304,7 @@ def bucket_pack(tensors: Sequence[torch.Tensor], bucket: torch.Tensor) -> None:
     check(lib().b200grpo_bucket_pack(ptrs, numel, is_f32, n, bucket.data_ptr(), bucket.numel(), ws.data_ptr(), ws.numel(), _stream()))
 
 
+@_on_tensor_device
 def bucket_pack_multicast(tensors: Sequence[torch.Tensor], mc_ptr: int, capacity: int) -> None:
     """K6 + broadcast in one pass: pack into the NVSwitch multicast mapping ``mc_ptr`` (bf16 elements, ``capacity`` of them)."""
     ptrs, numel, is_f32 = _tensor_table(tensors)
@@ -268,6 +313,7 @@ def bucket_pack_multicast(tensors: Sequence[torch.Tensor], mc_ptr: int, capacity
     check(lib().b200grpo_bucket_pack_multicast(ptrs, numel, is_f32, n, C.c_void_p(mc_ptr), int(capacity), ws.data_ptr(), ws.numel(), _stream()))
 
 
+@_on_tensor_device
 def bucket_pack_scatter(tensors: Sequence[torch.Tensor], peer_ptrs: Sequence[int], stripe_elems: int, capacity: int) -> None:
     """K6 + scatter in one pass: stripe j of the packed bucket is stored into ``peer_ptrs[j % len(peer_ptrs)]`` (device
     pointers to the receivers' copies of a symmetric slot, P2P-mapped) -- the first half of the scatter + relay broadcast."""
@@ -294,6 +340,7 @@ def bucket_relay_p2p(local_ptr: int, peer_ptrs: Sequence[int], numel: int, peer_
     check(lib().b200grpo_bucket_relay_p2p(C.c_void_p(local_ptr), peers, int(numel), int(peer_index), q, int(stripe_elems), int(ctas), _stream()))
 
 
+@_on_tensor_device
 def bucket_unpack(bucket: torch.Tensor, tensors: Sequence[torch.Tensor]) -> None:
     """K6 inverse: scatter a received bucket into the destination parameters."""
     _req(bucket, torch.bfloat16, "bucket")
@@ -303,6 +350,7 @@ def bucket_unpack(bucket: torch.Tensor, tensors: Sequence[torch.Tensor]) -> None
     check(lib().b200grpo_bucket_unpack(bucket.data_ptr(), ptrs, numel, is_f32, n, ws.data_ptr(), ws.numel(), _stream()))
 
 
+@_on_tensor_device
 def final_norm_fwd(x: torch.Tensor, gamma: torch.Tensor, eps: float, value_w: torch.Tensor | None = None,
                    value_b: torch.Tensor | None = None) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor | None]:
     """Final RMSNorm (+ value head) in one sweep: x bf16 [T,H] -> (y bf16 [T,H], rstd f32 [T], value f32 [T] | None)."""
@@ -322,6 +370,7 @@ def final_norm_fwd(x: torch.Tensor, gamma: torch.Tensor, eps: float, value_w: to
     return y, rstd, value
 
 
+@_on_tensor_device
 def final_norm_bwd(x: torch.Tensor, gamma: torch.Tensor, rstd: torch.Tensor, dy: torch.Tensor,
                    dvalue: torch.Tensor | None = None, value_w: torch.Tensor | None = None):
     """-> (dx bf16 [T,H], dgamma f32 [H], dvalue_w f32 [H] | None, dvalue_b f32 [1] | None)."""

@@ -107,3 +107,31 @@ def test_weight_update_call_shapes_and_transports_two_gpus():
            "--master-port", "29561", os.path.join(root, "tools", "check_weight_update.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "WEIGHT_UPDATE" in out.stdout and " OK " in out.stdout, out.stdout[-2000:] + out.stderr[-3000:]
+
+
+def test_one_process_second_gpu_while_the_first_is_current():
+    """A process that holds its model and batch on cuda:1 while cuda:0 is the current device (no ``torch.cuda.set_device``) gets
+    the same step as on cuda:0 -- torch code behaves that way, so the drop-in must too: the wrappers make the tensors' device
+    current for the launch, and kernel attributes (dynamic shared-memory limits) are configured per device."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from helpers import StubLM, synthetic_packed_batch
+    from pipelinerl_swe_b200 import RLConfig, ops, rl_step
+    T, H, V = 700, 264, 5000
+    batch = synthetic_packed_batch([300, 250, 150], V, seed=4)
+    cfg = RLConfig(batch_size=4, kl_coef=0.1, final_kl_coef=0.1)
+    assert torch.cuda.current_device() == 0
+    res = []
+    for dev in ("cuda:1", "cuda:0", "cuda:1"):       # cuda:1 first: nothing has been configured on any device yet in this test
+        model = StubLM(H, V, T, seed=5).to(dev)
+        b = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+        loss, stats = rl_step(model, b, 0, 1, cfg)
+        loss.backward()
+        assert loss.device == torch.device(dev) and model.lm_head.weight.grad.device == torch.device(dev)
+        res.append((loss.item(), stats, model.lm_head.weight.grad.cpu(), model.hidden.grad.cpu()))
+        assert torch.cuda.current_device() == 0      # the caller's current device is left alone
+    for r in res[1:]:
+        assert r[0] == res[0][0] and r[1] == res[0][1]
+        assert torch.equal(r[2], res[0][2]) and torch.equal(r[3], res[0][3])
+    pos = torch.randint(0, 50, (5000,), device="cuda:1")
+    assert ops.segment_bounds(pos).cpu().tolist() == ops.segment_bounds(pos.to("cuda:0")).cpu().tolist()
