@@ -248,3 +248,79 @@ def check_error_case(name, mutate, dev="cuda:0"):
         except Exception as e:  # noqa: BLE001
             out.append(type(e))
     return tuple(out)
+
+
+# ---- autograd usage patterns a trainer may apply to the returned loss ----------------------------------------------------------
+def usage_patterns(dev="cuda:0"):
+    """Each pattern is run on the reference arm and on the drop-in with identical inputs; returns [(name, ok, detail)]."""
+    kind, mod, PBE = _reference()
+    from pipelinerl_swe_b200 import RLConfig, rl_step
+    out = []
+
+    def both(case):
+        ref_model = _RefLM(case["hidden"].to(dev), case["weight"].to(dev), None)
+        our_model = _OurLM(case["hidden"], case["weight"], None).to(dev)
+        b = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in case["batch"].items()}
+
+        def ref_step():
+            if kind == "reference":
+                return mod.rl_step(ref_model, PBE(**case["batch"], model_version=0).to_device(dev), case["step"], case["max_step"], mod.RLConfig(**case["cfg"]))
+            return mod.oracle_rl_step(ref_model.hidden[0] if b["is_packed"] else ref_model.hidden, ref_model.weight, b, case["step"], case["max_step"],
+                                      mod.OracleRLConfig(**case["cfg"]))
+
+        def our_step():
+            return rl_step(our_model, b, case["step"], case["max_step"], RLConfig(**case["cfg"]))
+        return ref_model, our_model, ref_step, our_step
+
+    def grads_close(ref_model, our_model):
+        e1 = _rel(our_model.lm_head.weight.grad, ref_model.weight.grad)
+        e2 = _rel(our_model.hidden.grad.reshape(ref_model.hidden.grad.shape), ref_model.hidden.grad)
+        return max(e1, e2) < GRAD_RTOL, f"dW {e1:.2e} dH {e2:.2e}"
+
+    def base_case(seed, **cfg):
+        case = draw_case(random.Random(seed), seed)
+        case["values"] = None
+        case["cfg"].update(value_loss_coef=0.0, **cfg)
+        return case
+
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        # 1. scaled loss (gradient accumulation: DeepSpeed / accelerate divide the loss before backward)
+        rm, om, rs, os_ = both(base_case(901))
+        (rs()[0] * 0.25).backward(); (os_()[0] * 0.25).backward()
+        out.append(("scaled_loss", *grads_close(rm, om)))
+        # 2. two micro-batches' losses summed, ONE backward (both graphs alive at once; entropy term on)
+        rm, om, rs, os_ = both(base_case(902, entropy_bonus=0.01, final_entropy_bonus=0.01))
+        (rs()[0] + 2.0 * rs()[0]).backward(); (os_()[0] + 2.0 * os_()[0]).backward()
+        out.append(("two_graphs_one_backward", *grads_close(rm, om)))
+        # 3. the same graph backpropagated twice (retain_graph): the saved exponentials are consumed by the first pass
+        rm, om, rs, os_ = both(base_case(903))
+        lr, lo = rs()[0], os_()[0]
+        lr.backward(retain_graph=True); lr.backward()
+        lo.backward(retain_graph=True); lo.backward()
+        out.append(("backward_twice", *grads_close(rm, om)))
+        # 4. evaluation: no_grad -> same loss and stats, nothing to backpropagate
+        rm, om, rs, os_ = both(base_case(904))
+        with torch.no_grad():
+            (lr, sr), (lo, so) = rs(), os_()
+        ok = (not lo.requires_grad) and abs(float(lo) - float(lr)) <= LOSS_RTOL * abs(float(lr)) + 1e-5 and set(so) == set(sr)
+        out.append(("no_grad", ok, f"loss {float(lo)} vs {float(lr)}"))
+        # 5. torch.autograd.grad with respect to the hidden states only (no weight gradient wanted)
+        rm, om, rs, os_ = both(base_case(905))
+        (gr,) = torch.autograd.grad(rs()[0], rm.hidden)
+        (go,) = torch.autograd.grad(os_()[0], om.hidden)
+        e = _rel(go.reshape(gr.shape), gr)
+        out.append(("grad_wrt_hidden_only", e < GRAD_RTOL and om.lm_head.weight.grad is None, f"dH {e:.2e}"))
+        # 6. a side stream
+        rm, om, rs, os_ = both(base_case(906))
+        rs()[0].backward()
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            os_()[0].backward()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        out.append(("side_stream", *grads_close(rm, om)))
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    return out

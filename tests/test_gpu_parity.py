@@ -420,6 +420,15 @@ def test_rl_step_random_configs_vs_the_reference_rl_step(seed):
     assert ok, msg
 
 
+def test_rl_step_autograd_usage_patterns_match_the_reference():
+    """Scaled loss, two graphs alive + one backward, backward twice, no_grad evaluation, autograd.grad w.r.t. hidden only, a side
+    stream: same gradients as the reference's rl_step under the same use."""
+    from fuzz_rl_step import usage_patterns
+    res = usage_patterns()
+    print(res)
+    assert all(ok for _, ok, _ in res), [r for r in res if not r[1]]
+
+
 def test_rl_step_raises_what_the_reference_raises():
     """Non-finite inputs, group_tokens <= 0, unknown policy_loss: the same exception TYPE as the reference's rl_step (rl/__init__.py:209-313)."""
     from fuzz_rl_step import check_error_case, error_cases
