@@ -64,7 +64,10 @@ def set_fused_grad_accumulation(flag: bool) -> None:
     ``lm_head.weight.grad`` in bf16, as for any module.  On: the dW GEMM's epilogue adds straight into the f32 buffer
     ``lm_head.weight.main_grad`` (``red.global.add.v4.f32``; allocated zeroed on first use) and autograd sees no gradient
     for the weight -- no 2 B x V x H temporary per micro-batch, f32 accumulation across the micro-batches of an optimizer
-    step.  The optimizer side reads ``weight.main_grad`` or calls ``fold_main_grad(model)`` before its step."""
+    step.  The optimizer side reads ``weight.main_grad`` or calls ``fold_main_grad(model)`` before its step.
+
+    Precondition: nothing in the trainer may wait for an autograd gradient on ``lm_head.weight`` -- torch DDP's reducer, DeepSpeed
+    ZeRO's reduce hooks and FSDP do; with those keep this off (the default) or fold before THEIR reduction point."""
     global _FUSED_GRAD_ACC
     _FUSED_GRAD_ACC = bool(flag)
 
