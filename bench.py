@@ -290,6 +290,38 @@ def time_rl_step_api(wl, dev, steps, warmup=3):
         return {"unavailable": repr(e)[:200]}
 
 
+def time_cublas_same_box(dev, secs=2.0):
+    """The peak's own recipe on THIS box in THIS run: torch.matmul bf16 8192^3 back to back (MEASURED_PEAKS.json `how`: sustained).
+    Boxes of the pool differ by up to 13 % under the 1 kW cap; this lets `roofline.frac` be read against the box that ran the step.
+    A library GEMM as a yardstick only -- nothing of the measured path touches it."""
+    import torch
+    try:
+        n = 8192
+        a = torch.randn(n, n, device=dev, dtype=torch.bfloat16)
+        b = torch.randn(n, n, device=dev, dtype=torch.bfloat16)
+        c = torch.empty(n, n, device=dev, dtype=torch.bfloat16)
+        for _ in range(20):
+            torch.matmul(a, b, out=c)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        iters = 0
+        t0 = time.time()
+        e0.record()
+        while time.time() - t0 < secs:
+            for _ in range(50):
+                torch.matmul(a, b, out=c)
+            iters += 50
+            torch.cuda.synchronize()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        del a, b, c
+        torch.cuda.empty_cache()
+        return {"bf16_tflops_sustained": 2.0 * n ** 3 / (ms * 1e-3) / 1e12, "seconds": secs, "how": "torch.matmul bf16 8192^3 back to back, this box, this run"}
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": repr(e)[:200]}
+
+
 def time_torch_eager_gpu(wl, dev, steps=8, warmup=2):
     """The [T, V]-sized part of the reference's rl_step in plain torch on this GPU, bf16 like its HF model:
     lm_head -> /temperature -> log_softmax -> softmax -> entropy -> gather (rl/__init__.py:197-208) and autograd
@@ -903,6 +935,10 @@ def run_b200(args):
         torch_gpu = time_torch_eager_gpu(wl, dev)
         if torch_gpu and "value" in torch_gpu:
             torch_gpu["speedup_of_this_repo"] = value / torch_gpu["value"]
+        same_box = time_cublas_same_box(dev)
+        if "bf16_tflops_sustained" in same_box:
+            same_box["frac_of_it"] = roofline["achieved"] / same_box["bf16_tflops_sustained"]
+        roofline["same_box_cublas"] = same_box
 
     # ---------------- CPU baseline (rank 0, N=1 only): the reference's own rl_step on the host cores ----------------
     cpu = None
