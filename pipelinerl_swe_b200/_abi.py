@@ -126,6 +126,12 @@ def lib() -> C.CDLL:
             for name, (res, args) in SIGNATURES.items():
                 fn = getattr(handle, name)
                 fn.restype, fn.argtypes = res, args
+            # experiments: B200GRPO_TUNABLES="name=value,name=value" applies library tunables at load time, so that a whole
+            # test or bench run can be repeated under a non-default kernel schedule
+            for kv in filter(None, os.environ.get("B200GRPO_TUNABLES", "").split(",")):
+                name, _, val = kv.partition("=")
+                if handle.b200grpo_set_tunable(name.strip().encode(), int(val)) < 0:   # returns the previous value (>= 0) or an error code
+                    raise B200GrpoError(f"B200GRPO_TUNABLES: unknown tunable {name!r}")
             _lib = handle
     return _lib
 

@@ -61,10 +61,14 @@ int check_device_sm100() {
 //   same-box (profiles/r01/dw_zigzag_ab.md).
 //   rows_path: 1 = an entropy-free backward (coef_ent == NULL) runs its GEMMs on the saved exponentials; 0 = it forms dlogits
 //   in place first like the entropy path (A/B switch).
+//   lockstep_fwd / lockstep_dh / lockstep_dw: k-blocks per epoch of the soft K-lockstep between the clusters of a wave
+//   (gemm_sm100.cuh lockstep_pace; 0 = off) for the forward / recompute GEMM, dH and dW; lockstep_slack: epochs a cluster may
+//   run ahead of the slowest one.
 static const char* const g_tunable_names[TUNE_COUNT] = {"two_cta", "dh_ksplit", "dw_ksplit", "tail_split", "fwd_group_m", "dh_group_m",
                                                         "dw_group_m", "dw_group_n", "save_logits", "hint_resident", "hint_stream",
-                                                        "dh_big_m", "dw_big_m", "gemm_big_m", "fwd_big_m", "dw_zigzag", "rows_path"};
-static int g_tunables[TUNE_COUNT] = {1, 0, 0, 1, 16, 4, 1, 0, 1, 0, 0, 1, 0, 0, 0, 1, 1};
+                                                        "dh_big_m", "dw_big_m", "gemm_big_m", "fwd_big_m", "dw_zigzag", "rows_path", "lockstep_fwd",
+                                                        "lockstep_dh", "lockstep_dw", "lockstep_slack"};
+static int g_tunables[TUNE_COUNT] = {1, 0, 0, 1, 16, 4, 1, 0, 1, 0, 0, 1, 0, 0, 0, 1, 1, 16, 8, 32, 2};
 int get_tunable(int id) { return g_tunables[id]; }
 
 // ---- profiling ring (diagnostic; single-threaded use) -------------------------------------

@@ -17,7 +17,7 @@ int check_device_sm100();  // 0 or B200GRPO_EARCH / ECUDA (cached per thread)
 int get_tunable(int id);
 enum { TUNE_TWO_CTA = 0, TUNE_DH_KSPLIT, TUNE_DW_KSPLIT, TUNE_TAIL_SPLIT, TUNE_FWD_GROUP_M, TUNE_DH_GROUP_M, TUNE_DW_GROUP_M,
        TUNE_DW_GROUP_N, TUNE_SAVE_LOGITS, TUNE_HINT_RESIDENT, TUNE_HINT_STREAM, TUNE_DH_BIG_M, TUNE_DW_BIG_M, TUNE_GEMM_BIG_M,
-       TUNE_FWD_BIG_M, TUNE_DW_ZIGZAG, TUNE_ROWS_PATH, TUNE_COUNT };
+       TUNE_FWD_BIG_M, TUNE_DW_ZIGZAG, TUNE_ROWS_PATH, TUNE_LOCKSTEP_FWD, TUNE_LOCKSTEP_DH, TUNE_LOCKSTEP_DW, TUNE_LOCKSTEP_SLACK, TUNE_COUNT };
 
 #define B200_CUDA_OK(expr)                                                              \
   do {                                                                                  \

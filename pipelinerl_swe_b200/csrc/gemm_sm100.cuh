@@ -3,7 +3,8 @@
 //   D[M,N] (f32 in TMEM) = A[M,K] . B[N,K]^T          bf16 operands, fp32 accumulate
 //
 // One CTA owns 128 * kMRep rows x BLOCK_N columns of a tile (a cta_group::2 pair: twice the rows):
-//   warp 0 lane 0 : TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem ring)
+//   warp 0 lane 0 : TMA producer of operand A (cp.async.bulk.tensor -> 128B-swizzled smem ring)
+//   warp 3 lane 0 : TMA producer of operand B
 //   warp 1 lane 0 : MMA issuer    (tcgen05.mma; kMRep MMAs per k-step share one B tile in shared memory)
 //   warp 2        : TMEM allocator
 //   warps 4..7    : epilogue of accumulator rows 0-127   (tcgen05.ld: thread == row, 32 columns per load)
@@ -29,6 +30,7 @@
 #pragma once
 #include "common.cuh"
 #include "sm100_ptx.cuh"
+#include <type_traits>
 
 namespace b200grpo {
 
@@ -54,6 +56,13 @@ struct GemmParams {
   unsigned long long hint_a, hint_b;   // L2 eviction policy of the A / B operand loads
   int zigzag;               // odd tiles of a cluster walk K backwards: the operand rows touched last by one wave are the first
                             // the next wave asks L2 for (K-long operands that do not fit L2 whole, i.e. dW)
+  // soft K-lockstep (optional): the clusters of a wave pace their operand loads on shared progress counters so that tiles
+  // which share operand rows ask L2 for them within its residency window (see launch_gemm)
+  unsigned* sync;           // [waves][sync_epochs] arrival counters, zeroed before the launch; nullptr = off
+  int sync_kb;              //   k-blocks per epoch
+  int sync_epochs;          //   epochs per full-K tile
+  int sync_full;            //   full-K items of the launch (items [0, sync_full) are dealt wave by wave)
+  int sync_slack;           //   epochs a cluster may lead the slowest cluster of its wave by
   // EPI_STORE
   void* C;
   long long ldc;
@@ -318,6 +327,24 @@ __device__ __forceinline__ void store_chunk(const GemmParams& p, uint32_t (&v)[3
   }
 }
 
+// Soft K-lockstep of the producers of one wave.  Every cluster announces each epoch (sync_kb k-blocks) of its tile on a counter
+// shared by the wave, and does not start loading epoch e before all clusters of the wave have STARTED epoch e - sync_slack:
+// the clusters then walk K within sync_slack + 1 epochs of one another, so an operand row fetched from DRAM for one tile is
+// still in L2 when the other tiles of its row / column block ask for it.  Pacing only: the wait gives up after LOCKSTEP_WAIT_NS
+// (a cluster that is not resident yet, a concurrent kernel holding SMs) -- results never depend on it and nothing can hang.
+constexpr unsigned long long LOCKSTEP_WAIT_NS = 20000ull;
+__device__ __forceinline__ void lockstep_pace(const GemmParams& p, int wave, int epoch, int n_clusters) {
+  unsigned* c = p.sync + (long long)wave * p.sync_epochs + epoch;
+  atomicAdd(c, 1u);
+  if (epoch < p.sync_slack) return;
+  const int rem = p.sync_full - wave * n_clusters;
+  const unsigned need = (unsigned)(rem < n_clusters ? rem : n_clusters);
+  const volatile unsigned* w = c - p.sync_slack;
+  if (*w >= need) return;
+  const unsigned long long t0 = ptx::globaltimer_ns();
+  while (*w < need && ptx::globaltimer_ns() - t0 < LOCKSTEP_WAIT_NS) __nanosleep(64);
+}
+
 // ---------------------------------------------------------------------------------------
 // The kernel.  kMRep = 1: 128 rows per CTA, two accumulator stages (epilogue overlaps the next
 // tile's MMAs).  kMRep = 2: 256 rows per CTA = two 128-row MMAs per k-step that share one B tile
@@ -360,7 +387,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     ptx::prefetch_tensormap(&tm_b);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < kStages; ++i) { ptx::mbar_init(&full_bar[i], kCtas); ptx::mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < kStages; ++i) { ptx::mbar_init(&full_bar[i], 2 * kCtas); ptx::mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], 128 * kCtas * kMRep); }
     ptx::fence_mbar_init();
   }
@@ -371,54 +398,75 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
-  if (warp == 0 && lane == 0) {
-    // ===================== TMA producer =====================
-    uint32_t stage = 0, phase = 0, tile_iter = 0;
-    for (int item = cluster_id; item < n_items; item += n_clusters, ++tile_iter) {
-      const Item it = decode_item(p, item);
-      const int m0 = (it.m_blk * kCtas + (int)cta_rank) * CTA_M;
-      const int n0 = it.nb * BLOCK_N + (int)cta_rank * LOAD_N;
-      const bool rev = p.zigzag && (tile_iter & 1);
-      for (int kbi = it.kb0; kbi < it.kb1; ++kbi) {
-        const int kb = rev ? it.kb1 - 1 - (kbi - it.kb0) : kbi;
-        ptx::mbar_wait(&empty_bar[stage], phase ^ 1, 1);
-        uint8_t* sa = smem + stage * L::STAGE_BYTES;
-        uint8_t* sb = sa + L::A_BYTES;
-        if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], L::STAGE_BYTES * kCtas);
-        else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
-        const int k0 = kb * GEMM_BLOCK_K;
-        auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
-          const uint64_t pol = tm == &tm_a ? p.hint_a : p.hint_b;
-          if constexpr (kCtas == 1) ptx::tma_load_2d_hint(dst, tm, &full_bar[stage], c0, c1, pol);
-          else ptx::tma_load_2d_pair_hint(dst, tm, &full_bar[stage], c0, c1, pol);
-        };
-        auto load3 = [&](void* dst, const CUtensorMap* tm, int c0, int c1, int c2) {
-          if constexpr (kCtas == 1) ptx::tma_load_3d_hint(dst, tm, &full_bar[stage], c0, c1, c2, p.hint_a);
-          else ptx::tma_load_3d_pair_hint(dst, tm, &full_bar[stage], c0, c1, c2, p.hint_a);
-        };
-        if constexpr (kAPanel) {  // A lives in 256-column panels: element (r, c) at panel c/256, row r, column c%256
-          if constexpr (kAMajor == MAJOR_K) {
-            load3(sa, &tm_a, k0 % PANEL_W, m0, k0 / PANEL_W);        // box {64 k, CTA_M rows, 1}
-          } else {
-#pragma unroll
-            for (int a = 0; a < CTA_M / 64; ++a)
-              load3(sa + a * 8192, &tm_a, (m0 + a * 64) % PANEL_W, k0, (m0 + a * 64) / PANEL_W);  // box {64 m, 64 k, 1}
+  if ((warp == 0 || warp == 3) && lane == 0) {
+    // ===================== TMA producers =====================
+    // Two of them: warp 0 copies operand A, warp 3 operand B, each with its own walk over the items and the ring.  One
+    // thread issuing every copy of a k-block executes ~110 instructions per k-block for dW's four copies (coordinates,
+    // an ELECT / R2UR broadcast sequence per TMA operand, barrier traffic) -- about the 512 cycles the k-block's MMAs
+    // take, so the producer, not the tensor pipe, set the pace there.  Split in two, each stays well ahead.
+    auto produce = [&](auto a_side) {
+      constexpr bool kA = decltype(a_side)::value;
+      uint32_t stage = 0, phase = 0, tile_iter = 0;
+      for (int item = cluster_id; item < n_items; item += n_clusters, ++tile_iter) {
+        const Item it = decode_item(p, item);
+        const int m0 = (it.m_blk * kCtas + (int)cta_rank) * CTA_M;
+        const int n0 = it.nb * BLOCK_N + (int)cta_rank * LOAD_N;
+        const bool rev = p.zigzag && (tile_iter & 1);
+        const bool pace = kA && p.sync != nullptr && leader && it.slot < 0;
+        int pace_left = 0, pace_epoch = 0;          // k-blocks until the next epoch mark (no division in the loop)
+        int kb = rev ? it.kb1 - 1 : it.kb0;
+        const int kb_step = rev ? -1 : 1;
+        for (int kbi = it.kb0; kbi < it.kb1; ++kbi, kb += kb_step) {
+          if (pace) {
+            if (pace_left == 0) {
+              lockstep_pace(p, (int)tile_iter, pace_epoch++, n_clusters);
+              pace_left = p.sync_kb;
+            }
+            --pace_left;
           }
-        } else if constexpr (kAMajor == MAJOR_K) {
-          load(sa, &tm_a, k0, m0);                                   // box {64 k, CTA_M rows}
-        } else {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1, 1);
+          uint8_t* sa = smem + stage * L::STAGE_BYTES;
+          uint8_t* sb = sa + L::A_BYTES;
+          if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], (kA ? L::A_BYTES : L::B_BYTES) * kCtas);
+          else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
+          const int k0 = kb * GEMM_BLOCK_K;
+          auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
+            const uint64_t pol = tm == &tm_a ? p.hint_a : p.hint_b;
+            if constexpr (kCtas == 1) ptx::tma_load_2d_hint(dst, tm, &full_bar[stage], c0, c1, pol);
+            else ptx::tma_load_2d_pair_hint(dst, tm, &full_bar[stage], c0, c1, pol);
+          };
+          auto load3 = [&](void* dst, const CUtensorMap* tm, int c0, int c1, int c2) {
+            if constexpr (kCtas == 1) ptx::tma_load_3d_hint(dst, tm, &full_bar[stage], c0, c1, c2, p.hint_a);
+            else ptx::tma_load_3d_pair_hint(dst, tm, &full_bar[stage], c0, c1, c2, p.hint_a);
+          };
+          if constexpr (kA) {
+            if constexpr (kAPanel) {  // A lives in 256-column panels: element (r, c) at panel c/256, row r, column c%256
+              if constexpr (kAMajor == MAJOR_K) {
+                load3(sa, &tm_a, k0 % PANEL_W, m0, k0 / PANEL_W);        // box {64 k, CTA_M rows, 1}
+              } else {
 #pragma unroll
-          for (int a = 0; a < CTA_M / 64; ++a) load(sa + a * 8192, &tm_a, m0 + a * 64, k0);  // box {64 m, 64 k}
-        }
-        if constexpr (kBMajor == MAJOR_K) {
-          load(sb, &tm_b, k0, n0);                                   // box {64 k, LOAD_N rows}
-        } else {
+                for (int a = 0; a < CTA_M / 64; ++a)
+                  load3(sa + a * 8192, &tm_a, (m0 + a * 64) % PANEL_W, k0, (m0 + a * 64) / PANEL_W);  // box {64 m, 64 k, 1}
+              }
+            } else if constexpr (kAMajor == MAJOR_K) {
+              load(sa, &tm_a, k0, m0);                                   // box {64 k, CTA_M rows}
+            } else {
 #pragma unroll
-          for (int a = 0; a < LOAD_N / 64; ++a) load(sb + a * 8192, &tm_b, n0 + a * 64, k0);
+              for (int a = 0; a < CTA_M / 64; ++a) load(sa + a * 8192, &tm_a, m0 + a * 64, k0);  // box {64 m, 64 k}
+            }
+          } else {
+            if constexpr (kBMajor == MAJOR_K) {
+              load(sb, &tm_b, k0, n0);                                   // box {64 k, LOAD_N rows}
+            } else {
+#pragma unroll
+              for (int a = 0; a < LOAD_N / 64; ++a) load(sb + a * 8192, &tm_b, n0 + a * 64, k0);
+            }
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
-    }
+    };
+    if (warp == 0) produce(std::true_type{}); else produce(std::false_type{});
   } else if (warp == 1 && lane == 0 && leader) {
     // ===================== MMA issuer (leader CTA, one thread) =====================
     constexpr uint32_t idesc = ptx::idesc_bf16_f32(UMMA_M, BLOCK_N, kAMajor, kBMajor);

@@ -2,6 +2,8 @@
 // (recompute -> dlogits -> dH, dW), plus the plain GEMM entry used by the tests.
 // Replaces /root/reference/pipelinerl/finetune/rl/__init__.py:197-208 and its autograd.
 #include "gemm_sm100.cuh"
+#include <atomic>
+#include <mutex>
 #include <cudaTypedefs.h>
 #include <mutex>
 
@@ -82,8 +84,37 @@ static int choose_ksplits(int tiles, int clusters, int kb_total, int forced) {
   return best;
 }
 
+// ---- soft K-lockstep: arrival counters of one launch ----------------------------------------------------------------------
+// A ring of counters in device memory that belongs to the library (no caller workspace to size, nothing allocated): each
+// launch takes the next slice and zeroes it on its own stream right before the kernel.  A slice comes round again after
+// LOCKSTEP_RING / (counters per launch) launches -- hundreds of GEMMs later; should a launch that old still be running, its
+// pacing degrades to the time-out (lockstep_pace), nothing else.
+constexpr int LOCKSTEP_RING = 1 << 16;
+static __device__ __align__(256) unsigned g_lockstep_ring[LOCKSTEP_RING];
+static std::atomic<unsigned> g_lockstep_cursor{0};
+static void* g_lockstep_addr[64] = {};
+static std::mutex g_lockstep_mu;
+
+static int lockstep_slice(int n, cudaStream_t st, unsigned** out) {
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < 64, "lockstep: device ordinal %d out of range", dev);
+  void* base;
+  {
+    std::lock_guard<std::mutex> lk(g_lockstep_mu);
+    if (!g_lockstep_addr[dev]) B200_CUDA_OK(cudaGetSymbolAddress(&g_lockstep_addr[dev], g_lockstep_ring));
+    base = g_lockstep_addr[dev];
+  }
+  unsigned start = g_lockstep_cursor.fetch_add((unsigned)n) % LOCKSTEP_RING;
+  if (start + (unsigned)n > LOCKSTEP_RING) start = 0;   // do not straddle the end
+  *out = (unsigned*)base + start;
+  B200_CUDA_OK(cudaMemsetAsync(*out, 0, (size_t)n * sizeof(unsigned), st));
+  return 0;
+}
+
 template <int kEpi, int kAMajor, int kBMajor, int kCtas, bool kSave, bool kAPanel, int kMRep = 1>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p_in, cudaStream_t st) {
+  GemmParams p = p_in;
   constexpr int kStages = kMRep == 2 ? STAGES_BIGM : kCtas == 1 ? STAGES_1CTA : STAGES_2CTA;
   using L = GemmSmem<BN, kCtas, kStages, kMRep>;
   static_assert(BN == PANEL_W, "panels are one N tile wide");
@@ -97,6 +128,21 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   const long long n_items = p.n_items;
   int clusters = sm_count() / kCtas;
   if (clusters > n_items) clusters = (int)n_items;
+  // soft K-lockstep (tunables lockstep_fwd / _dh / _dw = k-blocks per epoch, lockstep_slack = epochs of lead allowed)
+  p.sync = nullptr;
+  {
+    const int epoch_kb = get_tunable(kEpi != EPI_STORE ? TUNE_LOCKSTEP_FWD : (kAMajor == MAJOR_K ? TUNE_LOCKSTEP_DH : TUNE_LOCKSTEP_DW));
+    const int slack = get_tunable(TUNE_LOCKSTEP_SLACK) < 1 ? 1 : get_tunable(TUNE_LOCKSTEP_SLACK);
+    const long long n_full = n_items < p.tail_first ? n_items : p.tail_first;
+    if (epoch_kb > 0 && p.k_splits <= 1 && clusters > 1 && n_full > 0) {
+      const int epochs = ceil_div(p.kb_total, epoch_kb);
+      const long long waves = (n_full + clusters - 1) / clusters;
+      if (epochs > slack && waves * epochs <= LOCKSTEP_RING / 4) {
+        if (int e = lockstep_slice((int)(waves * epochs), st, &p.sync)) return e;
+        p.sync_kb = epoch_kb; p.sync_epochs = epochs; p.sync_full = (int)n_full; p.sync_slack = slack;
+      }
+    }
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(clusters * kCtas);
   cfg.blockDim = dim3(GEMM_THREADS + 128 * (kMRep - 1));   // one more epilogue warpgroup per extra 128 rows
