@@ -311,6 +311,44 @@ def test_lmhead_bwd_tile_variants_agree(dh_big, dw_big, tail):
     assert _rel(gw - 0.5, wr.grad) < GRAD_RTOL
 
 
+@pytest.mark.parametrize("entropy", [True, False])
+def test_soft_k_lockstep_never_changes_a_bit(entropy):
+    """Pacing of the TMA producers (lockstep_fwd / _dh / _dw, any epoch length or slack, or off) is scheduling only: forward
+    statistics, dH and the accumulated f32 dW are bit-identical whatever the setting.  Shape with several waves, a long K for dH
+    and the tail split."""
+    from pipelinerl_swe_b200 import _abi, ops
+    d = _dev()
+    M, H, V, temp = 2100, 1024, 60000 + 8, 0.9
+    g = torch.Generator(device=d).manual_seed(19)
+    h = torch.randn(M, H, device=d, generator=g).bfloat16()
+    w = (torch.randn(V, H, device=d, generator=g) * 0.04).bfloat16()
+    tgt = torch.randint(0, V, (M,), device=d, generator=g)
+    c_lp = torch.randn(M, device=d, generator=g) * 0.1
+    c_ent = torch.randn(M, device=d, generator=g) * 0.01 if entropy else None
+    names = ("lockstep_fwd", "lockstep_dh", "lockstep_dw", "lockstep_slack")
+    shipped = [_abi.set_tunable(n, 0) for n in names]          # set_tunable returns the previous value
+    outs = []
+    try:
+        for setting in ((0, 0, 0, 2), tuple(shipped), (4, 4, 4, 1), (2, 16, 8, 3), (1, 1, 1, 1)):
+            for n, v in zip(names, setting):
+                _abi.set_tunable(n, v)
+            saved = ops.lmhead_saved_buffer(M, H, V, d)
+            stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp, saved=saved)
+            lp, ent, lse = ops.lmhead_finalize(stats)
+            gw = torch.full((V, H), 0.25, device=d)
+            gh, _ = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0 / temp, grad_weight_out=gw, accumulate=True, saved=saved)
+            gh2, gw2 = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, c_ent, 1.0 / temp)      # recompute mode, bf16 dW
+            torch.cuda.synchronize()
+            outs.append((stats.clone(), gh.clone(), gw, gh2.clone(), gw2.clone()))
+    finally:
+        for n, v in zip(names, shipped):
+            _abi.set_tunable(n, v)
+    assert shipped[0] > 0 and shipped[1] > 0     # the shipped schedule paces
+    for o in outs[1:]:
+        for a, b in zip(o, outs[0]):
+            assert torch.equal(a, b)
+
+
 class _EmbedLM(torch.nn.Module):
     """Token-wise 'trunk' (embedding lookup) + lm_head: hidden depends on the ids, so packing / offsets are exercised."""
 
