@@ -95,21 +95,27 @@ static std::atomic<unsigned> g_lockstep_cursor{0};
 static void* g_lockstep_addr[64] = {};
 static std::mutex g_lockstep_mu;
 
-static int lockstep_slice(int n, cudaStream_t st, unsigned** out) {
+// Pacing is optional: when the slice cannot be set up (symbol look-up refused, e.g. first use inside a stream capture) the
+// launch simply runs un-paced -- never an error of the GEMM.
+static bool lockstep_slice(int n, cudaStream_t st, unsigned** out) {
   int dev = 0;
-  B200_CUDA_OK(cudaGetDevice(&dev));
-  B200_REQUIRE(dev >= 0 && dev < 64, "lockstep: device ordinal %d out of range", dev);
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { (void)cudaGetLastError(); return false; }
   void* base;
   {
     std::lock_guard<std::mutex> lk(g_lockstep_mu);
-    if (!g_lockstep_addr[dev]) B200_CUDA_OK(cudaGetSymbolAddress(&g_lockstep_addr[dev], g_lockstep_ring));
+    if (!g_lockstep_addr[dev] && cudaGetSymbolAddress(&g_lockstep_addr[dev], g_lockstep_ring) != cudaSuccess) {
+      g_lockstep_addr[dev] = nullptr;
+      (void)cudaGetLastError();
+      return false;
+    }
     base = g_lockstep_addr[dev];
   }
   unsigned start = g_lockstep_cursor.fetch_add((unsigned)n) % LOCKSTEP_RING;
   if (start + (unsigned)n > LOCKSTEP_RING) start = 0;   // do not straddle the end
-  *out = (unsigned*)base + start;
-  B200_CUDA_OK(cudaMemsetAsync(*out, 0, (size_t)n * sizeof(unsigned), st));
-  return 0;
+  unsigned* slice = (unsigned*)base + start;
+  if (cudaMemsetAsync(slice, 0, (size_t)n * sizeof(unsigned), st) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+  *out = slice;
+  return true;
 }
 
 template <int kEpi, int kAMajor, int kBMajor, int kCtas, bool kSave, bool kAPanel, int kMRep = 1>
@@ -138,8 +144,11 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
       const int epochs = ceil_div(p.kb_total, epoch_kb);
       const long long waves = (n_full + clusters - 1) / clusters;
       if (epochs > slack && waves * epochs <= LOCKSTEP_RING / 4) {
-        if (int e = lockstep_slice((int)(waves * epochs), st, &p.sync)) return e;
-        p.sync_kb = epoch_kb; p.sync_epochs = epochs; p.sync_full = (int)n_full; p.sync_slack = slack;
+        if (lockstep_slice((int)(waves * epochs), st, &p.sync)) {
+          p.sync_kb = epoch_kb; p.sync_epochs = epochs; p.sync_full = (int)n_full; p.sync_slack = slack;
+        } else {
+          p.sync = nullptr;
+        }
       }
     }
   }
