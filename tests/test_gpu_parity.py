@@ -349,6 +349,42 @@ def test_soft_k_lockstep_never_changes_a_bit(entropy):
             assert torch.equal(a, b)
 
 
+def test_lmhead_forward_backward_replays_from_a_cuda_graph():
+    """K1 -> finalize -> K2 captured into a CUDA graph (after one warm-up call on the capture stream) and replayed: bit-equal to
+    the eager call every time.  The library allocates nothing, its per-launch lockstep counters are a memset node of the graph."""
+    from pipelinerl_swe_b200 import ops
+    d = _dev()
+    M, H, V = 1100, 768, 40000 + 8
+    g = torch.Generator(device=d).manual_seed(3)
+    h = torch.randn(M, H, device=d, generator=g).bfloat16()
+    w = (torch.randn(V, H, device=d, generator=g) * 0.04).bfloat16()
+    tgt = torch.randint(0, V, (M,), device=d, generator=g)
+    c_lp = torch.randn(M, device=d, generator=g) * 0.1
+
+    def step():
+        saved = ops.lmhead_saved_buffer(M, H, V, d)
+        stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0, saved=saved)
+        lp, ent, lse = ops.lmhead_finalize(stats)
+        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent, c_lp, None, 1.0, saved=saved)
+        return lp, ent, gh, gw
+
+    eager = [t.clone() for t in step()]
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        step()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out = step()
+    for _ in range(3):
+        for t in out:
+            t.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert all(torch.equal(a, b) for a, b in zip(out, eager))
+
+
 class _EmbedLM(torch.nn.Module):
     """Token-wise 'trunk' (embedding lookup) + lm_head: hidden depends on the ids, so packing / offsets are exercised."""
 
