@@ -49,13 +49,16 @@ int b200grpo_abi_version(void);
  *   weight  bf16 [Vloc,H] (ldw)                         this rank's vocab rows
  *   targets i64  [M]      global vocab id scored at each row (input_ids[t+1])
  *   v_offset              global id of weight row 0 (0 when the vocab is not sharded)
- *   stats   f32  [M,4]    out: (max z, sum exp(z-max), sum exp(z-max)*z, z[target] or 0)
- *                         with z = logit / temperature, over this rank's vocab rows
+ *   stats   f32  [M,4]    out: (r, sum exp(z-r), sum exp(z-r)*z, z[target] or 0) with z = logit /
+ *                         temperature over this rank's vocab rows and r a per-row reference known
+ *                         before the GEMM (max of the target logit and four sampled logits), which
+ *                         makes the epilogue one pass; b200grpo_lmhead_finalize merges ranks
  *   saved   nullable, b200grpo_lmhead_saved_bytes(), 256-byte aligned.  When given, the
- *           epilogue also keeps the bf16 logits of this micro-batch (stored relative to
- *           their 256-column tile maximum, so the rounding error vanishes where softmax
- *           mass is) for a recompute-free backward: the [M x Vloc] scratch lives only
- *           between this call and the matching b200grpo_lmhead_bwd, which consumes it.
+ *           epilogue also keeps E = exp(z - r) of this micro-batch as bf16 (f32's exponent
+ *           range, 2^-9 relative precision at any magnitude; every quantity of the backward
+ *           is a row-scaled multiple of it) in [Vloc/256][M][256] panels, plus r, for a
+ *           recompute-free backward: the [M x Vloc] scratch lives only between this call
+ *           and the matching b200grpo_lmhead_bwd.
  *           NULL: nothing of size [M x Vloc] is written by the forward.
  * ------------------------------------------------------------------------------------- */
 size_t b200grpo_lmhead_fwd_workspace(int M, int H, int Vloc);
@@ -166,6 +169,11 @@ int b200grpo_segment_bounds_static(const int64_t* position_ids, int T, int32_t* 
  *                   forward stored nothing of size [M x Vloc]);
  *   saved != NULL : the buffer the forward filled; turned into dlogits IN PLACE by one
  *                   HBM-bound pass (4 B/element) -- the buffer is consumed by this call.
+ *                   With coef_ent != NULL this pass works from bf16 exponentials: fine for the policy term,
+ *                   but on near-deterministic rows (entropy << 1e-2 nats) the entropy term p*(log p + H) at
+ *                   the peak token is a difference of nearly equal numbers and can be off by tens of per
+ *                   cent of that (tiny) term.  b200grpo_rl_step_host and the Python drop-in therefore run an
+ *                   entropy gradient in recompute mode (saved == NULL) and keep `saved` for coef_ent == NULL.
  * s = *grad_scale (device scalar, nullable = 1).
  *   grad_hidden bf16 [M,H] (ldgh)   -- partial sum over this rank's vocab rows
  *   grad_weight bf16 or f32 [Vloc,H] (ldgw); accumulate != 0 adds into it (f32 only)

@@ -61,8 +61,18 @@ extern "C" int b200grpo_rl_step_host(const b200grpo_host_batch* b, int L, int H,
   const float* f32_src[7] = {b->rewards, b->advantages, b->ref_logprobs, b->old_logprobs, b->group_tokens, b->num_labels, b->overflow};
   for (int i = 0; i < 7; ++i) B200_CUDA_OK(cudaMemcpyAsync(w + o.f32[i], f32_src[i], (size_t)L * 4, cudaMemcpyHostToDevice, st));
   const int64_t* targets = (const int64_t*)(w + o.ids) + 1;  // row t is scored against input_ids[t+1]
+  // An entropy gradient is formed from recomputed f32 logits, never from the saved bf16 exponentials: on near-deterministic rows
+  // (entropy << 1e-2 nats) p * (log p + H) is a difference of nearly equal numbers at the peak token and bf16's 2^-9 on E ~ 1
+  // is as large as H itself.  With entropy_coef != 0 the step therefore runs in recompute mode; the backward's dlogits scratch
+  // then takes the (unused) saved-exponentials region that follows its workspace.
+  const bool save = o.save && cfg->entropy_coef == 0.f;
+  size_t n_bwd = o.n_bwd;
+  if (o.save && !save) {
+    n_bwd = (size_t)((w + o.saved + o.n_saved) - (w + o.ws_bwd));
+    B200_REQUIRE(n_bwd >= b200grpo_lmhead_bwd_workspace(M, H, V, 0), "rl_step_host: workspace too small for the recompute backward");
+  }
   int e = b200grpo_lmhead_fwd(w + o.hidden, H, weight, ldw, targets, M, H, V, 0, 1.0f / temperature, (float*)(w + o.stats),
-                              o.save ? (void*)(w + o.saved) : nullptr, w + o.ws_fwd, o.n_fwd, stream);
+                              save ? (void*)(w + o.saved) : nullptr, w + o.ws_fwd, o.n_fwd, stream);
   if (e) return e;
   e = b200grpo_lmhead_finalize((const float*)(w + o.stats), 1, M, (float*)(w + o.logprob), (float*)(w + o.entropy),
                                (float*)(w + o.lse), stream);
@@ -76,10 +86,10 @@ extern "C" int b200grpo_rl_step_host(const b200grpo_host_batch* b, int L, int H,
   if (e) return e;
   if (grad_weight || grad_hidden_host_bf16) {
     e = b200grpo_lmhead_bwd(w + o.hidden, H, weight, ldw, targets, (const float*)(w + o.lse), (const float*)(w + o.entropy),
-                            (const float*)(w + o.coef_lp), (cfg->entropy_coef != 0.f || !o.save) ? (const float*)(w + o.coef_ent) : nullptr,
+                            (const float*)(w + o.coef_lp), save ? nullptr : (const float*)(w + o.coef_ent),
                             nullptr, M, H, V, 0,
-                            1.0f / temperature, o.save ? (void*)(w + o.saved) : nullptr, (void*)(w + o.ghid), H, grad_weight, H,
-                            grad_weight_is_f32, accumulate, w + o.ws_bwd, o.n_bwd, stream);
+                            1.0f / temperature, save ? (void*)(w + o.saved) : nullptr, (void*)(w + o.ghid), H, grad_weight, H,
+                            grad_weight_is_f32, accumulate, w + o.ws_bwd, n_bwd, stream);
     if (e) return e;
     B200_CUDA_OK(cudaMemsetAsync(w + o.ghid + (size_t)M * H * 2, 0, (size_t)H * 2, st));  // last position has no target
     if (grad_hidden_host_bf16)

@@ -148,8 +148,11 @@ class LMHeadLogprobFunction(torch.autograd.Function):
         chunks = row_chunks(M, Vloc)
         # keep bf16 logits for a recompute-free backward when a backward will follow: the whole micro-batch when it fits
         # the budget, else its first row chunk (the other chunks are recomputed in the backward)
+        # An entropy gradient (entropy_bonus != 0) is always formed from recomputed f32 logits: on near-deterministic rows
+        # p * (log p + H) at the peak token is a difference of nearly equal numbers, and the 2^-9 of a bf16 exponential ~ 1 is as
+        # large as H itself (found by tests/fuzz_rl_step.py: 30 % gradient error on a row of entropy 4.5e-3 nats).
         saved = None
-        if need_bwd and save_logits_enabled():
+        if need_bwd and save_logits_enabled() and not entropy_grad:
             r0, r1 = chunks[0]
             saved = ops.lmhead_saved_buffer(r1 - r0, H, Vloc, hidden.device)
 
