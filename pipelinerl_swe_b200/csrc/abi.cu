@@ -59,8 +59,10 @@ int check_device_sm100() {
 //   dw_zigzag: odd tiles of a cluster walk the token (K) axis of dW backwards, so a wave starts on the rows of `hidden`
 //   the previous wave touched last (L2 reuse instead of a DRAM re-read).  Ships on: dW DRAM reads 12.0 -> 10.4 GB, dW -1 %
 //   same-box (profiles/r01/dw_zigzag_ab.md).
-//   rows_path: 1 = an entropy-free backward (coef_ent == NULL) runs its GEMMs on the saved exponentials; 0 = it forms dlogits
-//   in place first like the entropy path (A/B switch).
+//   rows_path: an entropy-free backward (coef_ent == NULL) runs its GEMMs on the saved exponentials, the onehot terms added after
+//   them (dH epilogue gather + sparse target-row kernel): 2 = except for confident targets (p > 1/2), whose onehot is folded into
+//   the saved exponential before the GEMMs (shipped), 1 = for every row; 0 = dlogits formed in place first like the entropy
+//   path (A/B switches).
 //   lockstep_fwd / lockstep_dh / lockstep_dw: k-blocks per epoch of the soft K-lockstep between the clusters of a wave
 //   (gemm_sm100.cuh lockstep_pace; 0 = off) for the forward / recompute GEMM, dH and dW; lockstep_slack: epochs a cluster may
 //   run ahead of the slowest one.
@@ -68,7 +70,7 @@ static const char* const g_tunable_names[TUNE_COUNT] = {"two_cta", "dh_ksplit", 
                                                         "dw_group_m", "dw_group_n", "save_logits", "hint_resident", "hint_stream",
                                                         "dh_big_m", "dw_big_m", "gemm_big_m", "fwd_big_m", "dw_zigzag", "rows_path", "lockstep_fwd",
                                                         "lockstep_dh", "lockstep_dw", "lockstep_slack"};
-static int g_tunables[TUNE_COUNT] = {1, 0, 0, 1, 16, 4, 1, 0, 1, 0, 0, 1, 0, 0, 0, 1, 1, 16, 8, 32, 2};
+static int g_tunables[TUNE_COUNT] = {1, 0, 0, 1, 16, 4, 1, 0, 1, 0, 0, 1, 0, 0, 0, 1, 2, 16, 8, 32, 2};
 int get_tunable(int id) { return g_tunables[id]; }
 
 // ---- profiling ring (diagnostic; single-threaded use) -------------------------------------

@@ -449,15 +449,30 @@ __global__ void __launch_bounds__(256) bwd_rows_kernel(const __nv_bfloat16* __re
                                                        const float* __restrict__ grad_scale, float inv_temp, int M, int H,
                                                        const long long* __restrict__ targets, long long v_offset, int Vloc,
                                                        float* __restrict__ row_scale, float* __restrict__ row_coef, int* __restrict__ row_key,
-                                                       __nv_bfloat16* __restrict__ hs) {
+                                                       __nv_bfloat16* __restrict__ hs, __nv_bfloat16* __restrict__ panels) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= M) return;
   const float a = coef_lp[row] * (grad_scale ? *grad_scale : 1.0f) * inv_temp;
   const float sc = a != 0.f ? -a * __expf(row_ref[row] - lse[row]) : 0.f;
   if (lane == 0) {
-    row_scale[row] = sc; row_coef[row] = a;
     const long long t = targets[row] - v_offset;          // key of the onehot term: local target row, or -1 when there is none
-    row_key[row] = (a != 0.f && t >= 0 && t < Vloc) ? (int)t : -1;
+    bool has = a != 0.f && t >= 0 && t < Vloc;
+    float coef = a;
+    // dlogit[target] = a (1 - p) is a difference of nearly equal numbers for a confident token.  Adding the onehot terms
+    // (a * W[target] in dH's epilogue, a * hidden[t] in the sparse dW kernel) AFTER GEMMs whose operands were rounded to bf16
+    // keeps 2^-9 of 1 where 2^-9 of 1 - p is needed (dW 1.5x off at p = 0.998).  For p > 1/2 the onehot is therefore folded
+    // into the target's saved exponential here, in f32, BEFORE the GEMMs: s (E - exp(lse - r)) = a (1 - p), and only the
+    // difference is rounded.  For p <= 1/2 the onehot terms stay exact f32 additions after the GEMMs.
+    if (panels && has) {
+      __nv_bfloat16* e = panels + ((long long)(t / PANEL_W) * M + row) * PANEL_W + (t % PANEL_W);
+      const float ev = __bfloat162float(*e), big = __expf(lse[row] - row_ref[row]);
+      if (ev > 0.5f * big) {
+        *e = __float2bfloat16_rn(ev - big);
+        has = false; coef = 0.f;
+      }
+    }
+    row_scale[row] = sc; row_coef[row] = coef;
+    row_key[row] = has ? (int)t : -1;
   }
   if (!hs) return;
   const __nv_bfloat16* h = hidden + (long long)row * ldh;
@@ -846,6 +861,7 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
   if (!(stages & B200GRPO_BWD_DH)) grad_hidden = nullptr;
   if (!(stages & B200GRPO_BWD_DW)) grad_weight = nullptr;
   const bool rows_path = saved && !coef_ent && get_tunable(TUNE_ROWS_PATH);   // entropy-free + saved exponentials: GEMMs straight on E
+  const bool fold_onehot = rows_path && get_tunable(TUNE_ROWS_PATH) >= 2;     // confident targets: onehot folded into the saved exponential (bwd_rows_kernel)
   B200_REQUIRE(hidden && weight && workspace && targets, "lmhead_bwd: null pointer");
   B200_REQUIRE(!form || (lse && coef_lp && ((saved && !coef_ent) || (entropy && coef_ent))), "lmhead_bwd: null per-token input");
   B200_REQUIRE(saved || coef_ent || !form, "lmhead_bwd: the recompute backward needs coef_ent (pass zeros)");
@@ -882,7 +898,8 @@ static int lmhead_bwd_impl(const void* hidden, int64_t ldh, const void* weight, 
     ProfScope ps(PROF_DLOGITS_EW, st);
     B200_CUDA_OK(cudaMemsetAsync(row_key + M, 0xfe, key_bytes(M) - (size_t)M * 4, st));   // pad keys: 0xfefefefe < 0, never a match
     bwd_rows_kernel<<<ceil_div(M, 8), 256, 0, st>>>((const __nv_bfloat16*)hidden, ldh, row_ref, lse, coef_lp, grad_scale, inv_temperature,
-                                                    M, H, (const long long*)targets, v_offset, Vloc, row_scale, row_coef, row_key, hs);
+                                                    M, H, (const long long*)targets, v_offset, Vloc, row_scale, row_coef, row_key, hs,
+                                                    fold_onehot ? dlog : nullptr);
     count_launch();
     B200_CUDA_OK(cudaGetLastError());
   } else if (saved && form) {  // 1b. entropy term present: saved exponentials -> dlogits in place (no recompute GEMM)

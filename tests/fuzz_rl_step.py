@@ -10,7 +10,8 @@ restatement takes its place and the record says so.
 Each case draws: packed row or unpacked rows, sequence lengths, prompt lengths (some sequences fully masked), a slice that starts
 mid-sequence, H, V (ragged / tiny / several panels), temperature, every RLConfig switch (ppo / reinforce, advantages or rewards,
 relu weights, epsilon, KL coefficient + clamp, entropy bonus, group normalisation, overlong filtering, value head + value loss),
-step / max_step for the decayed coefficients, hot (repeated) targets, and the saved / recompute backward.  Tolerances are the
+step / max_step for the decayed coefficients, hot (repeated) targets, confident policies (the target is the peak of the row, p up to
+0.999+: gradients are differences of nearly equal numbers), and the saved / recompute backward.  Tolerances are the
 north star's: loss 1e-3, every statistic 2e-3 (+2e-4 absolute), gradients 2e-2 of the largest reference entry.
 """
 from __future__ import annotations
@@ -102,6 +103,11 @@ def draw_case(rnd: random.Random, seed: int):
     hidden = torch.randn(rows, T, H, generator=g).bfloat16()
     weight = (torch.randn(V, H, generator=g) * rnd.choice([0.02, 0.1, 0.3])).bfloat16()
     temp = rnd.choice([0.6, 1.0, 1.3])
+    if rnd.random() < 0.25:                         # a confident policy: the next token is the peak of most rows (p_target up to 0.999+)
+        wn = weight.float() / (weight.float().norm(dim=1, keepdim=True) + 1e-6)
+        weight = wn.bfloat16()
+        nxt = torch.roll(batch["input_ids"], shifts=-1, dims=1)
+        hidden = (wn[nxt] * rnd.choice([8.0, 12.0, 16.0]) * temp + 0.3 * torch.randn(rows, T, H, generator=g)).bfloat16()
     if rnd.random() < 0.7:
         near_policy_logprobs(batch, hidden, weight, temp, seed=seed, s_old=rnd.choice([0.02, 0.3]), s_ref=rnd.choice([0.05, 0.5, 3.0]))
     value_head = rnd.random() < 0.2
