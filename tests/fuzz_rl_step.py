@@ -16,6 +16,7 @@ north star's: loss 1e-3, every statistic 2e-3 (+2e-4 absolute), gradients 2e-2 o
 """
 from __future__ import annotations
 
+import math
 import os
 import random
 import sys
@@ -107,7 +108,10 @@ def draw_case(rnd: random.Random, seed: int):
         wn = weight.float() / (weight.float().norm(dim=1, keepdim=True) + 1e-6)
         weight = wn.bfloat16()
         nxt = torch.roll(batch["input_ids"], shifts=-1, dims=1)
-        hidden = (wn[nxt] * rnd.choice([8.0, 12.0, 16.0]) * temp + 0.3 * torch.randn(rows, T, H, generator=g)).bfloat16()
+        # margin ln(V) + 2..6 nats: 1 - p_target between ~0.13 and ~0.0025.  (Closer to 1 the comparison itself is ill-conditioned:
+        # two fp32 evaluations of 1 - p differ by 1e-5 / (1 - p) through the summation order of the logits alone.)
+        margin = math.log(V) + rnd.uniform(2.0, 6.0)
+        hidden = (wn[nxt] * margin * temp + 0.3 * torch.randn(rows, T, H, generator=g)).bfloat16()
     if rnd.random() < 0.7:
         near_policy_logprobs(batch, hidden, weight, temp, seed=seed, s_old=rnd.choice([0.02, 0.3]), s_ref=rnd.choice([0.05, 0.5, 3.0]))
     value_head = rnd.random() < 0.2
