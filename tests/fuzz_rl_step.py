@@ -10,6 +10,7 @@ restatement takes its place and the record says so.
 Each case draws: packed row or unpacked rows, sequence lengths, prompt lengths (some sequences fully masked), a slice that starts
 mid-sequence, H, V (ragged / tiny / several panels), temperature, every RLConfig switch (ppo / reinforce, advantages or rewards,
 relu weights, epsilon, KL coefficient + clamp, entropy bonus, group normalisation, overlong filtering, value head + value loss),
+the opt-in switches (skip masked tokens, fused f32 gradient accumulation + fold),
 step / max_step for the decayed coefficients, hot (repeated) targets, confident policies (the target is the peak of the row, p up to
 0.999+: gradients are differences of nearly equal numbers), and the saved / recompute backward.  Tolerances are the
 north star's: loss 1e-3, every statistic 2e-3 (+2e-4 absolute), gradients 2e-2 of the largest reference entry.
@@ -126,7 +127,7 @@ def draw_case(rnd: random.Random, seed: int):
     step = rnd.randint(0, max_step)
     values = torch.rand(rows, T, generator=g) if value_head else None
     return dict(batch=batch, hidden=hidden, weight=weight, values=values, cfg=cfg, step=step, max_step=max_step,
-                recompute=rnd.random() < 0.3, desc=dict(packed=packed, lens=lens, rows=rows, H=H, V=V, n_prompt=n_prompt, start_pos=start_pos,
+                recompute=rnd.random() < 0.3, skip_masked=rnd.random() < 0.25, fused_acc=rnd.random() < 0.25, desc=dict(packed=packed, lens=lens, rows=rows, H=H, V=V, n_prompt=n_prompt, start_pos=start_pos,
                                                        value_head=value_head, step=(step, max_step), **cfg))
 
 
@@ -152,16 +153,23 @@ def run_reference(case, dev):
 
 
 def run_ours(case, dev):
-    from pipelinerl_swe_b200 import RLConfig, rl_step, set_save_logits
+    from pipelinerl_swe_b200 import (RLConfig, fold_main_grad, rl_step, set_fused_grad_accumulation, set_save_logits,
+                                     set_skip_masked_tokens)
     b = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in case["batch"].items()}
     model = _OurLM(case["hidden"], case["weight"], case["values"]).to(dev)
     set_save_logits(not case["recompute"])
+    set_skip_masked_tokens(bool(case.get("skip_masked")))          # opt-in switches: same loss, statistics and gradients
+    set_fused_grad_accumulation(bool(case.get("fused_acc")))
     try:
         loss, stats = rl_step(model, b, case["step"], case["max_step"], RLConfig(**case["cfg"]))
         if loss.requires_grad:
             loss.backward()
+        if case.get("fused_acc"):
+            fold_main_grad(model)                                   # f32 main_grad -> .grad, what an unmodified optimizer reads
     finally:
         set_save_logits(True)
+        set_skip_masked_tokens(False)
+        set_fused_grad_accumulation(False)
     g = lambda p: None if p.grad is None else p.grad.detach()  # noqa: E731
     return float(loss.detach()), stats, g(model.hidden), g(model.lm_head.weight), (g(model.values) if hasattr(model, "values") else None)
 
