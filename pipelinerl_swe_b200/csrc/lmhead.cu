@@ -693,8 +693,11 @@ static int run_store_gemm(const void* A, long long lda, int a_mn, const void* B,
   const int tiles = ceil_div(M, GEMM_BLOCK_M * mrep * ctas) * ceil_div(N, BN);
   // forced_ksplit >= 1: uniform k-splits (1 = none); <= 0: automatic = tail split of the last partial wave
   // (or, with the tail_split tunable off, the uniform split count with the best wave efficiency)
-  const bool want_tail = forced_ksplit <= 0 && get_tunable(TUNE_TAIL_SPLIT);
+  // (a row epilogue travels with the tail split only -- tail_reduce_kernel applies it, splitk_reduce_kernel does not -- so it
+  // takes the tail split whatever the tunable says; found by the tunable-randomising fuzz: dH came back un-scaled)
+  const bool want_tail = forced_ksplit <= 0 && (get_tunable(TUNE_TAIL_SPLIT) || epi != nullptr);
   int ks = (N % 4 == 0 && slab && !want_tail) ? choose_ksplits(tiles, clusters_for(ctas), ceil_div(K, GEMM_BLOCK_K), forced_ksplit) : 1;
+  if (epi) ks = 1;
   if (ks > 1 && slab_bytes < (size_t)ks * M * N * 4) ks = 1;
   fill_tiling(p, M, N, K, ctas, group_m, ks, group_n, hint_a, hint_b, mrep);
   int tail = 0;
@@ -839,7 +842,8 @@ static size_t rows_scratch_bytes(int M, int H) { return 2 * align_up((size_t)M *
 extern "C" size_t b200grpo_lmhead_bwd_workspace(int M, int H, int Vloc, int with_saved) {
   const int ctas = ctas_for(M);
   size_t slab = store_gemm_slab_bytes(M, H, Vloc, ctas, get_tunable(TUNE_DH_KSPLIT), mrep_for(TUNE_DH_BIG_M, ctas));
-  size_t slab_t = store_gemm_slab_bytes(M, H, Vloc, ctas, 0, mrep_for(TUNE_DH_BIG_M, ctas));   // the row-epilogue path forces the tail split
+  size_t slab_t = tail_slab_bytes(ceil_div(M, GEMM_BLOCK_M * mrep_for(TUNE_DH_BIG_M, ctas) * ctas) * ceil_div(H, BN), clusters_for(ctas),
+                                  ceil_div(Vloc, GEMM_BLOCK_K), GEMM_BLOCK_M * mrep_for(TUNE_DH_BIG_M, ctas) * ctas);   // the row-epilogue path forces the tail split
   if (slab_t > slab) slab = slab_t;
   const size_t slab_dw = store_gemm_slab_bytes(Vloc, H, M, ctas, get_tunable(TUNE_DW_KSPLIT), mrep_for(TUNE_DW_BIG_M, ctas));
   if (slab_dw > slab) slab = slab_dw;   // the two GEMMs run back to back on one stream and share it

@@ -279,8 +279,11 @@ def probe_gemm_fuzz(seed, n_cases=24):
 
 def probe_lmhead_fuzz(seed, n_cases=16):
     """Random (M, H, V, temperature, tile variant, saved / recompute, with / without an entropy gradient, f32-accumulate / bf16
-    gradient output) forward + backward against torch autograd in fp32.  Targets are drawn from a small pool in half of the
-    cases so that many tokens share a target (the leader logic of the sparse target-row kernel)."""
+    gradient output, 1-3 contiguous vocab shards merged like the vocab-parallel path) forward + backward against torch autograd in
+    fp32.  Targets are drawn from a small pool in half of the cases so that many tokens share a target (the leader logic of the
+    sparse target-row kernel); in a third of the cases the policy is confident (the target is the peak of its row, 1 - p between
+    0.13 and 0.0025: gradients are differences of nearly equal numbers)."""
+    import math
     import random
     from pipelinerl_swe_b200 import _abi, ops
     rnd = random.Random(seed)
@@ -293,12 +296,21 @@ def probe_lmhead_fuzz(seed, n_cases=16):
         temp = rnd.choice([0.6, 1.0, 1.4])
         save, two = rnd.randint(0, 1), rnd.randint(0, 1)
         no_ent, f32_acc, hot = rnd.randint(0, 1), rnd.randint(0, 1), rnd.randint(0, 1)
+        confident = rnd.random() < 0.34
+        n_shards = rnd.choice([1, 1, 2, 3]) if V >= 64 else 1
         for name in ("dh_big_m", "dw_big_m", "tail_split"):
             _abi.set_tunable(name, rnd.randint(0, 1))
         _abi.set_tunable("two_cta", two)
-        h = torch.randn(M, H, device="cuda", generator=g).bfloat16()
-        w = (torch.randn(V, H, device="cuda", generator=g) * (1.0 / H ** 0.5)).bfloat16()
         tgt = torch.randint(0, min(V, 5) if hot else V, (M,), device="cuda", generator=g)
+        if confident:
+            wf = torch.randn(V, H, device="cuda", generator=g)
+            wf = wf / (wf.norm(dim=1, keepdim=True) + 1e-6)
+            w = wf.bfloat16()
+            margin = math.log(V) + rnd.uniform(2.0, 6.0)
+            h = (wf[tgt] * margin * temp + 0.3 * torch.randn(M, H, device="cuda", generator=g)).bfloat16()
+        else:
+            h = torch.randn(M, H, device="cuda", generator=g).bfloat16()
+            w = (torch.randn(V, H, device="cuda", generator=g) * (1.0 / H ** 0.5)).bfloat16()
         c_lp = torch.randn(M, device="cuda", generator=g) * 0.1
         c_lp[::3] = 0.0
         c_ent = torch.randn(M, device="cuda", generator=g) * (0.0 if no_ent else 0.01)
@@ -307,20 +319,27 @@ def probe_lmhead_fuzz(seed, n_cases=16):
         lp = logp.gather(1, tgt[:, None]).squeeze(1)
         ent = -(logp.exp() * logp).sum(-1)
         ((lp * c_lp).sum() + (ent * c_ent).sum()).backward()
-        saved = ops.lmhead_saved_buffer(M, H, V, h.device) if save else None
-        stats = ops.lmhead_fwd_stats(h, w, tgt, 1.0 / temp, saved=saved)
+        # contiguous vocab shards (multiples of 8 rows), each with its own forward partials and saved exponentials
+        cuts = [0] + sorted(rnd.sample(range(8, V, 8), n_shards - 1)) + [V] if n_shards > 1 else [0, V]
+        shards = [(cuts[i], cuts[i + 1], w[cuts[i]:cuts[i + 1]].contiguous()) for i in range(len(cuts) - 1)]
+        saved = [ops.lmhead_saved_buffer(M, H, hi - lo, h.device) if save else None for lo, hi, _ in shards]
+        stats = torch.stack([ops.lmhead_fwd_stats(h, ws, tgt, 1.0 / temp, v_offset=lo, saved=sv) for (lo, hi, ws), sv in zip(shards, saved)])
         lp2, ent2, lse = ops.lmhead_finalize(stats)
-        g0 = torch.randn(V, H, device="cuda", generator=g) if f32_acc else None
-        gh, gw = ops.lmhead_bwd(h, w, tgt, lse, ent2, c_lp, None if no_ent else c_ent, 1.0 / temp, saved=saved,
-                                grad_weight_out=g0.clone() if f32_acc else None, accumulate=bool(f32_acc))
+        gh = torch.zeros(M, H, device="cuda")
+        gws = []
+        for (lo, hi, ws), sv in zip(shards, saved):
+            g0 = torch.randn(hi - lo, H, device="cuda", generator=g) if f32_acc else None
+            gh_k, gw_k = ops.lmhead_bwd(h, ws, tgt, lse, ent2, c_lp, None if no_ent else c_ent, 1.0 / temp, v_offset=lo, saved=sv,
+                                        grad_weight_out=g0.clone() if f32_acc else None, accumulate=bool(f32_acc))
+            gh += gh_k.float()
+            gws.append((gw_k - g0) if f32_acc else gw_k.float())
+        gw = torch.cat(gws)
         torch.cuda.synchronize()
-        if f32_acc:
-            gw = gw - g0
         e = [float((lp2 - lp).abs().max() / (lp.abs().max() + 1e-9)), float((ent2 - ent).abs().max() / (ent.abs().max() + 1e-3)),
              _rel(gh, hr.grad), _rel(gw, wr.grad)]
         worst = max(worst, max(e))
         if not (e[0] < 1e-3 and e[1] < 2e-3 and e[2] < 2e-2 and e[3] < 2e-2):
-            bad.append((M, H, V, temp, save, two, no_ent, f32_acc, hot, [round(x, 5) for x in e]))
+            bad.append((M, H, V, temp, save, two, no_ent, f32_acc, hot, confident, n_shards, [round(x, 5) for x in e]))
     for name, v in (("dh_big_m", 1), ("dw_big_m", 0), ("tail_split", 1), ("two_cta", 1)):
         _abi.set_tunable(name, v)
     return not bad, f"{n_cases} cases worst={worst:.2e} bad={bad[:3]}"
