@@ -347,6 +347,30 @@ def test_packed_ingest_bit_exact(lens, sp):
     assert torch.equal(got2.rewards, want2.rewards) and torch.equal(got2.labels, want2.labels)
 
 
+@pytest.mark.parametrize("seed", [0, 1])
+def test_packed_ingest_random_layouts_bit_exact(seed):
+    """Random rollout lists (empty, single-token and long rollouts, any count, seq_parallel 1 / 2 / 4 / 8 padding): wire form +
+    device expansion == collate_packed + to_device, every field, bit for bit."""
+    import random
+    from helpers import StubTokenizer, synthetic_rollout_examples
+    from pipelinerl_swe_b200 import collate_packed
+    from pipelinerl_swe_b200.ingest import pack_rollouts
+    rnd = random.Random(seed)
+    for case in range(20):
+        lens = [rnd.choice([0, 1, 1, 2, 3, 7, 64, 129, 700, 2049]) for _ in range(rnd.randint(1, 40))]
+        if sum(lens) == 0:
+            lens.append(5)
+        sp = rnd.choice([1, 2, 4, 8])
+        ex = synthetic_rollout_examples(lens, 152064, seed=seed * 100 + case, n_prompt=rnd.choice([0, 3, 10000]))
+        want = collate_packed(copy.deepcopy(ex), StubTokenizer(), sp).to_device(_dev())
+        got = pack_rollouts(copy.deepcopy(ex), StubTokenizer(), sp).to_device(_dev())
+        for k in ("input_ids", "labels", "attention_mask", "position_ids", "rewards", "advantages", "ref_logprobs", "old_logprobs",
+                  "group_tokens", "num_labels", "overflow", "seq_boundaries"):
+            a, b = getattr(got, k), getattr(want, k)
+            assert a.dtype == b.dtype and a.shape == b.shape and torch.equal(a, b), (k, lens, sp)
+        assert (got.is_packed, got.padding, got.model_version) == (want.is_packed, want.padding, want.model_version)
+
+
 def test_rl_step_on_ingested_batch_equals_collated_batch():
     from helpers import StubTokenizer, synthetic_rollout_examples
     from pipelinerl_swe_b200 import RLConfig, collate_packed, rl_step
