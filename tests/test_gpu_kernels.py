@@ -246,7 +246,10 @@ def test_bucket_roundtrip_bit_exact():
 
 
 # ---- host-buffer C entry point == the piecewise calls -------------------------------------------
-def test_rl_step_host_entry_matches_piecewise():
+@pytest.mark.parametrize("entropy_bonus", [0.0, 0.01])
+def test_rl_step_host_entry_matches_piecewise(entropy_bonus):
+    """entropy_bonus != 0: both run the recompute backward (an entropy gradient is never formed from the saved exponentials); the
+    host entry's dlogits scratch then spans its backward workspace and the unused saved-exponentials region."""
     from pipelinerl_swe_b200 import RLConfig, rl_step
     from pipelinerl_swe_b200 import rl as prl
     from pipelinerl_swe_b200 import host_step
@@ -254,7 +257,8 @@ def test_rl_step_host_entry_matches_piecewise():
     T = sum(lens)
     batch = synthetic_packed_batch(lens, V, seed=21)
     model = StubLM(H, V, T, seed=8).to(_dev())
-    cfgkw = dict(policy_loss="ppo", batch_size=3, kl_coef=0.1, final_kl_coef=0.1, temperature=1.0)
+    cfgkw = dict(policy_loss="ppo", batch_size=3, kl_coef=0.1, final_kl_coef=0.1, temperature=1.0, entropy_bonus=entropy_bonus,
+                 final_entropy_bonus=entropy_bonus)
     loss, stats = rl_step(model, _to_dev(batch), 0, 1, RLConfig(**cfgkw))
     loss.backward()
     step = host_step.HostRLStep(T, H, V, model.lm_head.weight.detach(), RLConfig(**cfgkw), 0, 1)
